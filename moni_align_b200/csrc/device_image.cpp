@@ -1,0 +1,323 @@
+// Exporter: decoded builder files -> HBM image.  See device_image.hpp for the layout and the
+// reference functions each table replaces.
+#include "device_image.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+
+#include "index_files.hpp"
+
+namespace moni {
+namespace {
+
+inline void put40(uint8_t* d, uint64_t v) {
+    d[0] = (uint8_t)v; d[1] = (uint8_t)(v >> 8); d[2] = (uint8_t)(v >> 16); d[3] = (uint8_t)(v >> 24); d[4] = (uint8_t)(v >> 32);
+}
+
+double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+}  // namespace
+
+void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& img) {
+    const double t0 = now_s();
+    const uint64_t R = b.R, n = b.n;
+    if (opt.max_scan < 2) throw std::runtime_error("exporter: max_scan must be >= 2");
+    for (uint64_t k = 0; k < R; ++k)
+        if (b.samples_start[k] >= (1ULL << 40) || b.samples_last[k] >= (1ULL << 40))
+            throw std::runtime_error("exporter: SA sample does not fit 40 bits");
+
+    // ---- symbol tables -----------------------------------------------------------------------
+    SymbolTables& S = img.sym;
+    memset(&S, 0, sizeof(S));
+    memset(S.tcode, 0xFF, sizeof(S.tcode));
+    {
+        std::vector<int> present;
+        for (int c = 0; c < 256; ++c) {
+            S.F[c] = b.F[c];
+            S.count[c] = b.count[c];
+            if (b.nruns[c] >= 0xFFFFFFFFULL) throw std::runtime_error("exporter: too many runs of one symbol");
+            S.nruns[c] = (uint32_t)b.nruns[c];
+            if ((b.count[c] == 0) != (b.nruns[c] == 0)) throw std::runtime_error("exporter: count/run mismatch");
+            if (b.count[c]) {
+                present.push_back(c);
+                // thr_bv::rank can never exceed the number of gaps between c-runs in a usable index
+                // (otherwise the reference itself selects past the last c-run).
+                if (b.thr[c].size() > b.nruns[c] - 1)
+                    throw std::runtime_error("exporter: more stored thresholds than gaps between runs of a symbol");
+            } else if (!b.thr[c].empty()) {
+                throw std::runtime_error("exporter: thresholds for an absent symbol");
+            }
+        }
+        std::vector<int> by_runs = present;
+        std::stable_sort(by_runs.begin(), by_runs.end(), [&](int x, int y) { return b.nruns[x] > b.nruns[y]; });
+        if (by_runs.size() > 4) by_runs.resize(4);
+        std::sort(by_runs.begin(), by_runs.end());
+        img.hdr.n_table_syms = (uint32_t)by_runs.size();
+        for (size_t i = 0; i < by_runs.size(); ++i) {
+            S.tcode[by_runs[i]] = (uint8_t)i;
+            img.hdr.table_syms[i] = (uint8_t)by_runs[i];
+        }
+        uint64_t sb = 0, cb = 0;
+        for (int c = 0; c < 256; ++c) {
+            S.slot_base[c] = sb;
+            S.crun_base[c] = cb;
+            if (b.count[c]) { sb += b.nruns[c] + 1; cb += b.nruns[c]; }
+        }
+        img.slots.assign(sb, GapSlot{0, 0, 0, 0});
+        img.crun_row.assign(cb, 0);
+    }
+    const uint8_t* tcode = S.tcode;
+
+    // ---- rows: cut runs longer than kMaxPiece, then balance ------------------------------------
+    std::vector<uint64_t> pos;      // row starts
+    std::vector<uint32_t> run;      // run of each row
+    pos.reserve(R + R / 4 + 16);
+    run.reserve(R + R / 4 + 16);
+    for (uint64_t k = 0; k < R; ++k)
+        for (uint64_t s = b.starts[k]; s < b.starts[k + 1]; s += kMaxPiece) { pos.push_back(s); run.push_back((uint32_t)k); }
+
+    std::vector<uint64_t> cuts;     // absolute positions of new row starts found in one round
+    uint32_t worst = 0;
+    for (uint32_t round = 0;; ++round) {
+        const uint64_t nr = pos.size();
+        cuts.clear();
+        worst = 0;
+        uint64_t seen[4] = {0, 0, 0, 0};   // # of the table symbol before the current row
+        uint64_t q[4] = {0, 0, 0, 0};      // first row whose start is > the image start of the current row
+        for (uint64_t i = 0; i < nr; ++i) {
+            const uint8_t tc = tcode[b.heads[run[i]]];
+            if (tc == 0xFF) continue;
+            const uint64_t len = (i + 1 < nr ? pos[i + 1] : n) - pos[i];
+            const uint64_t pi = S.F[b.heads[run[i]]] + seen[tc];
+            seen[tc] += len;
+            uint64_t t = q[tc];
+            while (t < nr && pos[t] <= pi) ++t;
+            uint32_t inside = 0;
+            while (t < nr && pos[t] < pi + len) {
+                ++inside;
+                if (inside % opt.max_scan == 0 && round < opt.max_rounds) cuts.push_back(pos[i] + (pos[t] - pi));
+                ++t;
+            }
+            worst = std::max(worst, inside);
+            q[tc] = t;
+        }
+        if (opt.verbose)
+            fprintf(stderr, "[moni-gpu] balance round %u: rows %llu, new cuts %llu, widest image %u rows\n", round,
+                    (unsigned long long)nr, (unsigned long long)cuts.size(), worst);
+        if (cuts.empty()) break;
+        // merge the (sorted, distinct, strictly interior) cuts into the rows
+        std::vector<uint64_t> npos;
+        std::vector<uint32_t> nrun;
+        npos.reserve(nr + cuts.size());
+        nrun.reserve(nr + cuts.size());
+        size_t ci = 0;
+        for (uint64_t i = 0; i < nr; ++i) {
+            npos.push_back(pos[i]);
+            nrun.push_back(run[i]);
+            const uint64_t end = (i + 1 < nr ? pos[i + 1] : n);
+            while (ci < cuts.size() && cuts[ci] < end) {
+                if (cuts[ci] > npos.back()) { npos.push_back(cuts[ci]); nrun.push_back(run[i]); }
+                ++ci;
+            }
+        }
+        pos.swap(npos);
+        run.swap(nrun);
+    }
+    const uint64_t nr = pos.size();
+    if (nr >= 0xFFFFFFF0ULL) throw std::runtime_error("exporter: too many rows");
+    img.hdr.n = n;
+    img.hdr.R = R;
+    img.hdr.n_rows = nr;
+    img.hdr.max_scan = worst;
+    img.hdr.init_sample = (b.samples_last[R - 1] + 1) % n;
+    img.hdr.init_row = (uint32_t)(nr - 1);
+    img.hdr.init_off = (uint32_t)(n - 1 - pos[nr - 1]);
+
+    // ---- fill rows -----------------------------------------------------------------------------
+    img.rows.assign(nr + 1, MoveRow{});
+    img.row_pos.resize(nr + 1);
+    for (uint64_t i = 0; i < nr; ++i) img.row_pos[i] = pos[i];
+    img.row_pos[nr] = n;
+    const int nts = (int)img.hdr.n_table_syms;
+    {
+        // backward pass: row of the first piece of the next c-run after row i (for dist_dn)
+        uint64_t nxt[4] = {~0ULL, ~0ULL, ~0ULL, ~0ULL};
+        // store the clipped distance directly into the row while walking backwards
+        for (uint64_t ii = nr; ii-- > 0;) {
+            MoveRow& r = img.rows[ii];
+            const uint8_t h = b.heads[run[ii]];
+            const uint8_t th = tcode[h];
+            if (th != 0xFF) {
+                for (int c = 0, s = 0; c < nts; ++c) {
+                    if (c == th) continue;
+                    const uint64_t d = nxt[c] == ~0ULL ? kFar : nxt[c] - ii;
+                    r.dist_dn[s++] = (uint8_t)std::min<uint64_t>(d, kFar);
+                }
+                const bool first_piece = (ii == 0 || run[ii - 1] != run[ii]);
+                if (first_piece) nxt[th] = ii;
+            }
+        }
+    }
+    {
+        uint64_t seen[4] = {0, 0, 0, 0};
+        uint64_t q[4] = {0, 0, 0, 0};
+        uint64_t jc[256];                 // # c-runs that ended before the current run
+        uint64_t cum[256];                // # c before the current run
+        uint64_t last_piece[4] = {~0ULL, ~0ULL, ~0ULL, ~0ULL};
+        memset(jc, 0, sizeof(jc));
+        memset(cum, 0, sizeof(cum));
+        for (uint64_t i = 0; i < nr; ++i) {
+            MoveRow& r = img.rows[i];
+            const uint32_t k = run[i];
+            const uint8_t h = b.heads[k];
+            const uint8_t th = tcode[h];
+            const uint64_t len = img.row_pos[i + 1] - pos[i];
+            const bool first_piece = (i == 0 || run[i - 1] != k);
+            const bool last_piece_of_run = (i + 1 == nr || run[i + 1] != k);
+            r.len = (uint16_t)len;
+            r.head = h;
+            r.flags = th == 0xFF ? kRowSlow : 0;
+            put40(r.s_start, b.samples_start[k]);
+            put40(r.s_last, b.samples_last[k]);
+            if (first_piece) {
+                // general-path tables: c-run j of symbol h starts here
+                const uint64_t j = jc[h];
+                img.crun_row[S.crun_base[h] + j] = (uint32_t)i;
+                GapSlot& g = img.slots[S.slot_base[h] + j];
+                g.thr = j == 0 ? 0 : (j - 1 < b.thr[h].size() ? b.thr[h][j - 1] : kThrInf);
+                g.s_start = b.samples_start[k];
+                g.cum = cum[h];
+                GapSlot& g1 = img.slots[S.slot_base[h] + j + 1];
+                g1.s_last_prev = b.samples_last[k];
+            }
+            if (th != 0xFF) {
+                const uint64_t pi = S.F[h] + seen[th];
+                seen[th] += len;
+                uint64_t t = q[th];
+                while (t < nr && pos[t] <= pi) ++t;
+                q[th] = t;                    // images of later h-rows start further right
+                r.dest_row = (uint32_t)(t - 1);
+                r.dest_off = (uint16_t)(pi - pos[t - 1]);
+                for (int c = 0, s = 0; c < nts; ++c) {
+                    if (c == th) continue;
+                    const uint8_t sym = img.hdr.table_syms[c];
+                    const uint64_t j = jc[sym];
+                    const uint64_t T = j == 0 ? 0 : (j - 1 < b.thr[sym].size() ? b.thr[sym][j - 1] : kThrInf);
+                    const uint64_t rel = T <= pos[i] ? 0 : std::min<uint64_t>(T - pos[i], len);
+                    r.t_rel[s] = (uint16_t)rel;
+                    const uint64_t d = last_piece[c] == ~0ULL ? kFar : i - last_piece[c];
+                    r.dist_up[s] = (uint8_t)std::min<uint64_t>(d, kFar);
+                    ++s;
+                }
+            }
+            if (last_piece_of_run) {
+                jc[h] += 1;
+                cum[h] = cum[h] + (b.starts[k + 1] - b.starts[k]);
+                if (th != 0xFF) last_piece[th] = i;
+            }
+        }
+        for (int c = 0; c < 256; ++c) {
+            if (!b.count[c]) continue;
+            if (jc[c] != b.nruns[c] || cum[c] != b.count[c]) throw std::runtime_error("exporter: per-symbol totals mismatch");
+            GapSlot& g = img.slots[S.slot_base[c] + b.nruns[c]];
+            g.thr = kThrInf;              // after the last c-run the reference can only jump up
+            g.cum = b.count[c];
+        }
+    }
+    // sentinel row = "pos == n": never scanned past (len 1), always general path
+    MoveRow& z = img.rows[nr];
+    z.len = 1;
+    z.flags = kRowSlow;
+    if (opt.verbose)
+        fprintf(stderr, "[moni-gpu] move table: n %llu, runs %llu, rows %llu (+%.1f%%), widest image %u rows, %.2f s\n",
+                (unsigned long long)n, (unsigned long long)R, (unsigned long long)nr, 100.0 * (double)(nr - R) / (double)R,
+                worst, now_s() - t0);
+}
+
+void build_grammar_table(const FlatSlp& g, const ExportOptions& opt, HostImage& img) {
+    const double t0 = now_s();
+    const uint64_t A = g.alph_size, NR = g.num_rules;
+    const uint64_t L = std::max<uint32_t>(opt.leaf_len, 1);
+    if (g.text_len == 0) throw std::runtime_error("exporter: empty grammar");
+    img.hdr.text_len = g.text_len;
+    img.hdr.leaf_len = (uint32_t)L;
+    img.hdr.pool_shift = 3;
+    const uint64_t align = 1ULL << img.hdr.pool_shift;
+    auto explen = [&](uint32_t v) -> uint64_t { return v < A ? 1 : g.explen[v - A]; };
+    if (NR == 0 && (g.text_len != 1 || g.start_var >= A)) throw std::runtime_error("exporter: grammar without rules");
+
+    std::vector<uint32_t> ref(NR + A, 0xFFFFFFFFu);   // child reference of every variable once assigned
+    std::vector<uint32_t> order;                        // internal variables in breadth-first order
+    std::vector<uint8_t>& pool = img.pool;
+    pool.clear();
+    std::vector<uint32_t> stack;
+    auto leaf_ref = [&](uint32_t v) -> uint32_t {
+        if (ref[v] != 0xFFFFFFFFu) return ref[v];
+        while (pool.size() % align) pool.push_back(0);
+        const uint64_t off = pool.size() >> img.hdr.pool_shift;
+        if (off >= kLeafBit) throw std::runtime_error("exporter: literal pool exceeds the addressable range; lower leaf_len");
+        stack.clear();
+        stack.push_back(v);
+        while (!stack.empty()) {
+            const uint32_t x = stack.back();
+            stack.pop_back();
+            if (x < A) { pool.push_back(g.alph[x]); continue; }
+            stack.push_back(g.right[x - A]);
+            stack.push_back(g.left[x - A]);
+        }
+        ref[v] = kLeafBit | (uint32_t)off;
+        return ref[v];
+    };
+    auto child_ref = [&](uint32_t v) -> uint32_t {
+        if (explen(v) <= L) return leaf_ref(v);
+        if (ref[v] == 0xFFFFFFFFu) {
+            if (order.size() >= kLeafBit - 1) throw std::runtime_error("exporter: too many grammar nodes");
+            ref[v] = (uint32_t)order.size();
+            order.push_back(v);
+        }
+        return ref[v];
+    };
+    img.hdr.root_ref = child_ref(g.start_var);
+    img.nodes.clear();
+    for (size_t i = 0; i < order.size(); ++i) {     // order grows while we walk it: breadth-first
+        const uint32_t v = order[i];
+        const uint32_t lv = g.left[v - A], rv = g.right[v - A];
+        if (explen(lv) + explen(rv) != explen(v)) throw std::runtime_error("exporter: inconsistent expansion lengths");
+        SlpNode nd;
+        nd.left = child_ref(lv);
+        nd.right = child_ref(rv);
+        nd.left_len = explen(lv);
+        img.nodes.push_back(nd);
+    }
+    for (int i = 0; i < 32; ++i) pool.push_back(0);   // slack so 16-byte block loads never run off the end
+    img.hdr.n_nodes = img.nodes.size();
+    img.hdr.pool_bytes = pool.size();
+    // depth = nodes on the longest root-to-literal path.  A shared variable can be referenced from a
+    // later node, so relax until stable (a couple of sweeps in practice).
+    uint32_t depth_max = 0;
+    {
+        std::vector<uint16_t> depth(img.nodes.size(), 1);
+        for (bool changed = true; changed;) {
+            changed = false;
+            for (size_t i = 0; i < img.nodes.size(); ++i) {
+                const uint16_t d = (uint16_t)(depth[i] + 1);
+                const SlpNode& nd = img.nodes[i];
+                if (!(nd.left & kLeafBit) && depth[nd.left] < d) { depth[nd.left] = d; changed = changed || nd.left < i; }
+                if (!(nd.right & kLeafBit) && depth[nd.right] < d) { depth[nd.right] = d; changed = changed || nd.right < i; }
+            }
+        }
+        for (uint16_t d : depth) depth_max = std::max<uint32_t>(depth_max, d);
+    }
+    img.hdr.slp_depth_max = depth_max;
+    if (opt.verbose)
+        fprintf(stderr, "[moni-gpu] grammar table: text %llu, rules %llu -> %llu nodes (depth <= %u) + %.1f MB literals (leaf_len %u), %.2f s\n",
+                (unsigned long long)g.text_len, (unsigned long long)NR, (unsigned long long)img.nodes.size(), depth_max,
+                (double)pool.size() / 1e6, (unsigned)L, now_s() - t0);
+}
+
+}  // namespace moni

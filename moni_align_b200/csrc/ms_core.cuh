@@ -1,0 +1,258 @@
+// Per-read arithmetic of the two passes over the HBM image (device_image.hpp), written once as
+// host+device inline functions: the CUDA kernels (kernels.cu) call them per thread, and the CPU
+// test harness (tests/host_sim.cpp) compiles the very same functions with g++ so the logic can be
+// checked against the oracle on a machine without a GPU.  The host build is TEST-ONLY: the shipped
+// library has no CPU execution path.
+//
+// Reference behaviour being reproduced bit for bit:
+//   pass 1  ms_pointers<>::_query                      include/ms/ms_pointers.hpp:455-511
+//   pass 2  ms_c::matching_statistics length loop      src/matching_statistics.cpp:246-255
+//           mems_c::maxrimal_exact_matches MEM rule    src/mems.cpp:247-259
+#pragma once
+#include <cstdint>
+
+#include "device_image.hpp"
+
+#if defined(__CUDACC__)
+#define MONI_HD __host__ __device__ __forceinline__
+#else
+#define MONI_HD inline
+#endif
+
+namespace moni {
+
+struct ImageView {
+    const MoveRow* rows = nullptr;
+    const uint64_t* row_pos = nullptr;
+    const uint32_t* crun_row = nullptr;
+    const GapSlot* slots = nullptr;
+    const SlpNode* nodes = nullptr;
+    const uint8_t* pool = nullptr;
+    const SymbolTables* sym = nullptr;
+    ImageHeader hdr;
+};
+
+// Event counters of SURVEY.md 8(d) (B, J, S, D, C) plus the image-specific ones.
+struct Counters {
+    unsigned long long bases, jumps, restarts, restart_depth, chars, scan_rows, general_steps, descents;
+};
+
+// ---- a MoveRow held in registers ---------------------------------------------------------------
+struct RowRegs {
+    uint32_t w[8];
+    MONI_HD uint32_t dest_row() const { return w[0]; }
+    MONI_HD uint32_t dest_off() const { return w[1] & 0xFFFFu; }
+    MONI_HD uint32_t len() const { return w[1] >> 16; }
+    MONI_HD uint32_t head() const { return (w[3] >> 16) & 0xFFu; }
+    MONI_HD uint32_t flags() const { return w[3] >> 24; }
+    MONI_HD uint32_t t_rel(int s) const {
+        const uint64_t t = (uint64_t)w[2] | ((uint64_t)(w[3] & 0xFFFFu) << 32);
+        return (uint32_t)(t >> (16 * s)) & 0xFFFFu;
+    }
+    MONI_HD uint64_t s_start() const { return (uint64_t)w[4] | ((uint64_t)(w[5] & 0xFFu) << 32); }
+    MONI_HD uint64_t s_last() const { return (uint64_t)(w[5] >> 8) | ((uint64_t)(w[6] & 0xFFFFu) << 24); }
+    MONI_HD uint32_t dist_up(int s) const {
+        const uint32_t d = (w[6] >> 16) | ((w[7] & 0xFFu) << 16);
+        return (d >> (8 * s)) & 0xFFu;
+    }
+    MONI_HD uint32_t dist_dn(int s) const { return ((w[7] >> 8) >> (8 * s)) & 0xFFu; }
+};
+
+MONI_HD RowRegs load_row(const MoveRow* rows, uint64_t i) {
+    RowRegs r;
+#if defined(__CUDA_ARCH__)
+    const uint4* p = reinterpret_cast<const uint4*>(rows + i);
+    const uint4 a = __ldg(p), b = __ldg(p + 1);
+    r.w[0] = a.x; r.w[1] = a.y; r.w[2] = a.z; r.w[3] = a.w;
+    r.w[4] = b.x; r.w[5] = b.y; r.w[6] = b.z; r.w[7] = b.w;
+#else
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(rows + i);
+    for (int k = 0; k < 8; ++k) r.w[k] = p[k];
+#endif
+    return r;
+}
+
+template <typename T>
+MONI_HD T ld(const T* p) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(p);
+#else
+    return *p;
+#endif
+}
+
+// ---- exact general path (any symbol, any position incl. pos == n) ------------------------------
+// largest i in [0, n_rows] with row_pos[i] <= pos   (pos <= n; pos == n gives the sentinel row)
+MONI_HD uint64_t locate_row(const ImageView& v, uint64_t pos) {
+    uint64_t lo = 0, hi = v.hdr.n_rows;       // invariant: row_pos[lo] <= pos, answer in [lo, hi]
+    while (lo < hi) {
+        const uint64_t mid = lo + (hi - lo + 1) / 2;
+        if (ld(v.row_pos + mid) <= pos) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// number of entries of a[0..cnt) that are < key
+MONI_HD uint64_t count_less(const uint32_t* a, uint64_t cnt, uint64_t key) {
+    uint64_t lo = 0, hi = cnt;
+    while (lo < hi) {
+        const uint64_t mid = lo + (hi - lo) / 2;
+        if ((uint64_t)ld(a + mid) < key) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// One iteration of ms_pointers.hpp:466-507 on an absolute BWT position.
+MONI_HD void general_step(const ImageView& v, uint8_t c, uint64_t& pos, uint64_t& sample, bool& jumped) {
+    const SymbolTables& S = *v.sym;
+    jumped = false;
+    const uint64_t n_c = ld(&S.count[c]);
+    const uint64_t Fc = ld(&S.F[c]);
+    if (n_c == 0) {                                  // :470-475  rank() of an absent letter is 0
+        sample = 0;
+        pos = Fc;
+        return;
+    }
+    const uint64_t i = locate_row(v, pos);
+    const uint32_t* cr = v.crun_row + ld(&S.crun_base[c]);
+    const GapSlot* sl = v.slots + ld(&S.slot_base[c]);
+    const uint64_t nruns = ld(&S.nruns[c]);
+    if (pos < v.hdr.n && v.rows[i].head == c) {      // :476-481
+        const uint64_t j = count_less(cr, nruns, i + 1) - 1;      // the c-run whose first piece is at or before row i
+        const uint64_t first = ld(cr + j);
+        const uint64_t rank = ld(&sl[j].cum) + (pos - ld(v.row_pos + first));
+        sample = sample - 1;
+        pos = Fc + rank;
+        return;
+    }
+    jumped = true;                                   // :482-505
+    const uint64_t jc = pos >= v.hdr.n ? nruns : count_less(cr, nruns, i);
+    const uint64_t thr = ld(&sl[jc].thr);
+    const uint64_t cum = ld(&sl[jc].cum);
+    if (pos < thr) {                                 // rnk_c.first > thresholds.rank(pos + 1, c)
+        sample = ld(&sl[jc].s_last_prev);
+        pos = Fc + cum - 1;
+    } else {
+        sample = ld(&sl[jc].s_start);
+        pos = Fc + cum;
+    }
+}
+
+// ---- pass 1 -------------------------------------------------------------------------------------
+struct ScanState {
+    uint32_t cur;       // row
+    uint32_t off;       // offset inside the row (may exceed the row length until scanned forward)
+    uint64_t sample;
+};
+
+MONI_HD void scan_init(const ImageView& v, ScanState& s) {
+    s.cur = v.hdr.init_row;
+    s.off = v.hdr.init_off;
+    s.sample = v.hdr.init_sample;
+}
+
+// Consumes one symbol; on return s.sample is the pointer to store.  `tcode` is the 256-byte symbol
+// class table (shared memory on the device).
+MONI_HD void scan_step(const ImageView& v, const uint8_t* tcode, uint8_t c, ScanState& s, Counters* cnt) {
+    RowRegs row = load_row(v.rows, s.cur);
+    while (s.off >= row.len()) {                     // forward scan after the previous LF (bounded by balancing)
+        s.off -= row.len();
+        s.cur += 1;
+        row = load_row(v.rows, s.cur);
+        if (cnt) cnt->scan_rows++;
+    }
+    const uint32_t tc = tcode[c];
+    bool general = (tc == 0xFFu) || (row.flags() & kRowSlow);
+    if (!general) {
+        if (row.head() == c) {                       // match: rle_string::rank via the row's LF image
+            s.sample -= 1;
+            s.off += row.dest_off();
+            s.cur = row.dest_row();
+            return;
+        }
+        const uint32_t th = tcode[row.head()];
+        const int slot = (int)(tc < th ? tc : tc - 1);
+        const bool up = s.off < row.t_rel(slot);
+        const uint32_t d = up ? row.dist_up(slot) : row.dist_dn(slot);
+        if (d != kFar) {
+            const RowRegs q = load_row(v.rows, up ? (uint64_t)s.cur - d : (uint64_t)s.cur + d);
+            s.sample = up ? q.s_last() : q.s_start();
+            s.off = q.dest_off() + (up ? q.len() - 1 : 0);
+            s.cur = q.dest_row();
+            if (cnt) cnt->jumps++;
+            return;
+        }
+        general = true;
+    }
+    uint64_t pos = ld(v.row_pos + s.cur) + s.off;
+    bool jumped;
+    general_step(v, c, pos, s.sample, jumped);
+    const uint64_t i = locate_row(v, pos);
+    s.cur = (uint32_t)i;
+    s.off = (uint32_t)(pos - ld(v.row_pos + i));
+    if (cnt) { cnt->general_steps++; cnt->jumps += jumped ? 1 : 0; }
+}
+
+// ---- pass 2 -------------------------------------------------------------------------------------
+// Literal bytes of the text from position tp: returns a pointer to T[tp] inside the pool and sets
+// `rem` to how many consecutive text bytes are available there.  Replaces PlainSlp::charAt
+// (thirdparty/ShapedSlp/PlainSlp.hpp:101-126): one descent serves a whole literal block.
+MONI_HD const uint8_t* text_block(const ImageView& v, uint64_t tp, uint64_t& rem, Counters* cnt) {
+    uint32_t ref = v.hdr.root_ref;
+    uint64_t span = v.hdr.text_len, p = tp;
+    while (!(ref & kLeafBit)) {
+#if defined(__CUDA_ARCH__)
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(v.nodes + ref));
+        const uint32_t l = q.x, r = q.y;
+        const uint64_t ll = (uint64_t)q.z | ((uint64_t)q.w << 32);
+#else
+        const uint32_t l = v.nodes[ref].left, r = v.nodes[ref].right;
+        const uint64_t ll = v.nodes[ref].left_len;
+#endif
+        if (p < ll) { ref = l; span = ll; } else { p -= ll; span -= ll; ref = r; }
+        if (cnt) cnt->restart_depth++;
+    }
+    rem = span - p;
+    if (cnt) cnt->descents++;
+    return v.pool + ((uint64_t)(ref & ~kLeafBit) << v.hdr.pool_shift) + p;
+}
+
+// The length loop for one read.  ptr[] are the pass-1 pointers of this read.  Writes len[i] (if
+// len != nullptr) and returns the number of MEM records; records are written to mem_out (packed
+// (i << 32) | len) when mem_out != nullptr.
+MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, uint32_t* len,
+                              uint64_t* mem_out, Counters* cnt) {
+    const uint64_t N = v.hdr.text_len;
+    uint64_t l = 0, prev_ptr = 0, prev_len = 0;
+    uint32_t n_mems = 0;
+    for (uint64_t i = 0; i < m; ++i) {
+        const uint64_t pos = ptr[i];
+        if (i == 0 || pos != prev_ptr + 1) {
+            if (cnt) cnt->restarts++;
+            bool go = true;
+            while (go && i + l < m && pos + l < N) {             // u64 adds wrap exactly as in the reference
+                uint64_t rem;
+                const uint8_t* t = text_block(v, pos + l, rem, cnt);
+                uint64_t k = 0;
+                while (k < rem && i + l < m) {
+                    if (cnt) cnt->chars++;
+                    if (ld(t + k) != seq[i + l]) { go = false; break; }
+                    ++k;
+                    ++l;
+                }
+                if (k < rem) go = false;                        // read exhausted or mismatch inside the block
+            }
+        }
+        if (len) len[i] = (uint32_t)l;
+        if (i == 0 || l >= prev_len) {                           // src/mems.cpp:257-258
+            if (mem_out) mem_out[n_mems] = (i << 32) | l;
+            ++n_mems;
+        }
+        prev_len = l;
+        prev_ptr = pos;
+        l = l ? l - 1 : 0;
+    }
+    return n_mems;
+}
+
+}  // namespace moni

@@ -1,0 +1,313 @@
+"""TEST INFRASTRUCTURE -- NOT PART OF THE PRODUCT.
+
+Python side of the CPU oracle: an independent numpy reader of the reference's index files
+(`<idx>.thrbv.ms`, `<idx>.plain.slp`; layouts: SURVEY.md Appendix B, i.e. the serialize() methods at
+/root/reference include/ms/ms_pointers.hpp:279-297, thirdparty/r-index/internal/rle_string.hpp:347-359,
+thirdparty/sdsl-lite/include/sdsl/{int_vector,sd_vector,select_support_mcl,wt_pc,wt_helper}.hpp,
+thirdparty/ShapedSlp/PlainSlp.hpp:322-335) plus a ctypes binding of oracle/ms_oracle.c, the C
+restatement of the per-read algorithm.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module.  The product (moni_align_b200) never does.
+
+Pinned: tests/test_oracle_golden.py checks this oracle byte-for-byte against outputs of the UNMODIFIED
+reference binaries (oracle/_ref/bin/ms, mems) committed under tests/golden/.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(HERE, "_build", "libms_oracle.so")
+_SRC = os.path.join(HERE, "ms_oracle.c")
+
+
+def build(force: bool = False) -> str:
+    """gcc -O2 the C restatement into oracle/_build/libms_oracle.so."""
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(_SRC):
+        os.makedirs(os.path.dirname(_SO), exist_ok=True)
+        subprocess.check_call(["gcc", "-O2", "-std=c99", "-shared", "-fPIC", "-o", _SO, _SRC])
+    return _SO
+
+
+# ----------------------------------------------------------------------------- file decoding
+class _Cur:
+    def __init__(self, path: str):
+        self.buf = np.fromfile(path, dtype=np.uint8)
+        self.off = 0
+        self.path = path
+
+    def u64(self) -> int:
+        v = int.from_bytes(self.buf[self.off:self.off + 8].tobytes(), "little")
+        self.off += 8
+        return v
+
+    def u32(self) -> int:
+        v = int.from_bytes(self.buf[self.off:self.off + 4].tobytes(), "little")
+        self.off += 4
+        return v
+
+    def u8(self) -> int:
+        v = int(self.buf[self.off])
+        self.off += 1
+        return v
+
+    def raw(self, k: int) -> np.ndarray:
+        v = self.buf[self.off:self.off + k]
+        if v.shape[0] != k:
+            raise ValueError(f"{self.path}: truncated")
+        self.off += k
+        return v
+
+    def words(self, k: int) -> np.ndarray:
+        return np.frombuffer(self.raw(8 * k).tobytes(), dtype="<u8")
+
+
+def _int_vector(c: _Cur, fixed_width: int = 0):
+    bits = c.u64()
+    width = fixed_width if fixed_width else c.u8()
+    return bits, width, c.words((bits + 63) >> 6)
+
+
+def _unpack(bits: int, width: int, words: np.ndarray) -> np.ndarray:
+    m = bits // width if width else 0
+    if m == 0:
+        return np.zeros(0, dtype=np.uint64)
+    if width == 64:
+        return words[:m].astype(np.uint64)
+    w = np.concatenate([words, np.zeros(1, dtype=np.uint64)])
+    b = np.arange(m, dtype=np.uint64) * np.uint64(width)
+    wi = (b >> np.uint64(6)).astype(np.int64)
+    sh = b & np.uint64(63)
+    lo = w[wi] >> sh
+    hi = np.where(sh == 0, np.uint64(0), w[wi + 1] << ((np.uint64(64) - sh) & np.uint64(63)))
+    return (lo | hi) & np.uint64((1 << width) - 1)
+
+
+def _bit_positions(bits: int, words: np.ndarray) -> np.ndarray:
+    b = np.unpackbits(words.view(np.uint8), bitorder="little")[:bits]
+    return np.flatnonzero(b).astype(np.uint64)
+
+
+def _skip_select(c: _Cur) -> None:
+    arg_cnt = c.u64()
+    if not arg_cnt:
+        return
+    _int_vector(c)
+    _int_vector(c, 1)
+    for _ in range((arg_cnt + 4095) >> 12):
+        _int_vector(c)
+
+
+def _sd_vector(c: _Cur) -> np.ndarray:
+    c.u64()                      # size
+    wl = c.u8()
+    lb, lw, lwords = _int_vector(c)
+    hb, _, hwords = _int_vector(c, 1)
+    _skip_select(c)
+    _skip_select(c)
+    low = _unpack(lb, lw, lwords)
+    ones = _bit_positions(hb, hwords)[: low.shape[0]]
+    idx = np.arange(low.shape[0], dtype=np.uint64)
+    return ((ones - idx) << np.uint64(wl)) | low
+
+
+def _sparse_sd(c: _Cur):
+    u = c.u64()
+    if u == 0:
+        return 0, np.zeros(0, dtype=np.uint64)
+    return u, _sd_vector(c)
+
+
+def _wt_huff(c: _Cur) -> np.ndarray:
+    size = c.u64()
+    c.u64()                      # sigma
+    bvbits, _, bvwords = _int_vector(c, 1)
+    _int_vector(c, 64)
+    _skip_select(c)
+    _skip_select(c)
+    n_nodes = c.u64()
+    nodes = []
+    for _ in range(n_nodes):
+        raw = c.raw(22).tobytes()
+        nodes.append((int.from_bytes(raw[0:8], "little"), int.from_bytes(raw[18:20], "little"),
+                      int.from_bytes(raw[20:22], "little")))
+    c_to_leaf = np.frombuffer(c.raw(512).tobytes(), dtype="<u2")
+    c.raw(256 * 8)
+    leaf_sym = {int(l): s for s, l in enumerate(c_to_leaf) if l != 0xFFFF}
+    bv = np.unpackbits(bvwords.view(np.uint8), bitorder="little")[:bvbits]
+
+    def decode(v: int, count: int) -> np.ndarray:
+        pos, c0, c1 = nodes[v]
+        if c0 == 0xFFFF:
+            return np.full(count, leaf_sym[v], dtype=np.uint8)
+        bits = bv[pos:pos + count]
+        n1 = int(bits.sum())
+        out = np.empty(count, dtype=np.uint8)
+        out[bits == 0] = decode(c0, count - n1)
+        out[bits == 1] = decode(c1, n1)
+        return out
+
+    return decode(0, size) if size else np.zeros(0, dtype=np.uint8)
+
+
+def read_thrbv_ms(path: str) -> dict:
+    c = _Cur(path)
+    d: dict = {"terminator_position": c.u64()}
+    if c.u64() != 256:
+        raise ValueError("F size")
+    d["F"] = c.words(256).astype(np.uint64)
+    n, R, B = c.u64(), c.u64(), c.u64()
+    d.update(n=n, R=R, B=B)
+    _, d["run_marks"] = _sparse_sd(c)
+    per_letter = []
+    count = np.zeros(256, dtype=np.uint64)
+    for s in range(256):
+        u, ones = _sparse_sd(c)
+        count[s] = u
+        per_letter.append(ones)
+    heads = _wt_huff(c)
+    lens = np.zeros(R, dtype=np.uint64)
+    for s in range(256):
+        if per_letter[s].shape[0]:
+            ends = per_letter[s].astype(np.int64)
+            lens[heads == s] = np.diff(np.concatenate([[-1], ends])).astype(np.uint64)
+    starts = np.zeros(R + 1, dtype=np.uint64)
+    np.cumsum(lens, out=starts[1:])
+    if int(starts[-1]) != n:
+        raise ValueError("run lengths do not sum to n")
+    d.update(heads=heads, lens=lens, starts=starts, count=count)
+    d["samples_last"] = _unpack(*_int_vector(c)).astype(np.uint64)
+    thr = []
+    for s in range(256):
+        thr.append(_sparse_sd(c)[1])
+    d["thr"] = thr
+    d["samples_start"] = _unpack(*_int_vector(c)).astype(np.uint64)
+    if c.off != c.buf.shape[0]:
+        raise ValueError(f"{path}: {c.buf.shape[0] - c.off} trailing bytes")
+    return d
+
+
+def read_plain_slp(path: str) -> dict:
+    c = _Cur(path)
+    d: dict = {"text_len": c.u64(), "num_rules": c.u64(), "start_var": c.u32(), "alph_size": c.u64()}
+    d["alph"] = c.raw(d["alph_size"]).copy()
+    d["left"] = _unpack(*_int_vector(c)).astype(np.uint32)
+    d["right"] = _unpack(*_int_vector(c)).astype(np.uint32)
+    d["explen"] = _unpack(*_int_vector(c)).astype(np.uint64)
+    if c.off != c.buf.shape[0]:
+        raise ValueError(f"{path}: trailing bytes")
+    return d
+
+
+# ----------------------------------------------------------------------------- ctypes binding
+def _p(a: np.ndarray, t):
+    return a.ctypes.data_as(ctypes.POINTER(t))
+
+
+class OracleIndex:
+    """The CPU oracle over one index prefix (`prefix.thrbv.ms`, `prefix.plain.slp`)."""
+
+    def __init__(self, prefix: str):
+        self.lib = ctypes.CDLL(build())
+        L = self.lib
+        L.oracle_new.restype = ctypes.c_void_p
+        u64p, u8p, u32p = ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint8), ctypes.POINTER(ctypes.c_uint32)
+        L.oracle_free.argtypes = [ctypes.c_void_p]
+        L.oracle_set_bwt.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, u64p, u8p, u64p, u64p, u64p, u64p, u64p]
+        L.oracle_set_slp.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint64, u8p, u32p, u32p, u64p]
+        L.oracle_ms_batch.argtypes = [ctypes.c_void_p, u8p, u64p, ctypes.c_uint64, u64p, u64p]
+        L.oracle_mems_batch.argtypes = [ctypes.c_void_p, u8p, u64p, ctypes.c_uint64, u64p, u64p, u64p]
+        L.oracle_counters.argtypes = [ctypes.c_void_p, u64p, ctypes.c_int]
+        L.oracle_char_at.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
+        L.oracle_char_at.restype = ctypes.c_uint8
+        self.bwt = read_thrbv_ms(prefix + ".thrbv.ms")
+        self.slp = read_plain_slp(prefix + ".plain.slp")
+        b, s = self.bwt, self.slp
+        self._keep = dict(
+            F=np.ascontiguousarray(b["F"], dtype=np.uint64), heads=np.ascontiguousarray(b["heads"], dtype=np.uint8),
+            starts=np.ascontiguousarray(b["starts"], dtype=np.uint64),
+            ss=np.ascontiguousarray(b["samples_start"], dtype=np.uint64), sl=np.ascontiguousarray(b["samples_last"], dtype=np.uint64),
+            thr_vals=np.ascontiguousarray(np.concatenate(b["thr"] + [np.zeros(1, dtype=np.uint64)]), dtype=np.uint64),
+            thr_off=np.zeros(257, dtype=np.uint64),
+            alph=np.ascontiguousarray(s["alph"], dtype=np.uint8), left=np.ascontiguousarray(s["left"], dtype=np.uint32),
+            right=np.ascontiguousarray(s["right"], dtype=np.uint32), explen=np.ascontiguousarray(s["explen"], dtype=np.uint64))
+        k = self._keep
+        np.cumsum(np.array([t.shape[0] for t in b["thr"]], dtype=np.uint64), out=k["thr_off"][1:])
+        self.h = ctypes.c_void_p(L.oracle_new())
+        L.oracle_set_bwt(self.h, b["n"], b["R"], _p(k["F"], ctypes.c_uint64), _p(k["heads"], ctypes.c_uint8),
+                         _p(k["starts"], ctypes.c_uint64), _p(k["ss"], ctypes.c_uint64), _p(k["sl"], ctypes.c_uint64),
+                         _p(k["thr_vals"], ctypes.c_uint64), _p(k["thr_off"], ctypes.c_uint64))
+        L.oracle_set_slp(self.h, s["text_len"], s["num_rules"], s["start_var"], s["alph_size"], _p(k["alph"], ctypes.c_uint8),
+                         _p(k["left"], ctypes.c_uint32), _p(k["right"], ctypes.c_uint32), _p(k["explen"], ctypes.c_uint64))
+
+    def __del__(self):
+        try:
+            self.lib.oracle_free(self.h)
+        except Exception:
+            pass
+
+    @property
+    def n(self) -> int:
+        return self.bwt["n"]
+
+    @property
+    def text_len(self) -> int:
+        return self.slp["text_len"]
+
+    def ms(self, seqs: np.ndarray, offsets: np.ndarray):
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        ptr = np.zeros(max(total, 1), dtype=np.uint64)
+        ln = np.zeros(max(total, 1), dtype=np.uint64)
+        sq = seqs if seqs.shape[0] else np.zeros(1, dtype=np.uint8)
+        self.lib.oracle_ms_batch(self.h, _p(sq, ctypes.c_uint8), _p(offsets, ctypes.c_uint64), offsets.shape[0] - 1,
+                                 _p(ptr, ctypes.c_uint64), _p(ln, ctypes.c_uint64))
+        return ptr[:total], ln[:total]
+
+    def mems(self, seqs: np.ndarray, offsets: np.ndarray):
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        nr = offsets.shape[0] - 1
+        mo = np.zeros(nr + 1, dtype=np.uint64)
+        mp = np.zeros(max(total, 1), dtype=np.uint64)
+        ml = np.zeros(max(total, 1), dtype=np.uint64)
+        sq = seqs if seqs.shape[0] else np.zeros(1, dtype=np.uint8)
+        self.lib.oracle_mems_batch(self.h, _p(sq, ctypes.c_uint8), _p(offsets, ctypes.c_uint64), nr, _p(mo, ctypes.c_uint64),
+                                   _p(mp, ctypes.c_uint64), _p(ml, ctypes.c_uint64))
+        k = int(mo[-1])
+        return mo, mp[:k], ml[:k]
+
+    def counters(self, reset: bool = True) -> dict:
+        out = np.zeros(5, dtype=np.uint64)
+        self.lib.oracle_counters(self.h, _p(out, ctypes.c_uint64), 1 if reset else 0)
+        return dict(zip(["bases", "jumps", "restarts", "restart_depth", "chars"], (int(x) for x in out)))
+
+    def char_at(self, pos: int) -> int:
+        return int(self.lib.oracle_char_at(self.h, pos))
+
+
+# ----------------------------------------------------------------------------- text formats
+def format_ms(names, offsets, values) -> bytes:
+    """The reference's .pointers / .lengths text: '>' name '\\n' then each value + ' ', then '\\n'
+    (src/matching_statistics.cpp:569-598)."""
+    out = []
+    for r, nm in enumerate(names):
+        v = values[int(offsets[r]):int(offsets[r + 1])]
+        out.append(b">" + nm + b"\n" + b"".join(b"%d " % int(x) for x in v) + b"\n")
+    return b"".join(out)
+
+
+def format_mems(names, mem_offsets, mem_pos, mem_len) -> bytes:
+    """The reference's .mems text: '(' i ',' len ') ' tokens (src/mems.cpp:585-587)."""
+    out = []
+    for r, nm in enumerate(names):
+        a, b = int(mem_offsets[r]), int(mem_offsets[r + 1])
+        out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d) " % (int(mem_pos[t]), int(mem_len[t])) for t in range(a, b)) + b"\n")
+    return b"".join(out)

@@ -1,0 +1,85 @@
+// TEST-ONLY harness: compiles the per-read functions of moni_align_b200/csrc/ms_core.cuh with g++
+// and runs them over the host copy of the HBM image, so the exporter and the kernel arithmetic can
+// be checked against the oracle on a machine without a GPU.  Never linked into the library.
+//
+// usage: host_sim <index-prefix> <batch.bin> <out.bin> [leaf_len] [max_scan]
+//   batch.bin : u64 n_reads, u64 offsets[n_reads+1], u8 seqs[offsets[n_reads]]
+//   out.bin   : u64 ptr[total], u64 len[total], u64 mem_offsets[n_reads+1], u64 mem_pos[k], u64 mem_len[k], u64 counters[8]
+#include <cstdio>
+#include <cstdlib>
+#include <stdexcept>
+#include <vector>
+
+#include "../moni_align_b200/csrc/index_files.hpp"
+#include "../moni_align_b200/csrc/ms_core.cuh"
+
+using namespace moni;
+
+int main(int argc, char** argv) {
+    if (argc < 4) { fprintf(stderr, "usage: host_sim prefix batch.bin out.bin [leaf_len] [max_scan]\n"); return 2; }
+    try {
+        FlatRlbwt bwt;
+        FlatSlp slp;
+        read_thrbv_ms(std::string(argv[1]) + ".thrbv.ms", bwt);
+        read_plain_slp(std::string(argv[1]) + ".plain.slp", slp);
+        ExportOptions opt;
+        opt.verbose = true;
+        if (argc > 4) opt.leaf_len = (uint32_t)atoi(argv[4]);
+        if (argc > 5) opt.max_scan = (uint32_t)atoi(argv[5]);
+        HostImage img;
+        build_move_table(bwt, opt, img);
+        build_grammar_table(slp, opt, img);
+        ImageView v;
+        v.rows = img.rows.data(); v.row_pos = img.row_pos.data(); v.crun_row = img.crun_row.data();
+        v.slots = img.slots.data(); v.nodes = img.nodes.data(); v.pool = img.pool.data(); v.sym = &img.sym; v.hdr = img.hdr;
+
+        FILE* f = fopen(argv[2], "rb");
+        if (!f) throw std::runtime_error("cannot open batch");
+        uint64_t nr = 0;
+        if (fread(&nr, 8, 1, f) != 1) throw std::runtime_error("bad batch");
+        std::vector<uint64_t> off(nr + 1);
+        if (fread(off.data(), 8, nr + 1, f) != nr + 1) throw std::runtime_error("bad batch");
+        std::vector<uint8_t> seqs(off[nr] + 1);
+        if (off[nr] && fread(seqs.data(), 1, off[nr], f) != off[nr]) throw std::runtime_error("bad batch");
+        fclose(f);
+
+        const uint64_t total = off[nr];
+        std::vector<uint64_t> ptr(total + 1), len64(total + 1), mo(nr + 1), mems;
+        std::vector<uint32_t> len(total + 1);
+        Counters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (uint64_t r = 0; r < nr; ++r) {
+            const uint64_t o = off[r], m = off[r + 1] - o;
+            ScanState s;
+            scan_init(v, s);
+            for (uint64_t j = m; j-- > 0;) {
+                scan_step(v, img.sym.tcode, seqs[o + j], s, &cnt);
+                ptr[o + j] = s.sample;
+            }
+            cnt.bases += m;
+            std::vector<uint64_t> rec(m + 1);
+            const uint32_t k = lengths_read(v, seqs.data() + o, m, ptr.data() + o, len.data() + o, rec.data(), &cnt);
+            mo[r] = mems.size();
+            mems.insert(mems.end(), rec.begin(), rec.begin() + k);
+        }
+        mo[nr] = mems.size();
+        for (uint64_t i = 0; i < total; ++i) len64[i] = len[i];
+        std::vector<uint64_t> mp(mems.size() + 1), ml(mems.size() + 1);
+        for (size_t i = 0; i < mems.size(); ++i) { mp[i] = mems[i] >> 32; ml[i] = mems[i] & 0xFFFFFFFFu; }
+        f = fopen(argv[3], "wb");
+        if (!f) throw std::runtime_error("cannot open output");
+        fwrite(ptr.data(), 8, total, f);
+        fwrite(len64.data(), 8, total, f);
+        fwrite(mo.data(), 8, nr + 1, f);
+        fwrite(mp.data(), 8, mems.size(), f);
+        fwrite(ml.data(), 8, mems.size(), f);
+        unsigned long long c8[8] = {cnt.bases, cnt.jumps, cnt.restarts, cnt.restart_depth, cnt.chars, cnt.scan_rows, cnt.general_steps, cnt.descents};
+        fwrite(c8, 8, 8, f);
+        fclose(f);
+        fprintf(stderr, "host_sim: bases %llu jumps %llu restarts %llu depth %llu chars %llu scan_rows %llu general %llu descents %llu; image %.1f MB\n",
+                c8[0], c8[1], c8[2], c8[3], c8[4], c8[5], c8[6], c8[7], (double)img.bytes() / 1e6);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "host_sim: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}
