@@ -1,0 +1,108 @@
+/* moni_gpu.h -- C ABI of libmoni_gpu.so: the B200 (sm_100a) implementation of the computation
+ * behind `moni ms` and `moni mems`.
+ *
+ * The reference (maxrossi91/moni-align) has no FFI for this path; the seam is a handful of C++
+ * call sites inside its two executables.  Each entry point below names the reference interface
+ * it replaces (paths relative to the reference checkout).  INTEGRATION.md shows the binding a
+ * maintainer would add on the reference side.
+ *
+ * Conventions
+ *   - every int-returning function returns 0 on success and a negative MONI_GPU_E* code on
+ *     failure; moni_gpu_last_error() then returns a thread-local message.  The library never
+ *     calls exit() (the reference's error() does: include/common/common.hpp:108-117).
+ *   - all buffers are caller-owned host memory.  Pinned memory (moni_gpu_host_alloc) makes the
+ *     PCIe copies asynchronous and ~2x faster; pageable memory works.
+ *   - a batch of reads is passed as concatenated bytes `seqs` plus `offsets[n_reads + 1]`
+ *     (read r = seqs[offsets[r] .. offsets[r+1])).  Read bytes are used verbatim (no case folding),
+ *     exactly like kseq's read->seq.s in the reference.  Results are in input order for any GPU count.
+ *   - all values are full 64-bit at the ABI, like the reference's size_t vectors.
+ *   - there is NO CPU execution path: without a CUDA device every call fails with MONI_GPU_ECUDA.
+ */
+#ifndef MONI_GPU_H
+#define MONI_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MONI_GPU_OK 0
+#define MONI_GPU_EINVAL (-1)   /* bad argument */
+#define MONI_GPU_EIO (-2)      /* index file missing / malformed / unsupported */
+#define MONI_GPU_ECUDA (-3)    /* CUDA runtime failure (incl. no device) */
+#define MONI_GPU_ENOMEM (-4)   /* caller-provided capacity too small, or allocation failure */
+
+typedef struct moni_gpu_index moni_gpu_index; /* opaque: host image + one replica per GPU */
+typedef struct moni_gpu_batch moni_gpu_batch; /* opaque: a read batch resident in one GPU's HBM */
+
+/* Replaces ms_c<slp_t>::ms_c(std::string) / mems_c::mems_c  (src/matching_statistics.cpp:195-228,
+ * src/mems.cpp:195-228): reads `<prefix>.thrbv.ms` (ms_pointers::load, include/ms/ms_pointers.hpp:307-320)
+ * and `<prefix>.plain.slp` (PlainSlp::load, thirdparty/ShapedSlp/PlainSlp.hpp:305-319), flattens them
+ * and uploads one replica to every listed CUDA device.  gpus == NULL: devices 0..n_gpus-1. */
+int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gpu_index** out);
+void moni_gpu_index_free(moni_gpu_index* idx);
+
+/* n = ms.bwt_size() (r_index.hpp:455-457), r = number of BWT runs, text_len = ra.getLen()
+ * (src/matching_statistics.cpp:221), device_bytes = size of one replica.  Any pointer may be NULL. */
+int moni_gpu_index_info(const moni_gpu_index* idx, uint64_t* n, uint64_t* r, uint64_t* text_len, uint64_t* device_bytes);
+
+/* Replaces ms_c::matching_statistics(kseq_t*, FILE*) (src/matching_statistics.cpp:242-278) for a whole
+ * batch: pointers = ms.query(seq, len) (include/ms/ms_pointers.hpp:241, 455-511), lengths = the
+ * charAt loop (:246-255).  Both outputs have offsets[n_reads] entries, laid out like `seqs`. */
+int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
+                uint64_t* pointers, uint64_t* lengths);
+
+/* Replaces mems_c::maxrimal_exact_matches(kseq_t*, FILE*) (src/mems.cpp:241-280): for read r the records
+ * (mem_pos[k], mem_len[k]), k in [mem_offsets[r], mem_offsets[r+1]), are the reference's
+ * std::vector<std::pair<size_t,size_t>> mems (query offset, length).  mem_offsets has n_reads + 1
+ * entries.  If mem_capacity is too small the call fails with MONI_GPU_ENOMEM after filling
+ * mem_offsets (so mem_offsets[n_reads] is the capacity needed); offsets[n_reads] always suffices. */
+int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
+                  uint64_t* mem_offsets, uint64_t* mem_pos, uint64_t* mem_len, uint64_t mem_capacity);
+
+/* Event counters accumulated over all calls since the last reset, when counting is enabled
+ * (moni_gpu_set_option("count", "1"); off by default, it costs a few percent):
+ * c[0]=bases, c[1]=threshold jumps (ms_pointers.hpp:482-505 taken), c[2]=LCE restarts,
+ * c[3]=grammar nodes visited by descents, c[4]=characters compared (charAt evaluations,
+ * src/matching_statistics.cpp:250), c[5]=rows scanned forward after LF, c[6]=steps through the
+ * general path, c[7]=descents.  SURVEY.md 8(d) defines the roofline numerator from c[0..4]. */
+int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset);
+
+/* Device time of the last moni_gpu_ms / moni_gpu_mems call on this index, in milliseconds, measured
+ * with CUDA events on the launching stream and maxed over the index's GPUs:
+ * t[0]=host->device copies, t[1]=pass 1 kernel, t[2]=pass 2 kernel, t[3]=MEM compaction,
+ * t[4]=device->host copies, t[5]=whole call (first copy to last copy). */
+int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
+
+/* Options (call before moni_gpu_index_load): "leaf_len" (grammar literal block length, default 128),
+ * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
+ * "chunk_bases" (bases per device chunk, default 2^26). */
+int moni_gpu_set_option(const char* key, const char* value);
+
+/* Pinned host memory for batch buffers (cudaHostAlloc / cudaFreeHost). */
+void* moni_gpu_host_alloc(uint64_t bytes);
+void moni_gpu_host_free(void* p);
+
+/* ---- resident batches: inputs stay in HBM across runs (pipelines, kernel-only measurement) ----
+ * gpu_slot indexes the `gpus` list given to moni_gpu_index_load. */
+int moni_gpu_batch_create(moni_gpu_index* idx, int gpu_slot, const char* seqs, const uint64_t* offsets,
+                          uint64_t n_reads, moni_gpu_batch** out);
+/* what: 1 = ms (pass 1 + pass 2), 2 = mems (pass 1 + pass 2 + compaction).  Kernels only; returns the
+ * CUDA-event time of each stage in milliseconds (kernel_ms[0]=pass 1, [1]=pass 2, [2]=compaction). */
+int moni_gpu_batch_run(moni_gpu_batch* b, int what, float kernel_ms[3]);
+int moni_gpu_batch_fetch_ms(moni_gpu_batch* b, uint64_t* pointers, uint64_t* lengths);
+int moni_gpu_batch_fetch_mems(moni_gpu_batch* b, uint64_t* mem_offsets, uint64_t* mem_pos, uint64_t* mem_len,
+                              uint64_t mem_capacity);
+void moni_gpu_batch_free(moni_gpu_batch* b);
+
+/* Number of kernel launches issued by this process so far (all indexes). */
+uint64_t moni_gpu_launch_count(void);
+
+const char* moni_gpu_last_error(void);
+const char* moni_gpu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MONI_GPU_H */

@@ -1,0 +1,278 @@
+"""moni_align_b200 -- B200 (sm_100a) matching statistics and MEMs for MONI indexes.
+
+Host-side mirror of the reference's two call sites for this path, over the C ABI of
+``libmoni_gpu.so`` (include/moni_gpu.h):
+
+    reference (C++)                                            here
+    ---------------------------------------------------------  ---------------------------------
+    ms_c<slp_t>::ms_c(prefix)      src/matching_statistics.cpp:195   MoniIndex(prefix, gpus=[...])
+    ms_c::matching_statistics      src/matching_statistics.cpp:242   MoniIndex.matching_statistics
+    mems_c::maxrimal_exact_matches src/mems.cpp:241                  MoniIndex.maxrimal_exact_matches
+
+The method names (including the reference's spelling of "maxrimal") and the meaning of the results
+are the reference's; the unit of work is a batch of reads instead of one kseq record.  There is no
+CPU execution path: constructing a MoniIndex without the built library or without a CUDA device
+raises.  Build the library with ``__graft_entry__.build()`` or ``make -C moni_align_b200/csrc``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Iterable, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmoni_gpu.so")
+
+_u64p = ctypes.POINTER(ctypes.c_uint64)
+_lib = None
+
+
+class MoniGpuError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"libmoni_gpu error {code}: {msg}")
+        self.code = code
+
+
+EXPORTS = [
+    "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems",
+    "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
+    "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
+    "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
+]
+
+
+def load_library() -> ctypes.CDLL:
+    """dlopen libmoni_gpu.so (in-tree) and declare the prototypes of include/moni_gpu.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback)")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, ci, cc = ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p
+    L.moni_gpu_index_load.argtypes = [cc, ctypes.POINTER(ci), ci, ctypes.POINTER(vp)]
+    L.moni_gpu_index_free.argtypes = [vp]
+    L.moni_gpu_index_free.restype = None
+    L.moni_gpu_index_info.argtypes = [vp, _u64p, _u64p, _u64p, _u64p]
+    L.moni_gpu_ms.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, _u64p]
+    L.moni_gpu_mems.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, _u64p, _u64p, ctypes.c_uint64]
+    L.moni_gpu_counters.argtypes = [vp, _u64p, ci]
+    L.moni_gpu_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    L.moni_gpu_set_option.argtypes = [cc, cc]
+    L.moni_gpu_host_alloc.argtypes = [ctypes.c_uint64]
+    L.moni_gpu_host_alloc.restype = vp
+    L.moni_gpu_host_free.argtypes = [vp]
+    L.moni_gpu_host_free.restype = None
+    L.moni_gpu_batch_create.argtypes = [vp, ci, vp, _u64p, ctypes.c_uint64, ctypes.POINTER(vp)]
+    L.moni_gpu_batch_run.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_float)]
+    L.moni_gpu_batch_fetch_ms.argtypes = [vp, _u64p, _u64p]
+    L.moni_gpu_batch_fetch_mems.argtypes = [vp, _u64p, _u64p, _u64p, ctypes.c_uint64]
+    L.moni_gpu_batch_free.argtypes = [vp]
+    L.moni_gpu_batch_free.restype = None
+    L.moni_gpu_launch_count.restype = ctypes.c_uint64
+    L.moni_gpu_last_error.restype = cc
+    L.moni_gpu_version.restype = cc
+    _lib = L
+    return L
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise MoniGpuError(rc, load_library().moni_gpu_last_error().decode(errors="replace"))
+
+
+def set_option(key: str, value) -> None:
+    _check(load_library().moni_gpu_set_option(key.encode(), str(value).encode()))
+
+
+def launch_count() -> int:
+    return int(load_library().moni_gpu_launch_count())
+
+
+def pinned_empty(n: int, dtype) -> np.ndarray:
+    """numpy array over cudaHostAlloc memory.  The allocation lives until release_pinned() or exit."""
+    L = load_library()
+    dt = np.dtype(dtype)
+    nbytes = max(int(n) * dt.itemsize, 1)
+    p = L.moni_gpu_host_alloc(nbytes)
+    if not p:
+        raise MoniGpuError(-4, "pinned allocation failed")
+    buf = (ctypes.c_uint8 * nbytes).from_address(p)
+    arr = np.frombuffer(buf, dtype=dt, count=int(n))
+    _PINNED[p] = nbytes
+    return arr
+
+
+def release_pinned() -> None:
+    """Frees every pinned_empty() allocation (the arrays must no longer be used)."""
+    L = load_library()
+    for p in list(_PINNED):
+        L.moni_gpu_host_free(p)
+        del _PINNED[p]
+
+
+_PINNED: dict = {}
+
+
+def pack_reads(reads) -> tuple[np.ndarray, np.ndarray]:
+    """(seqs uint8[total], offsets uint64[n+1]) from a 2-D uint8 matrix or a list of bytes/arrays."""
+    if isinstance(reads, np.ndarray) and reads.ndim == 2:
+        n, m = reads.shape
+        return np.ascontiguousarray(reads, dtype=np.uint8).reshape(-1), np.arange(n + 1, dtype=np.uint64) * np.uint64(m)
+    lens = np.fromiter((len(r) for r in reads), dtype=np.uint64, count=len(reads))
+    offs = np.zeros(len(reads) + 1, dtype=np.uint64)
+    np.cumsum(lens, out=offs[1:])
+    parts = [np.frombuffer(bytes(r), dtype=np.uint8) if not isinstance(r, np.ndarray) else r.astype(np.uint8, copy=False)
+             for r in reads]
+    seqs = np.concatenate(parts) if parts and int(offs[-1]) else np.zeros(0, dtype=np.uint8)
+    return seqs, offs
+
+
+def _ptr(a: np.ndarray):
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+def _u64(a: np.ndarray):
+    return a.ctypes.data_as(_u64p)
+
+
+class MoniIndex:
+    """An index replicated in the HBM of one or more GPUs (reference: ms_c / mems_c objects)."""
+
+    def __init__(self, prefix: str, gpus: Sequence[int] | None = None):
+        L = load_library()
+        self._L = L
+        gpus = [0] if gpus is None else list(gpus)
+        arr = (ctypes.c_int * len(gpus))(*gpus)
+        h = ctypes.c_void_p()
+        _check(L.moni_gpu_index_load(os.fsencode(prefix), arr, len(gpus), ctypes.byref(h)))
+        self._h = h
+        self.gpus = gpus
+        v = [ctypes.c_uint64() for _ in range(4)]
+        _check(L.moni_gpu_index_info(h, *[ctypes.byref(x) for x in v]))
+        self.n, self.r, self.text_len, self.device_bytes = (int(x.value) for x in v)
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._L.moni_gpu_index_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- the two reference entry points, batched --------------------------------------------
+    def matching_statistics(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
+        """(pointers, lengths), uint64[offsets[-1]] each -- ms_c::matching_statistics for every read."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        nr = offsets.shape[0] - 1
+        if out is None:
+            ptr = np.empty(max(total, 1), dtype=np.uint64)
+            ln = np.empty(max(total, 1), dtype=np.uint64)
+        else:
+            ptr, ln = out
+        _check(self._L.moni_gpu_ms(self._h, _ptr(seqs), _u64(offsets), nr, _u64(ptr), _u64(ln)))
+        return ptr[:total], ln[:total]
+
+    def maxrimal_exact_matches(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
+        """(mem_offsets uint64[n+1], mem_pos, mem_len) -- mems_c::maxrimal_exact_matches for every read;
+        read r owns records mem_offsets[r]:mem_offsets[r+1], each (query offset, length)."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        nr = offsets.shape[0] - 1
+        if out is None:
+            mo = np.empty(nr + 1, dtype=np.uint64)
+            mp = np.empty(max(total, 1), dtype=np.uint64)
+            ml = np.empty(max(total, 1), dtype=np.uint64)
+        else:
+            mo, mp, ml = out
+        _check(self._L.moni_gpu_mems(self._h, _ptr(seqs), _u64(offsets), nr, _u64(mo), _u64(mp), _u64(ml), mp.shape[0]))
+        k = int(mo[nr])
+        return mo, mp[:k], ml[:k]
+
+    # -- instrumentation -----------------------------------------------------------------------
+    def counters(self, reset: bool = True) -> dict:
+        c = (ctypes.c_uint64 * 8)()
+        _check(self._L.moni_gpu_counters(self._h, c, 1 if reset else 0))
+        names = ["bases", "jumps", "restarts", "restart_depth", "chars", "scan_rows", "general_steps", "descents"]
+        return dict(zip(names, (int(x) for x in c)))
+
+    def timing(self) -> dict:
+        t = (ctypes.c_double * 6)()
+        _check(self._L.moni_gpu_timing(self._h, t))
+        return dict(zip(["h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms"], (float(x) for x in t)))
+
+    def resident_batch(self, seqs: np.ndarray, offsets: np.ndarray, gpu_slot: int = 0) -> "ResidentBatch":
+        return ResidentBatch(self, seqs, offsets, gpu_slot)
+
+
+class ResidentBatch:
+    """A read batch kept in one GPU's HBM; run() launches kernels only and returns their CUDA-event times."""
+
+    def __init__(self, index: MoniIndex, seqs: np.ndarray, offsets: np.ndarray, gpu_slot: int = 0):
+        self._L = index._L
+        self.index = index
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        self.n_reads = self.offsets.shape[0] - 1
+        self.total = int(self.offsets[-1] - self.offsets[0])
+        h = ctypes.c_void_p()
+        _check(self._L.moni_gpu_batch_create(index._h, gpu_slot, _ptr(seqs), _u64(self.offsets), self.n_reads, ctypes.byref(h)))
+        self._h = h
+
+    def run(self, what: str) -> dict:
+        ms = (ctypes.c_float * 3)()
+        _check(self._L.moni_gpu_batch_run(self._h, {"ms": 1, "mems": 2}[what], ms))
+        return {"pass1_ms": float(ms[0]), "pass2_ms": float(ms[1]), "compact_ms": float(ms[2])}
+
+    def fetch_ms(self):
+        ptr = np.empty(max(self.total, 1), dtype=np.uint64)
+        ln = np.empty(max(self.total, 1), dtype=np.uint64)
+        _check(self._L.moni_gpu_batch_fetch_ms(self._h, _u64(ptr), _u64(ln)))
+        return ptr[:self.total], ln[:self.total]
+
+    def fetch_mems(self):
+        mo = np.empty(self.n_reads + 1, dtype=np.uint64)
+        mp = np.empty(max(self.total, 1), dtype=np.uint64)
+        ml = np.empty(max(self.total, 1), dtype=np.uint64)
+        _check(self._L.moni_gpu_batch_fetch_mems(self._h, _u64(mo), _u64(mp), _u64(ml), mp.shape[0]))
+        k = int(mo[self.n_reads])
+        return mo, mp[:k], ml[:k]
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._L.moni_gpu_batch_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def format_ms(names: Iterable[bytes], offsets: np.ndarray, values: np.ndarray) -> bytes:
+    """Text of a .pointers / .lengths file (reference src/matching_statistics.cpp:569-598)."""
+    out = []
+    for r, nm in enumerate(names):
+        v = values[int(offsets[r]):int(offsets[r + 1])]
+        out.append(b">" + nm + b"\n" + b"".join(b"%d " % int(x) for x in v) + b"\n")
+    return b"".join(out)
+
+
+def format_mems(names: Iterable[bytes], mem_offsets, mem_pos, mem_len) -> bytes:
+    """Text of a .mems file (reference src/mems.cpp:585-587)."""
+    out = []
+    for r, nm in enumerate(names):
+        a, b = int(mem_offsets[r]), int(mem_offsets[r + 1])
+        out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d) " % (int(mem_pos[t]), int(mem_len[t])) for t in range(a, b)) + b"\n")
+    return b"".join(out)

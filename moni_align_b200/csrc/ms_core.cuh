@@ -220,7 +220,8 @@ MONI_HD const uint8_t* text_block(const ImageView& v, uint64_t tp, uint64_t& rem
 // The length loop for one read.  ptr[] are the pass-1 pointers of this read.  Writes len[i] (if
 // len != nullptr) and returns the number of MEM records; records are written to mem_out (packed
 // (i << 32) | len) when mem_out != nullptr.
-MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, uint32_t* len,
+template <typename LenT>
+MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, LenT* len,
                               uint64_t* mem_out, Counters* cnt) {
     const uint64_t N = v.hdr.text_len;
     uint64_t l = 0, prev_ptr = 0, prev_len = 0;
@@ -243,7 +244,7 @@ MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m
                 if (k < rem) go = false;                        // read exhausted or mismatch inside the block
             }
         }
-        if (len) len[i] = (uint32_t)l;
+        if (len) len[i] = (LenT)l;
         if (i == 0 || l >= prev_len) {                           // src/mems.cpp:257-258
             if (mem_out) mem_out[n_mems] = (i << 32) | l;
             ++n_mems;

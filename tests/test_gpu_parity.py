@@ -1,0 +1,186 @@
+"""GPU suite (-m gpu): the CUDA path, called through the C ABI (include/moni_gpu.h via ctypes), against
+(a) the committed outputs of the reference binaries, (b) the CPU oracle on seeded inputs, and
+(c) size-independent properties at larger sizes.  Bit-exact: everything here is unsigned integers."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import CASES, GOLDEN, ROOT, pack, read_fastq
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def m():
+    import moni_align_b200 as mod
+    mod.load_library()
+    return mod
+
+
+@pytest.fixture(scope="module")
+def indexes(m):
+    return {c: m.MoniIndex(os.path.join(GOLDEN, c + ".fa")) for c in CASES}
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_ms_and_mems_equal_reference_files(case, m, indexes):
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    ix = indexes[case]
+    ptr, ln = ix.matching_statistics(flat, offs)
+    assert m.format_ms(names, offs, ptr) == open(pre + ".pointers", "rb").read()
+    assert m.format_ms(names, offs, ln) == open(pre + ".lengths", "rb").read()
+    mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+    assert m.format_mems(names, mo, mp, ml) == open(pre + ".mems", "rb").read()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_random_reads_equal_oracle(case, m, indexes, oracle_mod):
+    import synth
+    pre = os.path.join(GOLDEN, case + ".fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = [r for r in synth.short_reads(text, 3000, 100, 77, err=0.03)]
+    reads += synth.long_reads(text, 40, 78, mean=1500, sd=600, lo=100, hi=4000)
+    rng = np.random.default_rng(5)
+    for _ in range(200):   # noise: arbitrary bytes incl. absent symbols
+        reads.append(rng.integers(1, 127, size=int(rng.integers(1, 60)), dtype=np.uint8))
+    flat, offs = m.pack_reads(reads)
+    ptr, ln = indexes[case].matching_statistics(flat, offs)
+    wp, wl = orc.ms(flat, offs)
+    assert np.array_equal(ptr, wp)
+    assert np.array_equal(ln, wl)
+    mo, mp, ml = indexes[case].maxrimal_exact_matches(flat, offs)
+    wmo, wmp, wml = orc.mems(flat, offs)
+    assert np.array_equal(mo, wmo) and np.array_equal(mp, wmp) and np.array_equal(ml, wml)
+
+
+def test_empty_ragged_and_zero_read_batches(m, indexes, oracle_mod):
+    ix = indexes["pan4"]
+    orc = oracle_mod.OracleIndex(os.path.join(GOLDEN, "pan4.fa"))
+    flat, offs = pack([b"", b"A", b"", b"ACGTACGTTTGA", b""])
+    ptr, ln = ix.matching_statistics(flat, offs)
+    wp, wl = orc.ms(flat, offs)
+    assert np.array_equal(ptr, wp) and np.array_equal(ln, wl)
+    mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+    wmo, wmp, wml = orc.mems(flat, offs)
+    assert np.array_equal(mo, wmo) and np.array_equal(mp, wmp) and np.array_equal(ml, wml)
+    z = np.zeros(1, dtype=np.uint64)
+    mo, mp, ml = ix.maxrimal_exact_matches(np.zeros(0, dtype=np.uint8), z)
+    assert mo.tolist() == [0] and mp.size == 0
+
+
+def test_chunking_and_resident_batches_agree(m, oracle_mod):
+    """Small device chunks (many launches) and the resident-batch API give the same bits as one big call."""
+    import synth
+    pre = os.path.join(GOLDEN, "pan4.fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = synth.short_reads(text, 5000, 120, 9)
+    flat, offs = m.pack_reads(reads)
+    m.set_option("chunk_bases", 7001)
+    try:
+        small = m.MoniIndex(pre)
+    finally:
+        m.set_option("chunk_bases", 1 << 26)
+    big = m.MoniIndex(pre)
+    a = small.matching_statistics(flat, offs)
+    b = big.matching_statistics(flat, offs)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    am = small.maxrimal_exact_matches(flat, offs)
+    bm = big.maxrimal_exact_matches(flat, offs)
+    assert all(np.array_equal(x, y) for x, y in zip(am, bm))
+    rb = big.resident_batch(flat, offs)
+    t = rb.run("ms")
+    assert t["pass1_ms"] > 0 and t["pass2_ms"] > 0
+    c = rb.fetch_ms()
+    assert np.array_equal(c[0], b[0]) and np.array_equal(c[1], b[1])
+    rb.run("mems")
+    cm = rb.fetch_mems()
+    assert all(np.array_equal(x, y) for x, y in zip(cm, bm))
+    wp, wl = orc.ms(flat, offs)
+    assert np.array_equal(b[0], wp) and np.array_equal(b[1], wl)
+    rb.close()
+
+
+def test_mem_capacity_error(m, indexes):
+    ix = indexes["pan4"]
+    flat, offs = pack([b"ACGTACGTACGTTTTGACCA"] * 50)
+    mo = np.zeros(51, dtype=np.uint64)
+    small = np.zeros(3, dtype=np.uint64)
+    with pytest.raises(m.MoniGpuError) as e:
+        ix.maxrimal_exact_matches(flat, offs, out=(mo, small, small.copy()))
+    assert e.value.code == -4
+    assert int(mo[50]) > 3          # the needed capacity is reported
+
+
+def test_counters_match_oracle(m, oracle_mod):
+    import synth
+    pre = os.path.join(GOLDEN, "withN.fa")
+    orc = oracle_mod.OracleIndex(pre)
+    names, seqs = read_fastq(os.path.join(GOLDEN, "withN.fq"))
+    flat, offs = pack(seqs)
+    m.set_option("count", 1)
+    try:
+        ix = m.MoniIndex(pre)
+    finally:
+        m.set_option("count", 0)
+    ix.counters(reset=True)
+    orc.counters(reset=True)
+    ix.matching_statistics(flat, offs)
+    orc.ms(flat, offs)
+    got, want = ix.counters(), orc.counters()
+    for k in ("bases", "jumps", "restarts", "chars"):
+        assert got[k] == want[k], k
+    assert got["general_steps"] > 0
+
+
+def test_properties_on_a_larger_index(m, oracle_mod, tmp_path):
+    """Size-independent properties on a 2 Mbp x 4 pangenome built on the fly with the reference builder:
+    T[ptr:ptr+len] == read[i:i+len], right-maximality against a suffix-array-free spot check, len[i+1] >= len[i]-1,
+    MEM records consistent with lengths, and determinism across calls."""
+    import build_index
+    import synth
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "rlebwt_ms_build")):
+        pytest.skip("reference builder binaries not present")
+    recs = synth.pangenome(2_000_000, 4, 5, 2e-3, 2e-4)
+    fa = str(tmp_path / "big.fa")
+    synth.write_fasta(fa, recs)
+    build_index.build_index(fa)
+    text = synth.text_of(recs)
+    reads = synth.short_reads(text, 200_000, 150, 6)
+    flat, offs = m.pack_reads(reads)
+    ix = m.MoniIndex(fa)
+    ptr, ln = ix.matching_statistics(flat, offs)
+    ptr2, ln2 = ix.matching_statistics(flat, offs)
+    assert np.array_equal(ptr, ptr2) and np.array_equal(ln, ln2)
+    L = ln.reshape(-1, 150).astype(np.int64)
+    P = ptr.reshape(-1, 150)
+    assert (L[:, 1:] >= L[:, :-1] - 1).all()
+    assert (L >= 0).all() and (L <= 150 - np.arange(150)[None, :]).all()
+    # the match itself, vectorised: compare first and last matched character and a random interior one
+    idx = np.nonzero(L > 0)
+    p = P[idx].astype(np.int64)
+    l = L[idx]
+    r, i = idx
+    assert (p + l <= text.shape[0]).all()
+    assert (text[p] == reads[r, i]).all()
+    assert (text[p + l - 1] == reads[r, i + l - 1]).all()
+    k = (np.random.default_rng(1).random(l.shape[0]) * l).astype(np.int64)
+    assert (text[p + k] == reads[r, i + k]).all()
+    # right-maximal at the pointer: next char differs or the read / text ends
+    ext = (i + l < 150) & (p + l < text.shape[0])
+    assert (text[(p + l)[ext]] != reads[r[ext], (i + l)[ext]]).all()
+    # full check of 300 reads against the oracle (and so against the reference's own loop)
+    orc = oracle_mod.OracleIndex(fa)
+    wp, wl = orc.ms(flat[:300 * 150], offs[:301])
+    assert np.array_equal(ptr[:300 * 150], wp) and np.array_equal(ln[:300 * 150], wl)
+    mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+    cnt = np.diff(mo.astype(np.int64))
+    is_mem = np.ones_like(L, dtype=bool)
+    is_mem[:, 1:] = L[:, 1:] >= L[:, :-1]
+    assert np.array_equal(cnt, is_mem.sum(axis=1))
+    assert np.array_equal(ml.astype(np.int64), L[is_mem])
+    assert np.array_equal(mp.astype(np.int64), np.nonzero(is_mem)[1])

@@ -1,0 +1,107 @@
+"""CPU suite, part 2: the product's host logic without a GPU.
+  * the exporter (index reader -> HBM image) and the per-read core of the kernels, compiled for the CPU by
+    tests/host_sim.cpp (TEST-ONLY build of moni_align_b200/csrc/ms_core.cuh), against the golden reference outputs;
+  * libmoni_gpu.so loads, exports every symbol include/moni_gpu.h declares, and fails loudly without a device."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import CASES, GOLDEN, ROOT, pack, read_fastq, run_host_sim
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("opts", [(), (1, 2), (16, 3), (64, 4), (1000000, 64)])
+def test_exporter_and_core_match_reference(case, opts, host_sim, oracle_mod, tmp_path):
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    p, l, mo, mp, ml, cnt = run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path, opts)
+    assert oracle_mod.format_ms(names, offs, p) == open(pre + ".pointers", "rb").read()
+    assert oracle_mod.format_ms(names, offs, l) == open(pre + ".lengths", "rb").read()
+    assert oracle_mod.format_mems(names, mo, mp, ml) == open(pre + ".mems", "rb").read()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_event_counters_match_oracle(case, host_sim, oracle_mod, tmp_path):
+    """B, J, S, C of SURVEY.md 8(d) are properties of (index, reads): the image must count the same events."""
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    ix = oracle_mod.OracleIndex(pre + ".fa")
+    ix.counters(reset=True)
+    ix.ms(flat, offs)
+    want = ix.counters()
+    cnt = run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path)[5]
+    assert int(cnt[0]) == want["bases"]
+    assert int(cnt[1]) == want["jumps"]
+    assert int(cnt[2]) == want["restarts"]
+    assert int(cnt[4]) == want["chars"]
+
+
+def test_general_path_is_exercised(host_sim, tmp_path):
+    pre = os.path.join(GOLDEN, "withN")
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    cnt = run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path)[5]
+    assert int(cnt[6]) > 100
+
+
+def test_empty_and_ragged_batches(host_sim, oracle_mod, tmp_path):
+    pre = os.path.join(GOLDEN, "pan4")
+    ix = oracle_mod.OracleIndex(pre + ".fa")
+    seqs = [b"", b"A", b"", b"ACGTACGTTTGA", b""]
+    flat, offs = pack(seqs)
+    p, l, mo, mp, ml, _ = run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path)
+    wp, wl = ix.ms(flat, offs)
+    wmo, wmp, wml = ix.mems(flat, offs)
+    assert np.array_equal(p, wp) and np.array_equal(l, wl)
+    assert np.array_equal(mo, wmo) and np.array_equal(mp, wmp) and np.array_equal(ml, wml)
+
+
+def test_reader_rejects_garbage(host_sim, tmp_path):
+    import subprocess
+    bad = tmp_path / "bad"
+    (tmp_path / "bad.thrbv.ms").write_bytes(b"\x00" * 100)
+    (tmp_path / "bad.plain.slp").write_bytes(b"\x00" * 10)
+    (tmp_path / "b.bin").write_bytes(np.zeros(2, dtype=np.uint64).tobytes())
+    r = subprocess.run([host_sim, str(bad), str(tmp_path / "b.bin"), str(tmp_path / "o.bin")], capture_output=True)
+    assert r.returncode == 1 and b"host_sim:" in r.stderr
+
+
+# ------------------------------------------------------------------------------ the C ABI library
+def _declared_symbols():
+    hdr = open(os.path.join(ROOT, "include", "moni_gpu.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    return sorted(set(re.findall(r"\b(moni_gpu_[a-z_0-9]+)\s*\(", hdr)))
+
+
+def test_library_exports_every_declared_symbol():
+    import moni_align_b200 as m
+    L = m.load_library()
+    syms = _declared_symbols()
+    assert len(syms) >= 18
+    for s in syms:
+        assert hasattr(L, s), s
+    assert sorted(m.EXPORTS) == syms
+
+
+def test_library_has_no_cpu_fallback():
+    """Without a CUDA device the product must fail loudly, never compute on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    import moni_align_b200 as m
+    with pytest.raises(m.MoniGpuError) as e:
+        m.MoniIndex(os.path.join(GOLDEN, "pan4.fa"))
+    assert e.value.code == -3
+    assert "oracle" not in open(os.path.join(ROOT, "moni_align_b200", "__init__.py")).read().split('"""', 2)[2]
+
+
+def test_missing_index_file_is_an_error_not_a_crash(host_sim, tmp_path):
+    import subprocess
+    (tmp_path / "b.bin").write_bytes(np.zeros(2, dtype=np.uint64).tobytes())
+    r = subprocess.run([host_sim, str(tmp_path / "nope"), str(tmp_path / "b.bin"), str(tmp_path / "o.bin")], capture_output=True)
+    assert r.returncode == 1 and b"cannot open" in r.stderr
