@@ -75,7 +75,7 @@ int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset);
  * t[4]=device->host copies, t[5]=whole call (first copy to last copy). */
 int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
 
-/* Options (call before moni_gpu_index_load): "leaf_len" (grammar literal block length, default 128),
+/* Options ("leaf_len", "max_scan", "chunk_bases" apply to indexes loaded afterwards; "count" and "verbose" apply at once): "leaf_len" (grammar literal block length, default 128),
  * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
  * "chunk_bases" (bases per device chunk, default 2^26). */
 int moni_gpu_set_option(const char* key, const char* value);

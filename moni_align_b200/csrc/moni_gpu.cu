@@ -109,6 +109,7 @@ namespace {
 
 thread_local std::string g_err;
 std::atomic<uint64_t> g_launches{0};
+std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
     uint32_t leaf_len = 128, max_scan = 8;
@@ -166,7 +167,6 @@ struct Replica {
     cudaEvent_t ev[8] = {nullptr};
     std::mutex mu;
     double t[6] = {0, 0, 0, 0, 0, 0};
-    bool count = false;
     ~Replica() {
         cudaSetDevice(dev);
         rows.release(); row_pos.release(); crun_row.release(); slots.release(); nodes.release(); pool.release();
@@ -210,7 +210,7 @@ struct ChunkTimes { float pass1 = 0, pass2 = 0, compact = 0; };
 void launch_pass1(Replica& R, Scratch& S, uint64_t base, uint32_t n) {
     if (!n) return;
     const dim3 grid((n + kBlock - 1) / kBlock);
-    if (R.count)
+    if (g_count.load())
         k_ms_pointers<true><<<grid, kBlock, 0, R.stream>>>(R.view, S.seqs.as<uint8_t>(), S.offs.as<uint64_t>(), base, n,
                                                            S.ptr.as<uint64_t>(), R.counters.as<Counters>());
     else
@@ -228,10 +228,10 @@ void launch_pass2(Replica& R, Scratch& S, uint64_t base, uint32_t n, bool mems) 
     const uint64_t* of = S.offs.as<uint64_t>();
     uint64_t* p = S.ptr.as<uint64_t>();
     if (mems) {
-        if (R.count) k_ms_lengths<true, true><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, nullptr, S.counts.as<uint32_t>(), g);
+        if (g_count.load()) k_ms_lengths<true, true><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, nullptr, S.counts.as<uint32_t>(), g);
         else k_ms_lengths<true, false><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, nullptr, S.counts.as<uint32_t>(), nullptr);
     } else {
-        if (R.count) k_ms_lengths<false, true><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, S.len.as<uint64_t>(), nullptr, g);
+        if (g_count.load()) k_ms_lengths<false, true><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, S.len.as<uint64_t>(), nullptr, g);
         else k_ms_lengths<false, false><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, S.len.as<uint64_t>(), nullptr, nullptr);
     }
     g_launches++;
@@ -396,7 +396,7 @@ int moni_gpu_set_option(const char* key, const char* value) {
     if (k == "leaf_len" && v >= 1 && v <= (1 << 20)) g_opt.leaf_len = (uint32_t)v;
     else if (k == "max_scan" && v >= 2 && v <= 4096) g_opt.max_scan = (uint32_t)v;
     else if (k == "verbose") g_opt.verbose = v != 0;
-    else if (k == "count") g_opt.count = v != 0;
+    else if (k == "count") { g_opt.count = v != 0; g_count.store(v != 0); }
     else if (k == "chunk_bases" && v >= 1) g_opt.chunk_bases = (uint64_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }
     return 0;
@@ -451,7 +451,6 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
         for (int g = 0; g < n_gpus; ++g) {
             std::unique_ptr<Replica> R(new Replica);
             R->dev = devs[g];
-            R->count = idx->opt.count;
             CK(cudaSetDevice(R->dev));
             CK(cudaStreamCreateWithFlags(&R->stream, cudaStreamNonBlocking));
             for (auto& e : R->ev) CK(cudaEventCreate(&e));

@@ -122,14 +122,14 @@ def test_counters_match_oracle(m, oracle_mod):
     orc = oracle_mod.OracleIndex(pre)
     names, seqs = read_fastq(os.path.join(GOLDEN, "withN.fq"))
     flat, offs = pack(seqs)
+    ix = m.MoniIndex(pre)
     m.set_option("count", 1)
     try:
-        ix = m.MoniIndex(pre)
+        ix.counters(reset=True)
+        orc.counters(reset=True)
+        ix.matching_statistics(flat, offs)
     finally:
         m.set_option("count", 0)
-    ix.counters(reset=True)
-    orc.counters(reset=True)
-    ix.matching_statistics(flat, offs)
     orc.ms(flat, offs)
     got, want = ix.counters(), orc.counters()
     for k in ("bases", "jumps", "restarts", "chars"):
