@@ -291,7 +291,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "small"])
+    ap.add_argument("--workload", default="cfg2s", choices=["cfg2", "cfg2s", "small"])
     ap.add_argument("--pairs", type=int, default=0, help="read pairs per GPU per step (default: the workload's)")
     ap.add_argument("--ref-reads", type=int, default=100_000, help="reads in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -184,3 +184,41 @@ def test_properties_on_a_larger_index(m, oracle_mod, tmp_path):
     assert np.array_equal(cnt, is_mem.sum(axis=1))
     assert np.array_equal(ml.astype(np.int64), L[is_mem])
     assert np.array_equal(mp.astype(np.int64), np.nonzero(is_mem)[1])
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("threads", [1, 3])
+def test_drop_in_cli_writes_identical_files(case, threads, tmp_path):
+    """moni_align_b200/bin/{ms,mems}: the reference's command line, file names and output bytes."""
+    import subprocess
+    pre = os.path.join(GOLDEN, case)
+    out = str(tmp_path / "o")
+    for exe in ("ms", "mems"):
+        r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", exe), pre + ".fa", "-p", pre + ".fq", "-o", out,
+                            "-t", str(threads)], capture_output=True)
+        assert r.returncode == 0, r.stderr
+    for ext in (".pointers", ".lengths", ".mems"):
+        assert open(out + ext, "rb").read() == open(pre + ext, "rb").read(), ext
+
+
+def test_cli_rejects_q_like_the_reference(tmp_path):
+    import subprocess
+    pre = os.path.join(GOLDEN, "pan4")
+    r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", "ms"), pre + ".fa", "-p", pre + ".fq", "-q"], capture_output=True)
+    assert r.returncode == 1 and b"[ERROR]" in r.stderr
+
+
+def test_cli_reads_gzip_and_fasta(tmp_path):
+    import gzip
+    import subprocess
+    pre = os.path.join(GOLDEN, "pan4")
+    names, seqs = read_fastq(pre + ".fq")
+    fa = tmp_path / "reads.fa.gz"
+    with gzip.open(fa, "wb") as f:
+        for n, s in zip(names, seqs):
+            body = b"\n".join(s[i:i + 60] for i in range(0, len(s), 60))
+            f.write(b">" + n + b" some comment\n" + body + b"\n")
+    out = str(tmp_path / "o")
+    r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", "mems"), pre + ".fa", "-p", str(fa), "-o", out], capture_output=True)
+    assert r.returncode == 0, r.stderr
+    assert open(out + ".mems", "rb").read() == open(pre + ".mems", "rb").read()

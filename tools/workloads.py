@@ -25,6 +25,11 @@ WORKLOADS = {
     "cfg2": dict(base_len=61_400_000, haplotypes=7, seed=201, snp=5e-3, indel=5e-4, read_seed=203, read_len=150,
                  pairs=1_000_000, insert=(400, 50), err=0.01,
                  desc="cfg2 stand-in: 61.4 Mbp x 7 haplotypes, mems on 1M x 2 x 150 bp paired-end reads"),
+    # cfg2 scaled so that the two index files fit the 512 MiB gpurun snapshot (the full-size index takes ~13 min of
+    # the reference's pfp_thresholds to build and cannot be shipped): same haplotype model, same reads.
+    "cfg2s": dict(base_len=28_000_000, haplotypes=7, seed=201, snp=5e-3, indel=5e-4, read_seed=203, read_len=150,
+                  pairs=1_000_000, insert=(400, 50), err=0.01,
+                  desc="cfg2 stand-in scaled to the snapshot limit: 28 Mbp x 7 haplotypes, mems on 1M x 2 x 150 bp paired-end reads"),
     "small": dict(base_len=2_000_000, haplotypes=4, seed=5, snp=2e-3, indel=2e-4, read_seed=6, read_len=150,
                   pairs=100_000, insert=(400, 50), err=0.01, desc="functional check: 2 Mbp x 4 haplotypes"),
 }
