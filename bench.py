@@ -157,6 +157,9 @@ def ours_arm(args) -> None:
     t0 = time.time()
     if args.verbose:
         m.set_option("verbose", 1)
+    for kv in args.opt:
+        k, _, val = kv.partition("=")
+        m.set_option(k, val)
     ix = m.MoniIndex(prefix, gpus=[local])
     t_load = time.time() - t0
     log(f"rank {rank}: index n={ix.n} r={ix.r} image {ix.device_bytes / 1e9:.2f} GB loaded in {t_load:.1f} s")
@@ -278,7 +281,7 @@ def ours_arm(args) -> None:
                 "d2h_bytes_per_step": int(8 * (n_reads + 1) + 16 * n_mems), "ms_per_step_wall": e2e_wall_ms / args.steps,
                 "ms_per_step_device": e2e_dev_ms / args.steps, "same_bits_as_resident_run": same,
                 "stage_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage / args.steps).tolist()))},
-        "gpu_launches": int(launches), "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
+        "gpu_launches": int(launches), "options": args.opt, "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -296,6 +299,7 @@ def main():
     ap.add_argument("--ref-reads", type=int, default=100_000, help="reads in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="library option key=value (moni_gpu_set_option), repeatable")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

@@ -242,10 +242,10 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
 void build_grammar_table(const FlatSlp& g, const ExportOptions& opt, HostImage& img) {
     const double t0 = now_s();
     const uint64_t A = g.alph_size, NR = g.num_rules;
-    const uint64_t L = std::max<uint32_t>(opt.leaf_len, 1);
+    const uint64_t L = std::max<uint64_t>(opt.leaf_len, 1);
     if (g.text_len == 0) throw std::runtime_error("exporter: empty grammar");
     img.hdr.text_len = g.text_len;
-    img.hdr.leaf_len = (uint32_t)L;
+    img.hdr.leaf_len = (uint32_t)std::min<uint64_t>(L, 0xFFFFFFFFull);
     img.hdr.pool_shift = 3;
     const uint64_t align = 1ULL << img.hdr.pool_shift;
     auto explen = [&](uint32_t v) -> uint64_t { return v < A ? 1 : g.explen[v - A]; };

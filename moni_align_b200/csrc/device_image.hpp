@@ -111,7 +111,7 @@ struct FlatRlbwt;
 struct FlatSlp;
 
 struct ExportOptions {
-    uint32_t leaf_len = 128;     // variables expanding to <= leaf_len bytes become literal blocks
+    uint64_t leaf_len = 128;     // variables expanding to <= leaf_len bytes become literal blocks
     uint32_t max_scan = 8;       // balancing target: rows covered by one row's LF image
     uint32_t max_rounds = 24;
     bool verbose = false;

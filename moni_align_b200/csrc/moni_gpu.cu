@@ -1,9 +1,13 @@
 // libmoni_gpu.so: CUDA kernels (sm_100a) and the C ABI of include/moni_gpu.h.
 //
-// Kernel mapping (DESIGN.md "Kernels"): one read per thread.  Every backward step of pass 1 is one
-// dependent random 32-byte sector (a MoveRow), so throughput comes from the ~10^5 independent
-// reads in flight per GPU, not from cooperation inside a read; the per-read arithmetic lives in
-// ms_core.cuh.  No tensor cores, no CPU fallback: without a device every entry point fails.
+// Kernel mapping (DESIGN.md "Kernels"): one read per thread, 32 reads per warp.  Every backward step
+// of pass 1 is one dependent random 32-byte sector (a MoveRow, fetched with one LDG.256), so
+// throughput comes from the ~10^5 independent reads in flight per GPU, not from cooperation inside
+// a read.  What the warp does share is the traffic around the walk: the read bytes of its 32 reads
+// are staged through shared memory 32 steps at a time with coalesced loads, and the pointers are
+// stored warp-transposed (step-major, lane-minor) so that every store instruction writes one
+// contiguous 256-byte line.  The per-read arithmetic lives in ms_core.cuh.
+// No tensor cores, no CPU fallback: without a device every entry point fails.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -18,6 +22,7 @@
 #include <thread>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include "../../include/moni_gpu.h"
@@ -30,7 +35,9 @@ using namespace moni;
 // ================================================================================ kernels
 namespace {
 
-constexpr int kBlock = 128;
+constexpr int kBlock = 128;          // 4 warps; warps never synchronise with each other after the prologue
+constexpr int kTile = 32;            // steps staged per refill
+constexpr int kTileStride = 36;      // bytes per read in the tile: 9 words, odd -> conflict-free column reads
 
 __device__ __forceinline__ void flush_counters(const Counters& c, Counters* g) {
     atomicAdd(&g->bases, c.bases);
@@ -43,56 +50,132 @@ __device__ __forceinline__ void flush_counters(const Counters& c, Counters* g) {
     atomicAdd(&g->descents, c.descents);
 }
 
-// Pass 1: MS pointers.  ptr[] uses the layout of seqs[] (chunk-relative offsets = offs[r] - base).
+// How the reads of a chunk map to threads and where a warp keeps its pointers.
+//   slot  = global thread index; read = perm ? perm[slot] : slot   (perm sorts ragged chunks by length,
+//           longest first, so the 32 reads of a warp retire together and padding stays small)
+//   pointers of warp w: ptr_t[wbase(w) + step * 32 + lane], step = number of symbols consumed before
+//           (query offset i = m - 1 - step); wbase(w) = w * 32 * uniform_len, or wbase[w] for ragged chunks.
+struct ChunkMap {
+    const uint64_t* offs;      // n_reads + 1 absolute offsets into the caller's seqs
+    const uint32_t* perm;      // or null
+    const uint64_t* wbase;     // or null (uniform_len != 0)
+    uint64_t base;             // offs[0]: seqs on the device start here
+    uint32_t n_reads;
+    uint32_t uniform_len;
+};
+
+__device__ __forceinline__ uint64_t warp_base(const ChunkMap& cm, uint32_t w) {
+    return cm.wbase ? __ldg(cm.wbase + w) : (uint64_t)w * 32u * cm.uniform_len;
+}
+
+__device__ __forceinline__ uint32_t warp_max(uint32_t x) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) x = max(x, __shfl_xor_sync(0xFFFFFFFFu, x, o));
+    return x;
+}
+
+// ---- chunk preparation (ragged chunks only) -----------------------------------------------------
+__global__ void k_read_len(const uint64_t* __restrict__ offs, uint32_t n, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    keys[r] = (uint32_t)(offs[r + 1] - offs[r]);
+    vals[r] = r;
+}
+
+// ext[w] = 32 * (longest read of warp w); ext[n_warps] = 0.  An exclusive scan turns it into wbase.
+__global__ void k_warp_extent(const uint64_t* __restrict__ offs, const uint32_t* __restrict__ perm, uint32_t n, uint32_t n_warps,
+                              uint64_t* __restrict__ ext) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, w = slot >> 5;
+    if (w > n_warps) return;
+    uint32_t m = 0;
+    if (slot < n) {
+        const uint32_t r = perm ? perm[slot] : slot;
+        m = (uint32_t)(offs[r + 1] - offs[r]);
+    }
+    m = warp_max(m);
+    if ((threadIdx.x & 31) == 0) ext[w] = w < n_warps ? (uint64_t)m * 32u : 0;
+}
+
+// ---- pass 1: MS pointers -------------------------------------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock) k_ms_pointers(ImageView v, const uint8_t* __restrict__ seqs,
-                                                        const uint64_t* __restrict__ offs, uint64_t base,
-                                                        uint32_t n_reads, uint64_t* __restrict__ ptr, Counters* g) {
+__global__ void __launch_bounds__(kBlock) k_ms_pointers(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
+                                                        uint64_t* __restrict__ ptr_t, Counters* g) {
     __shared__ uint8_t tcode[256];
+    __shared__ __align__(16) uint8_t tiles[kBlock / 32][32 * kTileStride];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) tcode[i] = v.sym->tcode[i];
     __syncthreads();
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_reads) return;
-    const uint64_t o = offs[r] - base, m = offs[r + 1] - offs[r];
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
+    if ((w << 5) >= cm.n_reads) return;                       // warp-uniform
+    uint8_t* tile = tiles[threadIdx.x >> 5];
+    uint32_t o = 0, m = 0;                                    // chunk-relative offset (< 2^32) and length
+    if (slot < cm.n_reads) {
+        const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
+        const uint64_t a = __ldg(cm.offs + r);
+        o = (uint32_t)(a - cm.base);
+        m = (uint32_t)(__ldg(cm.offs + r + 1) - a);
+    }
+    const uint32_t mw = warp_max(m);
+    uint64_t* out = ptr_t + warp_base(cm, w) + lane;
     ScanState s;
     scan_init(v, s);
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (uint64_t j = m; j-- > 0;) {
-        scan_step(v, tcode, seqs[o + j], s, COUNT ? &c : nullptr);
-        ptr[o + j] = s.sample;
+    for (uint32_t t0 = 0; t0 < mw; t0 += kTile) {
+        __syncwarp();
+        // refill: lane L fetches the byte of step t0 + L for each of the warp's reads in turn (one
+        // 32-byte window per read: 1-2 sectors per load instruction instead of 32)
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+            const uint32_t o_r = __shfl_sync(0xFFFFFFFFu, o, rr), m_r = __shfl_sync(0xFFFFFFFFu, m, rr);
+            const uint32_t step = t0 + lane;
+            if (step < m_r) tile[rr * kTileStride + lane] = __ldg(seqs + (uint64_t)o_r + (m_r - 1 - step));
+        }
+        __syncwarp();
+        const uint32_t lim = min((uint32_t)kTile, mw - t0);
+        for (uint32_t t = 0; t < lim; ++t) {
+            const uint32_t step = t0 + t;
+            if (step < m) {
+                scan_step(v, tcode, tile[lane * kTileStride + t], s, COUNT ? &c : nullptr);
+                out[(uint64_t)step * 32u] = s.sample;
+            }
+        }
     }
     if (COUNT) { c.bases = m; flush_counters(c, g); }
 }
 
-// Pass 2.  MEMS == false: len[] (u64) per position.  MEMS == true: the read's MEM records are packed
-// in place over its own pointers (record k is produced at query offset i >= k, after ptr[i] was
-// consumed) and counts[r] receives their number.
+// ---- pass 2: MS lengths / MEM records --------------------------------------------------------------
+// MEMS == false: ptr_out[] and len_out[] (u64, laid out like seqs).  MEMS == true: the read's MEM
+// records, packed (i << 32) | len, go to rec[] at the read's own offset (at most one per base) and
+// counts[read] receives their number.
 template <bool MEMS, bool COUNT>
-__global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_t* __restrict__ seqs,
-                                                       const uint64_t* __restrict__ offs, uint64_t base,
-                                                       uint32_t n_reads, uint64_t* ptr, uint64_t* len,
-                                                       uint32_t* counts, Counters* g) {
-    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_reads) return;
-    const uint64_t o = offs[r] - base, m = offs[r + 1] - offs[r];
+__global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
+                                                       const uint64_t* __restrict__ ptr_t, uint64_t* __restrict__ ptr_out,
+                                                       uint64_t* __restrict__ len_out, uint64_t* __restrict__ rec,
+                                                       uint32_t* __restrict__ counts, Counters* g) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
+    if (slot >= cm.n_reads) return;
+    const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
+    const uint64_t a = __ldg(cm.offs + r);
+    const uint64_t o = a - cm.base, m = __ldg(cm.offs + r + 1) - a;
+    if (m == 0) { if (MEMS) counts[r] = 0; return; }
+    const uint64_t* in = ptr_t + warp_base(cm, w) + lane + (m - 1) * 32u;     // query offset 0 = last step
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
-    const uint32_t k = lengths_read<uint64_t>(v, seqs + o, m, ptr + o, MEMS ? nullptr : len + o, MEMS ? ptr + o : nullptr,
-                                              COUNT ? &c : nullptr);
+    const uint32_t k = lengths_read<uint64_t>(v, seqs + o, m, in, -32, MEMS ? nullptr : ptr_out + o, MEMS ? nullptr : len_out + o,
+                                              MEMS ? rec + o : nullptr, COUNT ? &c : nullptr);
     if (MEMS) counts[r] = k;
     if (COUNT) flush_counters(c, g);
 }
 
 // MEM compaction: one warp per read copies its packed records to their final place.
-__global__ void __launch_bounds__(kBlock) k_mem_gather(const uint64_t* __restrict__ packed, const uint64_t* __restrict__ offs,
+__global__ void __launch_bounds__(kBlock) k_mem_gather(const uint64_t* __restrict__ rec, const uint64_t* __restrict__ offs,
                                                        uint64_t base, uint32_t n_reads, const uint64_t* __restrict__ moff,
                                                        uint64_t* __restrict__ mem_pos, uint64_t* __restrict__ mem_len) {
     const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (r >= n_reads) return;
     const uint64_t o = offs[r] - base, a = moff[r], cnt = moff[r + 1] - a;
     for (uint64_t k = lane; k < cnt; k += 32) {
-        const uint64_t rec = packed[o + k];
-        mem_pos[a + k] = rec >> 32;
-        mem_len[a + k] = rec & 0xFFFFFFFFull;
+        const uint64_t x = rec[o + k];
+        mem_pos[a + k] = x >> 32;
+        mem_len[a + k] = x & 0xFFFFFFFFull;
     }
 }
 
@@ -112,9 +195,11 @@ std::atomic<uint64_t> g_launches{0};
 std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
-    uint32_t leaf_len = 128, max_scan = 8;
+    uint64_t leaf_len = 128;
+    uint32_t max_scan = 8;
     bool verbose = false, count = false;
     uint64_t chunk_bases = 1ull << 26;
+    uint32_t l2_fetch = 0;          // 0 = leave the device default
 };
 Options g_opt;
 std::mutex g_opt_mu;
@@ -150,30 +235,82 @@ struct DevBuf {
     T* as() const { return (T*)p; }
 };
 
-struct Scratch {   // device buffers of one batch / one chunk
-    DevBuf seqs, offs, ptr, len, counts, moff, mem_pos, mem_len, cub;
+// What the host knows about a chunk before it is enqueued.
+struct ChunkPlan {
+    uint64_t first = 0, n = 0;          // reads [first, first + n) of the caller's batch
+    uint64_t base = 0, bases = 0;       // offsets[first], total bases
+    uint32_t uniform_len = 0;           // common read length, or 0 for a ragged chunk
+    uint64_t max_len = 0;
+    uint64_t n_warps() const { return (n + 31) / 32; }
+    bool ragged() const { return uniform_len == 0 && max_len != 0; }
+    // entries of the warp-transposed pointer buffer: exact when uniform, else the bound that holds
+    // once reads are sorted by length (sum over warps of 32 * longest <= bases + 32 * max_len)
+    uint64_t ptr_entries() const { return ragged() ? bases + 32 * max_len + 32 : n_warps() * 32 * (uint64_t)uniform_len + 32; }
+};
+
+struct Scratch {   // device buffers of one chunk
+    DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, wbase, ptr_t, out_ptr, out_len, rec, counts, moff, mem_pos, mem_len, cub;
     void release() {
-        seqs.release(); offs.release(); ptr.release(); len.release(); counts.release();
-        moff.release(); mem_pos.release(); mem_len.release(); cub.release();
+        for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &wbase, &ptr_t, &out_ptr, &out_len, &rec, &counts, &moff,
+                          &mem_pos, &mem_len, &cub})
+            b->release();
+    }
+    void reserve(const ChunkPlan& p, bool ms, bool mems) {
+        seqs.reserve(p.bases + 16);
+        offs.reserve((p.n + 1) * 8);
+        ptr_t.reserve(p.ptr_entries() * 8);
+        if (p.ragged()) {
+            keys_in.reserve(p.n * 4); keys_out.reserve(p.n * 4); vals_in.reserve(p.n * 4); perm.reserve(p.n * 4);
+            wbase.reserve((p.n_warps() + 1) * 8);
+        }
+        if (ms) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); }
+        if (mems) {
+            rec.reserve(p.bases * 8 + 16);
+            counts.reserve((p.n + 1) * 4);
+            moff.reserve((p.n + 1) * 16);
+            mem_pos.reserve(p.bases * 8 + 16);
+            mem_len.reserve(p.bases * 8 + 16);
+        }
+    }
+};
+
+constexpr int kLanes = 2;        // chunks in flight per GPU: copies of one overlap the kernels of the other
+constexpr int kEv = 6;           // events per chunk: start, h2d done, pass 1 done, pass 2 done, compaction done, d2h done
+
+struct Lane {
+    cudaStream_t stream = nullptr;
+    Scratch scratch;
+    std::vector<cudaEvent_t> events;     // kEv per chunk processed on this lane in the current call
+    size_t used = 0;
+    cudaEvent_t* take() {
+        if (used + kEv > events.size()) {
+            const size_t old = events.size();
+            events.resize(old + kEv, nullptr);
+            for (size_t i = old; i < events.size(); ++i) CK(cudaEventCreate(&events[i]));
+        }
+        cudaEvent_t* e = events.data() + used;     // callers finish with the pointer before the next take()
+        used += kEv;
+        return e;
     }
 };
 
 struct Replica {
     int dev = 0;
-    cudaStream_t stream = nullptr;
+    Lane lanes[kLanes];
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
     ImageView view;
-    Scratch scratch;
-    cudaEvent_t ev[8] = {nullptr};
     std::mutex mu;
     double t[6] = {0, 0, 0, 0, 0, 0};
+    cudaStream_t stream() const { return lanes[0].stream; }
     ~Replica() {
         cudaSetDevice(dev);
         rows.release(); row_pos.release(); crun_row.release(); slots.release(); nodes.release(); pool.release();
         sym.release(); counters.release();
-        scratch.release();
-        for (auto& e : ev) if (e) cudaEventDestroy(e);
-        if (stream) cudaStreamDestroy(stream);
+        for (Lane& L : lanes) {
+            L.scratch.release();
+            for (auto& e : L.events) if (e) cudaEventDestroy(e);
+            if (L.stream) cudaStreamDestroy(L.stream);
+        }
     }
 };
 
@@ -197,77 +334,98 @@ struct moni_gpu_batch {
     moni_gpu_index* idx = nullptr;
     Replica* rep = nullptr;
     Scratch s;
-    uint64_t n_reads = 0, total = 0, n_mems = 0;
-    std::vector<uint64_t> offsets;   // host copy (for sizes)
+    ChunkPlan plan;
+    uint64_t n_mems = 0;
     int last = 0;
+    bool prepared = false;
 };
 
 namespace {
 
-// ---- one chunk on one replica (device pointers already filled) ---------------------------------
-struct ChunkTimes { float pass1 = 0, pass2 = 0, compact = 0; };
+// ---- one chunk on one stream (device pointers already filled) ------------------------------------
+ChunkMap chunk_map(const Scratch& S, const ChunkPlan& p) {
+    ChunkMap cm;
+    cm.offs = S.offs.as<uint64_t>();
+    cm.perm = p.ragged() ? S.perm.as<uint32_t>() : nullptr;
+    cm.wbase = p.ragged() ? S.wbase.as<uint64_t>() : nullptr;
+    cm.base = p.base;
+    cm.n_reads = (uint32_t)p.n;
+    cm.uniform_len = p.uniform_len;
+    return cm;
+}
 
-void launch_pass1(Replica& R, Scratch& S, uint64_t base, uint32_t n) {
-    if (!n) return;
-    const dim3 grid((n + kBlock - 1) / kBlock);
+// Ragged chunks: sort the reads by length (longest first) and lay out the per-warp pointer areas.
+void launch_prepare(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
+    if (!p.ragged()) return;
+    const uint32_t n = (uint32_t)p.n, nw = (uint32_t)p.n_warps();
+    k_read_len<<<(n + 255) / 256, 256, 0, st>>>(S.offs.as<uint64_t>(), n, S.keys_in.as<uint32_t>(), S.vals_in.as<uint32_t>());
+    g_launches++;
+    int bits = 1;
+    while (bits < 32 && (p.max_len >> bits)) ++bits;
+    size_t tmp = 0;
+    CK(cub::DeviceRadixSort::SortPairsDescending(nullptr, tmp, S.keys_in.as<uint32_t>(), S.keys_out.as<uint32_t>(), S.vals_in.as<uint32_t>(),
+                                                 S.perm.as<uint32_t>(), (int)n, 0, bits, st));
+    S.cub.reserve(tmp);
+    CK(cub::DeviceRadixSort::SortPairsDescending(S.cub.p, tmp, S.keys_in.as<uint32_t>(), S.keys_out.as<uint32_t>(), S.vals_in.as<uint32_t>(),
+                                                 S.perm.as<uint32_t>(), (int)n, 0, bits, st));
+    g_launches += 3;
+    k_warp_extent<<<(nw * 32 + 32 + 255) / 256, 256, 0, st>>>(S.offs.as<uint64_t>(), S.perm.as<uint32_t>(), n, nw, S.wbase.as<uint64_t>());
+    g_launches++;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, S.wbase.as<uint64_t>(), S.wbase.as<uint64_t>(), (int)(nw + 1), st));
+    S.cub.reserve(tmp);
+    CK(cub::DeviceScan::ExclusiveSum(S.cub.p, tmp, S.wbase.as<uint64_t>(), S.wbase.as<uint64_t>(), (int)(nw + 1), st));
+    g_launches += 2;
+    CK(cudaGetLastError());
+}
+
+void launch_pass1(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st) {
+    if (!p.n) return;
+    const dim3 grid((unsigned)((p.n_warps() * 32 + kBlock - 1) / kBlock));
+    const ChunkMap cm = chunk_map(S, p);
     if (g_count.load())
-        k_ms_pointers<true><<<grid, kBlock, 0, R.stream>>>(R.view, S.seqs.as<uint8_t>(), S.offs.as<uint64_t>(), base, n,
-                                                           S.ptr.as<uint64_t>(), R.counters.as<Counters>());
+        k_ms_pointers<true><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.ptr_t.as<uint64_t>(), R.counters.as<Counters>());
     else
-        k_ms_pointers<false><<<grid, kBlock, 0, R.stream>>>(R.view, S.seqs.as<uint8_t>(), S.offs.as<uint64_t>(), base, n,
-                                                            S.ptr.as<uint64_t>(), nullptr);
+        k_ms_pointers<false><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.ptr_t.as<uint64_t>(), nullptr);
     g_launches++;
     CK(cudaGetLastError());
 }
 
-void launch_pass2(Replica& R, Scratch& S, uint64_t base, uint32_t n, bool mems) {
-    if (!n) return;
-    const dim3 grid((n + kBlock - 1) / kBlock);
-    Counters* g = R.counters.as<Counters>();
+void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, bool mems, cudaStream_t st) {
+    if (!p.n) return;
+    const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
+    const ChunkMap cm = chunk_map(S, p);
+    Counters* g = g_count.load() ? R.counters.as<Counters>() : nullptr;
     const uint8_t* sq = S.seqs.as<uint8_t>();
-    const uint64_t* of = S.offs.as<uint64_t>();
-    uint64_t* p = S.ptr.as<uint64_t>();
+    const uint64_t* pt = S.ptr_t.as<uint64_t>();
     if (mems) {
-        if (g_count.load()) k_ms_lengths<true, true><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, nullptr, S.counts.as<uint32_t>(), g);
-        else k_ms_lengths<true, false><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, nullptr, S.counts.as<uint32_t>(), nullptr);
+        if (g) k_ms_lengths<true, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, S.rec.as<uint64_t>(), S.counts.as<uint32_t>(), g);
+        else k_ms_lengths<true, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, S.rec.as<uint64_t>(), S.counts.as<uint32_t>(), nullptr);
     } else {
-        if (g_count.load()) k_ms_lengths<false, true><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, S.len.as<uint64_t>(), nullptr, g);
-        else k_ms_lengths<false, false><<<grid, kBlock, 0, R.stream>>>(R.view, sq, of, base, n, p, S.len.as<uint64_t>(), nullptr, nullptr);
+        if (g) k_ms_lengths<false, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, g);
+        else k_ms_lengths<false, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, nullptr);
     }
     g_launches++;
     CK(cudaGetLastError());
 }
 
-// counts -> exclusive offsets (n + 1 entries) -> gather.  Buffers mem_pos/mem_len must hold `total_bases` entries.
-void launch_compact(Replica& R, Scratch& S, uint64_t base, uint32_t n) {
-    if (!n) return;
+// counts -> exclusive offsets (n + 1 entries) -> gather.  mem_pos/mem_len hold `bases` entries.
+void launch_compact(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
+    if (!p.n) return;
+    const uint32_t n = (uint32_t)p.n;
     uint64_t* wide = S.moff.as<uint64_t>() + (n + 1);          // second half of moff: widened counts
-    k_widen_counts<<<(n + 1 + 255) / 256, 256, 0, R.stream>>>(S.counts.as<uint32_t>(), wide, n);
+    k_widen_counts<<<(n + 1 + 255) / 256, 256, 0, st>>>(S.counts.as<uint32_t>(), wide, n);
     g_launches++;
     size_t tmp = 0;
-    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, wide, S.moff.as<uint64_t>(), (int)(n + 1), R.stream));
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, wide, S.moff.as<uint64_t>(), (int)(n + 1), st));
     S.cub.reserve(tmp);
-    CK(cub::DeviceScan::ExclusiveSum(S.cub.p, tmp, wide, S.moff.as<uint64_t>(), (int)(n + 1), R.stream));
-    g_launches++;
+    CK(cub::DeviceScan::ExclusiveSum(S.cub.p, tmp, wide, S.moff.as<uint64_t>(), (int)(n + 1), st));
+    g_launches += 2;
     const uint64_t threads = (uint64_t)n * 32;
-    k_mem_gather<<<(unsigned)((threads + kBlock - 1) / kBlock), kBlock, 0, R.stream>>>(
-        S.ptr.as<uint64_t>(), S.offs.as<uint64_t>(), base, n, S.moff.as<uint64_t>(), S.mem_pos.as<uint64_t>(), S.mem_len.as<uint64_t>());
+    k_mem_gather<<<(unsigned)((threads + kBlock - 1) / kBlock), kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n,
+                                                                                 S.moff.as<uint64_t>(), S.mem_pos.as<uint64_t>(),
+                                                                                 S.mem_len.as<uint64_t>());
     g_launches++;
     CK(cudaGetLastError());
-}
-
-void reserve_scratch(Scratch& S, uint64_t n, uint64_t bases, bool mems) {
-    S.seqs.reserve(bases + 16);
-    S.offs.reserve((n + 1) * 8);
-    S.ptr.reserve(bases * 8 + 16);
-    if (mems) {
-        S.counts.reserve((n + 1) * 4);
-        S.moff.reserve((n + 1) * 16);
-        S.mem_pos.reserve(bases * 8 + 16);
-        S.mem_len.reserve(bases * 8 + 16);
-    } else {
-        S.len.reserve(bases * 8 + 16);
-    }
 }
 
 float ev_ms(cudaEvent_t a, cudaEvent_t b) {
@@ -276,62 +434,114 @@ float ev_ms(cudaEvent_t a, cudaEvent_t b) {
     return ms;
 }
 
-// Processes reads [r0, r1) of a host batch on one replica, chunk by chunk.  For mems, records go to
-// rec_pos/rec_len (contiguous from index 0, capacity rec_cap) and per-read record offsets (relative
-// to this shard) to rec_off[0 .. r1-r0]; *needed receives the number of records of the shard.
+// Next chunk of reads [a, r1): as many reads as fit chunk_bases (at least one).
+ChunkPlan plan_chunk(const uint64_t* offsets, uint64_t a, uint64_t r1, uint64_t chunk_bases) {
+    ChunkPlan p;
+    p.first = a;
+    p.base = offsets[a];
+    uint64_t b = a, lo = ~0ull, hi = 0;
+    while (b < r1 && (b == a || offsets[b + 1] - offsets[a] <= chunk_bases) && b - a < 0x7FFFFFE0ull) {
+        const uint64_t m = offsets[b + 1] - offsets[b];
+        lo = std::min(lo, m);
+        hi = std::max(hi, m);
+        ++b;
+    }
+    p.n = b - a;
+    p.bases = offsets[b] - p.base;
+    p.max_len = hi;
+    p.uniform_len = (lo == hi) ? (uint32_t)hi : 0;
+    return p;
+}
+
+__global__ void k_shift(uint64_t* __restrict__ a, uint64_t n, uint64_t by) {
+    const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (i < n) a[i] += by;
+}
+
+// Processes reads [r0, r1) of a host batch on one replica.  Chunks alternate between the replica's
+// lanes (stream + scratch each), so the copies of one chunk overlap the kernels of the other.
+// mems: records go to rec_pos/rec_len (contiguous from index 0, capacity rec_cap) and per-read record
+// offsets (relative to this shard) to rec_off[0 .. r1-r0]; *needed receives the shard's record count.
 void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, const uint64_t* offsets, uint64_t r0, uint64_t r1,
                uint64_t* pointers, uint64_t* lengths, uint64_t* rec_off, uint64_t* rec_pos, uint64_t* rec_len, uint64_t rec_cap,
                uint64_t* needed) {
     std::lock_guard<std::mutex> lock(R.mu);
     CK(cudaSetDevice(R.dev));
     for (double& x : R.t) x = 0;
-    Scratch& S = R.scratch;
+    std::vector<ChunkPlan> plans;
+    for (uint64_t a = r0; a < r1;) {
+        plans.push_back(plan_chunk(offsets, a, r1, idx->opt.chunk_bases));
+        a += plans.back().n;
+    }
+    const size_t nc = plans.size();
+    for (Lane& L : R.lanes) L.used = 0;
+    std::vector<size_t> ev_at(nc);
     uint64_t rec_total = 0;
     if (mems) rec_off[0] = 0;
-    std::vector<uint64_t> moff_host;
-    const uint64_t chunk_bases = idx->opt.chunk_bases;
-    for (uint64_t a = r0; a < r1;) {
-        uint64_t b = a + 1;
-        while (b < r1 && offsets[b + 1] - offsets[a] <= chunk_bases && b - a < 0x7FFFFFF0ull) ++b;
-        const uint64_t n = b - a, base = offsets[a], bases = offsets[b] - base;
-        reserve_scratch(S, n, bases, mems);
-        CK(cudaEventRecord(R.ev[0], R.stream));
-        if (bases) CK(cudaMemcpyAsync(S.seqs.p, seqs + base, bases, cudaMemcpyHostToDevice, R.stream));
-        CK(cudaMemcpyAsync(S.offs.p, offsets + a, (n + 1) * 8, cudaMemcpyHostToDevice, R.stream));
-        CK(cudaEventRecord(R.ev[1], R.stream));
-        launch_pass1(R, S, base, (uint32_t)n);
-        CK(cudaEventRecord(R.ev[2], R.stream));
-        launch_pass2(R, S, base, (uint32_t)n, mems);
-        CK(cudaEventRecord(R.ev[3], R.stream));
+
+    auto enqueue_front = [&](size_t c) {
+        const ChunkPlan& p = plans[c];
+        Lane& L = R.lanes[c % kLanes];
+        Scratch& S = L.scratch;
+        S.reserve(p, !mems, mems);
+        ev_at[c] = L.used;
+        L.take();
+        cudaEvent_t* e = L.events.data() + ev_at[c];
+        CK(cudaEventRecord(e[0], L.stream));
+        if (p.bases) CK(cudaMemcpyAsync(S.seqs.p, seqs + p.base, p.bases, cudaMemcpyHostToDevice, L.stream));
+        CK(cudaMemcpyAsync(S.offs.p, offsets + p.first, (p.n + 1) * 8, cudaMemcpyHostToDevice, L.stream));
+        CK(cudaEventRecord(e[1], L.stream));
+        launch_prepare(S, p, L.stream);
+        launch_pass1(R, S, p, L.stream);
+        CK(cudaEventRecord(e[2], L.stream));
+        launch_pass2(R, S, p, mems, L.stream);
+        CK(cudaEventRecord(e[3], L.stream));
         if (mems) {
-            launch_compact(R, S, base, (uint32_t)n);
-            CK(cudaEventRecord(R.ev[4], R.stream));
-            moff_host.resize(n + 1);
-            CK(cudaMemcpyAsync(moff_host.data(), S.moff.p, (n + 1) * 8, cudaMemcpyDeviceToHost, R.stream));
-            CK(cudaStreamSynchronize(R.stream));
-            const uint64_t k = moff_host[n];
-            for (uint64_t i = 0; i <= n; ++i) rec_off[a - r0 + i] = rec_total + moff_host[i];
-            if (rec_total + k <= rec_cap && k) {
-                CK(cudaMemcpyAsync(rec_pos + rec_total, S.mem_pos.p, k * 8, cudaMemcpyDeviceToHost, R.stream));
-                CK(cudaMemcpyAsync(rec_len + rec_total, S.mem_len.p, k * 8, cudaMemcpyDeviceToHost, R.stream));
-            }
-            rec_total += k;
+            launch_compact(S, p, L.stream);
+            CK(cudaEventRecord(e[4], L.stream));
         } else {
-            CK(cudaEventRecord(R.ev[4], R.stream));
-            if (bases) {
-                CK(cudaMemcpyAsync(pointers + base, S.ptr.p, bases * 8, cudaMemcpyDeviceToHost, R.stream));
-                CK(cudaMemcpyAsync(lengths + base, S.len.p, bases * 8, cudaMemcpyDeviceToHost, R.stream));
+            CK(cudaEventRecord(e[4], L.stream));
+            if (p.bases) {
+                CK(cudaMemcpyAsync(pointers + p.base, S.out_ptr.p, p.bases * 8, cudaMemcpyDeviceToHost, L.stream));
+                CK(cudaMemcpyAsync(lengths + p.base, S.out_len.p, p.bases * 8, cudaMemcpyDeviceToHost, L.stream));
             }
+            CK(cudaEventRecord(e[5], L.stream));
         }
-        CK(cudaEventRecord(R.ev[5], R.stream));
-        CK(cudaStreamSynchronize(R.stream));
-        R.t[0] += ev_ms(R.ev[0], R.ev[1]);
-        R.t[1] += ev_ms(R.ev[1], R.ev[2]);
-        R.t[2] += ev_ms(R.ev[2], R.ev[3]);
-        R.t[3] += ev_ms(R.ev[3], R.ev[4]);
-        R.t[4] += ev_ms(R.ev[4], R.ev[5]);
-        R.t[5] += ev_ms(R.ev[0], R.ev[5]);
-        a = b;
+    };
+    // mems only: learn the chunk's record count, then send offsets (shifted to shard-relative) and records home
+    auto finish_mems = [&](size_t c) {
+        const ChunkPlan& p = plans[c];
+        Lane& L = R.lanes[c % kLanes];
+        Scratch& S = L.scratch;
+        cudaEvent_t* e = L.events.data() + ev_at[c];
+        uint64_t k = 0;
+        CK(cudaMemcpyAsync(&k, S.moff.as<uint64_t>() + p.n, 8, cudaMemcpyDeviceToHost, L.stream));
+        CK(cudaStreamSynchronize(L.stream));
+        if (rec_total) {
+            k_shift<<<(unsigned)((p.n + 1 + 255) / 256), 256, 0, L.stream>>>(S.moff.as<uint64_t>(), p.n + 1, rec_total);
+            g_launches++;
+        }
+        const bool last = c + 1 == nc;
+        CK(cudaMemcpyAsync(rec_off + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
+        if (rec_total + k <= rec_cap && k) {
+            CK(cudaMemcpyAsync(rec_pos + rec_total, S.mem_pos.p, k * 8, cudaMemcpyDeviceToHost, L.stream));
+            CK(cudaMemcpyAsync(rec_len + rec_total, S.mem_len.p, k * 8, cudaMemcpyDeviceToHost, L.stream));
+        }
+        CK(cudaEventRecord(e[5], L.stream));
+        rec_total += k;
+    };
+
+    if (nc) enqueue_front(0);
+    for (size_t c = 0; c < nc; ++c) {
+        if (c + 1 < nc) enqueue_front(c + 1);
+        if (mems) finish_mems(c);
+    }
+    for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
+    for (size_t c = 0; c < nc; ++c) {
+        cudaEvent_t* e = R.lanes[c % kLanes].events.data() + ev_at[c];
+        for (int k = 0; k < 5; ++k) R.t[k] += ev_ms(e[k], e[k + 1]);
+        cudaEvent_t* e0 = R.lanes[0].events.data() + ev_at[0];
+        R.t[5] = std::max<double>(R.t[5], ev_ms(e0[0], e[5]));
     }
     if (needed) *needed = rec_total;
 }
@@ -385,7 +595,7 @@ void collect_times(moni_gpu_index* idx) {
 extern "C" {
 
 const char* moni_gpu_last_error(void) { return g_err.c_str(); }
-const char* moni_gpu_version(void) { return "moni-gpu 0.1 (sm_100a)"; }
+const char* moni_gpu_version(void) { return "moni-gpu 0.2 (sm_100a)"; }
 uint64_t moni_gpu_launch_count(void) { return g_launches.load(); }
 
 int moni_gpu_set_option(const char* key, const char* value) {
@@ -393,11 +603,12 @@ int moni_gpu_set_option(const char* key, const char* value) {
     std::lock_guard<std::mutex> lock(g_opt_mu);
     const std::string k(key);
     const long long v = atoll(value);
-    if (k == "leaf_len" && v >= 1 && v <= (1 << 20)) g_opt.leaf_len = (uint32_t)v;
+    if (k == "leaf_len" && v >= 1 && v <= (1ll << 40)) g_opt.leaf_len = (uint64_t)v;
     else if (k == "max_scan" && v >= 2 && v <= 4096) g_opt.max_scan = (uint32_t)v;
     else if (k == "verbose") g_opt.verbose = v != 0;
     else if (k == "count") { g_opt.count = v != 0; g_count.store(v != 0); }
-    else if (k == "chunk_bases" && v >= 1) g_opt.chunk_bases = (uint64_t)v;
+    else if (k == "chunk_bases" && v >= 1 && v <= (1ll << 31)) g_opt.chunk_bases = (uint64_t)v;
+    else if (k == "l2_fetch" && (v == 0 || v == 32 || v == 64 || v == 128)) g_opt.l2_fetch = (uint32_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }
     return 0;
 }
@@ -431,7 +642,6 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
         HostImage img;
         {
             ExportOptions eo;
-            eo.leaf_len = idx->opt.leaf_len;
             eo.max_scan = idx->opt.max_scan;
             eo.verbose = idx->opt.verbose;
             FlatRlbwt bwt;
@@ -452,19 +662,20 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             std::unique_ptr<Replica> R(new Replica);
             R->dev = devs[g];
             CK(cudaSetDevice(R->dev));
-            CK(cudaStreamCreateWithFlags(&R->stream, cudaStreamNonBlocking));
-            for (auto& e : R->ev) CK(cudaEventCreate(&e));
-            upload(R->rows, img.rows, R->stream);
-            upload(R->row_pos, img.row_pos, R->stream);
-            upload(R->crun_row, img.crun_row, R->stream);
-            upload(R->slots, img.slots, R->stream);
-            upload(R->nodes, img.nodes, R->stream);
-            upload(R->pool, img.pool, R->stream);
+            if (idx->opt.l2_fetch) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, idx->opt.l2_fetch));
+            for (Lane& L : R->lanes) CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+            cudaStream_t st = R->stream();
+            upload(R->rows, img.rows, st);
+            upload(R->row_pos, img.row_pos, st);
+            upload(R->crun_row, img.crun_row, st);
+            upload(R->slots, img.slots, st);
+            upload(R->nodes, img.nodes, st);
+            upload(R->pool, img.pool, st);
             R->sym.reserve(sizeof(SymbolTables));
-            CK(cudaMemcpyAsync(R->sym.p, &img.sym, sizeof(SymbolTables), cudaMemcpyHostToDevice, R->stream));
+            CK(cudaMemcpyAsync(R->sym.p, &img.sym, sizeof(SymbolTables), cudaMemcpyHostToDevice, st));
             R->counters.reserve(sizeof(Counters));
-            CK(cudaMemsetAsync(R->counters.p, 0, sizeof(Counters), R->stream));
-            CK(cudaStreamSynchronize(R->stream));
+            CK(cudaMemsetAsync(R->counters.p, 0, sizeof(Counters), st));
+            CK(cudaStreamSynchronize(st));
             ImageView& v = R->view;
             v.rows = R->rows.as<MoveRow>();
             v.row_pos = R->row_pos.as<uint64_t>();
@@ -547,11 +758,11 @@ int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets
                     Part& P = parts[g];
                     P.rc = guarded([&]() -> int {
                         const uint64_t nr = cut[g + 1] - cut[g], cap = offsets[cut[g + 1]] - offsets[cut[g]];
-                        P.off.resize(nr + 1);
+                        P.off.assign(nr + 1, 0);
                         P.pos.resize(cap + 1);
                         P.len.resize(cap + 1);
-                        run_shard(idx, *idx->reps[g], true, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, P.off.data(), P.pos.data(),
-                                  P.len.data(), cap, &P.k);
+                        if (nr) run_shard(idx, *idx->reps[g], true, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, P.off.data(), P.pos.data(),
+                                          P.len.data(), cap, &P.k);
                         return 0;
                     });
                     if (P.rc) P.err = g_err;
@@ -586,9 +797,9 @@ int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset) {
             std::lock_guard<std::mutex> lock(R->mu);
             CK(cudaSetDevice(R->dev));
             Counters h;
-            CK(cudaMemcpyAsync(&h, R->counters.p, sizeof(h), cudaMemcpyDeviceToHost, R->stream));
-            if (reset) CK(cudaMemsetAsync(R->counters.p, 0, sizeof(Counters), R->stream));
-            CK(cudaStreamSynchronize(R->stream));
+            CK(cudaMemcpyAsync(&h, R->counters.p, sizeof(h), cudaMemcpyDeviceToHost, R->stream()));
+            if (reset) CK(cudaMemsetAsync(R->counters.p, 0, sizeof(Counters), R->stream()));
+            CK(cudaStreamSynchronize(R->stream()));
             const unsigned long long* p = &h.bases;
             for (int k = 0; k < 8; ++k) c[k] += p[k];
         }
@@ -604,11 +815,12 @@ int moni_gpu_timing(const moni_gpu_index* idx, double t[6]) {
 
 // ---- resident batches ---------------------------------------------------------------------------
 int moni_gpu_batch_create(moni_gpu_index* idx, int gpu_slot, const char* seqs, const uint64_t* offsets, uint64_t n_reads, moni_gpu_batch** out) {
-    if (!idx || !offsets || !out || gpu_slot < 0 || gpu_slot >= (int)idx->reps.size() || n_reads == 0 || n_reads >= 0x7FFFFFF0ull) {
+    if (!idx || !offsets || !out || gpu_slot < 0 || gpu_slot >= (int)idx->reps.size() || n_reads == 0 || n_reads >= 0x7FFFFFE0ull) {
         g_err = "bad arguments";
         return MONI_GPU_EINVAL;
     }
     if (int e = check_batch(offsets, n_reads)) return e;
+    if (offsets[n_reads] - offsets[0] >= 0xFFFFFFFFull) { g_err = "a resident batch holds fewer than 2^32 bases"; return MONI_GPU_EINVAL; }
     *out = nullptr;
     return guarded([&]() -> int {
         std::unique_ptr<moni_gpu_batch> b(new moni_gpu_batch);
@@ -617,14 +829,12 @@ int moni_gpu_batch_create(moni_gpu_index* idx, int gpu_slot, const char* seqs, c
         Replica& R = *b->rep;
         std::lock_guard<std::mutex> lock(R.mu);
         CK(cudaSetDevice(R.dev));
-        b->n_reads = n_reads;
-        b->offsets.assign(offsets, offsets + n_reads + 1);
-        b->total = offsets[n_reads] - offsets[0];
-        reserve_scratch(b->s, n_reads, b->total, true);
-        b->s.len.reserve(b->total * 8 + 16);
-        if (b->total) CK(cudaMemcpyAsync(b->s.seqs.p, seqs + offsets[0], b->total, cudaMemcpyHostToDevice, R.stream));
-        CK(cudaMemcpyAsync(b->s.offs.p, offsets, (n_reads + 1) * 8, cudaMemcpyHostToDevice, R.stream));
-        CK(cudaStreamSynchronize(R.stream));
+        b->plan = plan_chunk(offsets, 0, n_reads, ~0ull);
+        const ChunkPlan& p = b->plan;
+        b->s.reserve(p, true, true);
+        if (p.bases) CK(cudaMemcpyAsync(b->s.seqs.p, seqs + p.base, p.bases, cudaMemcpyHostToDevice, R.stream()));
+        CK(cudaMemcpyAsync(b->s.offs.p, offsets, (n_reads + 1) * 8, cudaMemcpyHostToDevice, R.stream()));
+        CK(cudaStreamSynchronize(R.stream()));
         *out = b.release();
         return 0;
     });
@@ -636,20 +846,24 @@ int moni_gpu_batch_run(moni_gpu_batch* b, int what, float kernel_ms[3]) {
         Replica& R = *b->rep;
         std::lock_guard<std::mutex> lock(R.mu);
         CK(cudaSetDevice(R.dev));
-        const uint64_t base = b->offsets[0];
-        CK(cudaEventRecord(R.ev[0], R.stream));
-        launch_pass1(R, b->s, base, (uint32_t)b->n_reads);
-        CK(cudaEventRecord(R.ev[1], R.stream));
-        launch_pass2(R, b->s, base, (uint32_t)b->n_reads, what == 2);
-        CK(cudaEventRecord(R.ev[2], R.stream));
-        if (what == 2) launch_compact(R, b->s, base, (uint32_t)b->n_reads);
-        CK(cudaEventRecord(R.ev[3], R.stream));
-        CK(cudaStreamSynchronize(R.stream));
+        Lane& L = R.lanes[0];
+        L.used = 0;
+        L.take();
+        cudaEvent_t* e = L.events.data();
+        CK(cudaEventRecord(e[0], L.stream));
+        launch_prepare(b->s, b->plan, L.stream);
+        launch_pass1(R, b->s, b->plan, L.stream);
+        CK(cudaEventRecord(e[1], L.stream));
+        launch_pass2(R, b->s, b->plan, what == 2, L.stream);
+        CK(cudaEventRecord(e[2], L.stream));
+        if (what == 2) launch_compact(b->s, b->plan, L.stream);
+        CK(cudaEventRecord(e[3], L.stream));
+        CK(cudaStreamSynchronize(L.stream));
         b->last = what;
         if (kernel_ms) {
-            kernel_ms[0] = ev_ms(R.ev[0], R.ev[1]);
-            kernel_ms[1] = ev_ms(R.ev[1], R.ev[2]);
-            kernel_ms[2] = ev_ms(R.ev[2], R.ev[3]);
+            kernel_ms[0] = ev_ms(e[0], e[1]);
+            kernel_ms[1] = ev_ms(e[1], e[2]);
+            kernel_ms[2] = ev_ms(e[2], e[3]);
         }
         return 0;
     });
@@ -662,11 +876,11 @@ int moni_gpu_batch_fetch_ms(moni_gpu_batch* b, uint64_t* pointers, uint64_t* len
         Replica& R = *b->rep;
         std::lock_guard<std::mutex> lock(R.mu);
         CK(cudaSetDevice(R.dev));
-        if (b->total) {
-            CK(cudaMemcpyAsync(pointers, b->s.ptr.p, b->total * 8, cudaMemcpyDeviceToHost, R.stream));
-            CK(cudaMemcpyAsync(lengths, b->s.len.p, b->total * 8, cudaMemcpyDeviceToHost, R.stream));
+        if (b->plan.bases) {
+            CK(cudaMemcpyAsync(pointers, b->s.out_ptr.p, b->plan.bases * 8, cudaMemcpyDeviceToHost, R.stream()));
+            CK(cudaMemcpyAsync(lengths, b->s.out_len.p, b->plan.bases * 8, cudaMemcpyDeviceToHost, R.stream()));
         }
-        CK(cudaStreamSynchronize(R.stream));
+        CK(cudaStreamSynchronize(R.stream()));
         return 0;
     });
 }
@@ -678,15 +892,16 @@ int moni_gpu_batch_fetch_mems(moni_gpu_batch* b, uint64_t* mem_offsets, uint64_t
         Replica& R = *b->rep;
         std::lock_guard<std::mutex> lock(R.mu);
         CK(cudaSetDevice(R.dev));
-        CK(cudaMemcpyAsync(mem_offsets, b->s.moff.p, (b->n_reads + 1) * 8, cudaMemcpyDeviceToHost, R.stream));
-        CK(cudaStreamSynchronize(R.stream));
-        const uint64_t k = mem_offsets[b->n_reads];
+        const uint64_t n = b->plan.n;
+        CK(cudaMemcpyAsync(mem_offsets, b->s.moff.p, (n + 1) * 8, cudaMemcpyDeviceToHost, R.stream()));
+        CK(cudaStreamSynchronize(R.stream()));
+        const uint64_t k = mem_offsets[n];
         if (k > mem_capacity) { g_err = "mem_capacity too small: " + std::to_string(k) + " records needed"; return MONI_GPU_ENOMEM; }
         if (k) {
-            CK(cudaMemcpyAsync(mem_pos, b->s.mem_pos.p, k * 8, cudaMemcpyDeviceToHost, R.stream));
-            CK(cudaMemcpyAsync(mem_len, b->s.mem_len.p, k * 8, cudaMemcpyDeviceToHost, R.stream));
+            CK(cudaMemcpyAsync(mem_pos, b->s.mem_pos.p, k * 8, cudaMemcpyDeviceToHost, R.stream()));
+            CK(cudaMemcpyAsync(mem_len, b->s.mem_len.p, k * 8, cudaMemcpyDeviceToHost, R.stream()));
         }
-        CK(cudaStreamSynchronize(R.stream));
+        CK(cudaStreamSynchronize(R.stream()));
         return 0;
     });
 }

@@ -58,13 +58,13 @@ struct RowRegs {
     MONI_HD uint32_t dist_dn(int s) const { return ((w[7] >> 8) >> (8 * s)) & 0xFFu; }
 };
 
+// One 32-byte row = one DRAM sector = one load instruction (sm_100 LDG.E.256).
 MONI_HD RowRegs load_row(const MoveRow* rows, uint64_t i) {
     RowRegs r;
 #if defined(__CUDA_ARCH__)
-    const uint4* p = reinterpret_cast<const uint4*>(rows + i);
-    const uint4 a = __ldg(p), b = __ldg(p + 1);
-    r.w[0] = a.x; r.w[1] = a.y; r.w[2] = a.z; r.w[3] = a.w;
-    r.w[4] = b.x; r.w[5] = b.y; r.w[6] = b.z; r.w[7] = b.w;
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7])
+                 : "l"(rows + i));
 #else
     const uint32_t* p = reinterpret_cast<const uint32_t*>(rows + i);
     for (int k = 0; k < 8; ++k) r.w[k] = p[k];
@@ -217,17 +217,18 @@ MONI_HD const uint8_t* text_block(const ImageView& v, uint64_t tp, uint64_t& rem
     return v.pool + ((uint64_t)(ref & ~kLeafBit) << v.hdr.pool_shift) + p;
 }
 
-// The length loop for one read.  ptr[] are the pass-1 pointers of this read.  Writes len[i] (if
-// len != nullptr) and returns the number of MEM records; records are written to mem_out (packed
-// (i << 32) | len) when mem_out != nullptr.
+// The length loop for one read.  The pass-1 pointer of query offset i is ptr[i * ptr_stride] (the
+// kernels keep pointers warp-transposed, so the stride is -32 there; +1 on a plain array).  Writes
+// len[i] and ptr_out[i] when those are not null, and returns the number of MEM records; records are
+// written to mem_out (packed (i << 32) | len) when mem_out != nullptr.
 template <typename LenT>
-MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, LenT* len,
-                              uint64_t* mem_out, Counters* cnt) {
+MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, int64_t ptr_stride,
+                              uint64_t* ptr_out, LenT* len, uint64_t* mem_out, Counters* cnt) {
     const uint64_t N = v.hdr.text_len;
     uint64_t l = 0, prev_ptr = 0, prev_len = 0;
     uint32_t n_mems = 0;
     for (uint64_t i = 0; i < m; ++i) {
-        const uint64_t pos = ptr[i];
+        const uint64_t pos = ptr[(int64_t)i * ptr_stride];
         if (i == 0 || pos != prev_ptr + 1) {
             if (cnt) cnt->restarts++;
             bool go = true;
@@ -237,13 +238,14 @@ MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m
                 uint64_t k = 0;
                 while (k < rem && i + l < m) {
                     if (cnt) cnt->chars++;
-                    if (ld(t + k) != seq[i + l]) { go = false; break; }
+                    if (ld(t + k) != ld(seq + i + l)) { go = false; break; }
                     ++k;
                     ++l;
                 }
                 if (k < rem) go = false;                        // read exhausted or mismatch inside the block
             }
         }
+        if (ptr_out) ptr_out[i] = pos;
         if (len) len[i] = (LenT)l;
         if (i == 0 || l >= prev_len) {                           // src/mems.cpp:257-258
             if (mem_out) mem_out[n_mems] = (i << 32) | l;

@@ -24,7 +24,7 @@ int main(int argc, char** argv) {
         read_plain_slp(std::string(argv[1]) + ".plain.slp", slp);
         ExportOptions opt;
         opt.verbose = true;
-        if (argc > 4) opt.leaf_len = (uint32_t)atoi(argv[4]);
+        if (argc > 4) opt.leaf_len = (uint64_t)atoll(argv[4]);
         if (argc > 5) opt.max_scan = (uint32_t)atoi(argv[5]);
         HostImage img;
         build_move_table(bwt, opt, img);
@@ -57,7 +57,7 @@ int main(int argc, char** argv) {
             }
             cnt.bases += m;
             std::vector<uint64_t> rec(m + 1);
-            const uint32_t k = lengths_read(v, seqs.data() + o, m, ptr.data() + o, len.data() + o, rec.data(), &cnt);
+            const uint32_t k = lengths_read(v, seqs.data() + o, m, ptr.data() + o, 1, (uint64_t*)nullptr, len.data() + o, rec.data(), &cnt);
             mo[r] = mems.size();
             mems.insert(mems.end(), rec.begin(), rec.begin() + k);
         }

@@ -1,20 +1,22 @@
 // gather_bench: measured random-access HBM roofline of this box (SURVEY.md 8(d) denominator).
 //
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/_build/gather_bench tools/gather_bench.cu
-//   tools/_build/gather_bench [table_GiB=16] > profiles/random_access_peak.json
+//   tools/_build/gather_bench [max_table_GiB=16] [l2_fetch_granularity] > profiles/random_access_peak.json
 //
-// Two access models over a table much larger than L2, for 32 / 64 / 128-byte aligned granules:
-//   "indep"  every thread issues UNROLL independent random granule reads per iteration (bandwidth cap of
-//            random sectors: what the memory system can deliver when latency is fully hidden);
-//   "chain"  every thread follows ONE dependent chain (next address = hash(loaded data)), the shape of an
-//            LF walk: throughput = resident threads / latency, capped by the above.
-// Reported GB/s count only the granule bytes requested (granule x accesses / time).
+// Every thread follows dependent chains (next address = hash(loaded data)): the shape of an LF walk.
+// Granule G in {32, 64, 128} bytes, aligned.  Load shapes:
+//   "2x128"  one thread loads its 32-byte granule with two 16-byte loads (LDG.128 x2)
+//   "1x256"  one thread loads its 32-byte granule with one 32-byte load (sm_100 LDG.256)
+//   "coop"   G/32 adjacent lanes share one chain and each load 32 bytes of the granule (one LDG.256
+//            warp instruction fetches 32*32/G granules), so L1 sees whole-granule requests
+// `chains` = independent chains per thread (software pipelining, MLP per thread).
+// Reported GB/s count only granule bytes requested (G x accesses / time); table sizes bracket the index
+// image (about 1-3 GB) and a table far beyond L2 / TLB reach.
 #include <cuda_runtime.h>
 
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
-#include <vector>
 
 #define CK(x)                                                                                   \
     do {                                                                                        \
@@ -25,10 +27,14 @@
         }                                                                                       \
     } while (0)
 
+struct alignas(32) Sector { uint32_t w[8]; };
+
 __device__ __forceinline__ uint64_t mix(uint64_t x) {
     x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
     return x;
 }
+// uniform in [0, n) without a 64-bit division
+__device__ __forceinline__ uint64_t reduce(uint64_t h, uint64_t n) { return __umul64hi(h, n); }
 
 __global__ void k_fill(uint4* t, uint64_t n16) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x) {
@@ -37,42 +43,43 @@ __global__ void k_fill(uint4* t, uint64_t n16) {
     }
 }
 
-template <int G16>   // granule in 16-byte units: 2, 4, 8
-__device__ __forceinline__ uint32_t load_granule(const uint4* t, uint64_t g) {
-    const uint4* p = t + g * G16;
-    uint32_t acc = 0;
-#pragma unroll
-    for (int k = 0; k < G16; ++k) {
-        const uint4 v = __ldg(p + k);
-        acc ^= v.x ^ v.y ^ v.z ^ v.w;
-    }
-    return acc;
+__device__ __forceinline__ uint32_t ld256(const Sector* p) {
+    uint32_t a, b, c, d, e, f, g, h;
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a), "=r"(b), "=r"(c), "=r"(d), "=r"(e), "=r"(f), "=r"(g), "=r"(h) : "l"(p));
+    return a ^ b ^ c ^ d ^ e ^ f ^ g ^ h;
+}
+__device__ __forceinline__ uint32_t ld2x128(const Sector* p) {
+    const uint4 x = __ldg(reinterpret_cast<const uint4*>(p)), y = __ldg(reinterpret_cast<const uint4*>(p) + 1);
+    return x.x ^ x.y ^ x.z ^ x.w ^ y.x ^ y.y ^ y.z ^ y.w;
 }
 
-template <int G16, int UNROLL>
-__global__ void __launch_bounds__(256) k_indep(const uint4* __restrict__ t, uint64_t n_gran, int iters, uint32_t* out) {
+// MODE 0: 2x128 per thread, MODE 1: 1x256 per thread, MODE 2: coop (LANES lanes per granule, 1x256 each)
+template <int MODE, int LANES, int CHAINS>
+__global__ void __launch_bounds__(256) k_chain(const Sector* __restrict__ t, uint64_t n_gran, int iters, uint32_t* out) {
     const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-    uint64_t s = mix(tid + 1);
+    const uint32_t sub = threadIdx.x % LANES;
+    uint64_t g[CHAINS];
+#pragma unroll
+    for (int c = 0; c < CHAINS; ++c) g[c] = reduce(mix((tid / LANES) * CHAINS + c + 1), n_gran);
     uint32_t acc = 0;
     for (int it = 0; it < iters; ++it) {
-        uint64_t g[UNROLL];
+        uint32_t v[CHAINS];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) { s = s * 6364136223846793005ULL + 1442695040888963407ULL; g[u] = (s >> 20) % n_gran; }
+        for (int c = 0; c < CHAINS; ++c) {
+            const Sector* p = t + g[c] * LANES + sub;
+            v[c] = MODE == 0 ? ld2x128(p) : ld256(p);
+        }
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) acc ^= load_granule<G16>(t, g[u]);
-    }
-    if (acc == 0x12345678u) out[0] = acc;
-}
-
-template <int G16>
-__global__ void __launch_bounds__(256) k_chain(const uint4* __restrict__ t, uint64_t n_gran, int iters, uint32_t* out) {
-    const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-    uint64_t g = mix(tid + 1) % n_gran;
-    uint32_t acc = 0;
-    for (int it = 0; it < iters; ++it) {
-        const uint32_t v = load_granule<G16>(t, g);
-        acc ^= v;
-        g = mix(((uint64_t)v << 20) ^ g ^ (uint64_t)it) % n_gran;      // depends on the loaded data
+        for (int c = 0; c < CHAINS; ++c) {
+            uint32_t x = v[c];
+            if (LANES > 1) {   // the whole granule decides the next address
+#pragma unroll
+                for (int o = 1; o < LANES; o <<= 1) x ^= __shfl_xor_sync(0xFFFFFFFFu, x, o);
+            }
+            acc ^= x;
+            g[c] = reduce(mix(((uint64_t)x << 20) ^ g[c] ^ (uint64_t)it), n_gran);
+        }
     }
     if (acc == 0x12345678u) out[0] = acc;
 }
@@ -95,43 +102,52 @@ static double time_ms(F&& launch, int reps) {
         if (ms < best) best = ms;
     }
     CK(cudaGetLastError());
+    CK(cudaEventDestroy(a));
+    CK(cudaEventDestroy(b));
     return best;
 }
 
 int main(int argc, char** argv) {
-    const double gib = argc > 1 ? atof(argv[1]) : 16.0;
-    const uint64_t bytes = (uint64_t)(gib * 1073741824.0) & ~127ULL;
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, 0));
-    uint4* t;
-    uint32_t* out;
-    CK(cudaMalloc(&t, bytes));
-    CK(cudaMalloc(&out, 4));
-    k_fill<<<prop.multiProcessorCount * 8, 256>>>(t, bytes / 16);
-    CK(cudaDeviceSynchronize());
     const int sms = prop.multiProcessorCount;
-    printf("{\"gpu\": \"%s\", \"sms\": %d, \"table_gib\": %.1f, \"results\": [", prop.name, sms, gib);
+    const double max_gib = argc > 1 ? atof(argv[1]) : 16.0;
+    size_t fetch = 0;
+    if (argc > 2) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(argv[2])));   // 32, 64 or 128: a hint
+    CK(cudaDeviceGetLimit(&fetch, cudaLimitMaxL2FetchGranularity));
+    uint32_t* out;
+    CK(cudaMalloc(&out, 4));
+    printf("{\"gpu\": \"%s\", \"sms\": %d, \"l2_fetch_granularity\": %d, \"results\": [", prop.name, sms, (int)fetch);
     bool first = true;
-    auto emit = [&](const char* model, int gran, int threads_per_sm, int unroll, double ms, double accesses) {
-        printf("%s\n  {\"model\": \"%s\", \"granule\": %d, \"threads_per_sm\": %d, \"unroll\": %d, \"ms\": %.3f, \"gacc_per_s\": %.3f, \"gb_per_s\": %.1f}",
-               first ? "" : ",", model, gran, threads_per_sm, unroll, ms, accesses / ms / 1e6, accesses * gran / ms / 1e6);
-        first = false;
-    };
-    for (int occ : {1024, 2048}) {
-        const int blocks = sms * occ / 256;
-        const double threads = (double)blocks * 256;
-        {
-            const int it = 64;
-            emit("indep", 32, occ, 4, time_ms([&] { k_indep<2, 4><<<blocks, 256>>>(t, bytes / 32, it, out); }, 3), threads * it * 4);
-            emit("indep", 64, occ, 4, time_ms([&] { k_indep<4, 4><<<blocks, 256>>>(t, bytes / 64, it, out); }, 3), threads * it * 4);
-            emit("indep", 128, occ, 4, time_ms([&] { k_indep<8, 4><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), threads * it * 4);
+    const double sizes[3] = {1.0, 3.0, max_gib};
+    for (double gib : sizes) {
+        const uint64_t bytes = (uint64_t)(gib * 1073741824.0) & ~127ULL;
+        Sector* t;
+        CK(cudaMalloc(&t, bytes));
+        k_fill<<<sms * 8, 256>>>((uint4*)t, bytes / 16);
+        CK(cudaDeviceSynchronize());
+        auto emit = [&](const char* shape, int gran, int occ, int chains, double ms, double accesses) {
+            printf("%s\n  {\"table_gib\": %.1f, \"shape\": \"%s\", \"granule\": %d, \"threads_per_sm\": %d, \"chains_per_thread\": %d, "
+                   "\"ms\": %.3f, \"gacc_per_s\": %.2f, \"gb_per_s\": %.1f}",
+                   first ? "" : ",", gib, shape, gran, occ, chains, ms, accesses / ms / 1e6, accesses * gran / ms / 1e6);
+            first = false;
+            fflush(stdout);
+        };
+        const int it = 256;
+        for (int occ : {1024, 2048}) {
+            const int blocks = sms * occ / 256;
+            const double th = (double)blocks * 256;
+            emit("2x128", 32, occ, 1, time_ms([&] { k_chain<0, 1, 1><<<blocks, 256>>>(t, bytes / 32, it, out); }, 3), th * it);
+            emit("1x256", 32, occ, 1, time_ms([&] { k_chain<1, 1, 1><<<blocks, 256>>>(t, bytes / 32, it, out); }, 3), th * it);
+            emit("1x256", 32, occ, 2, time_ms([&] { k_chain<1, 1, 2><<<blocks, 256>>>(t, bytes / 32, it, out); }, 3), th * it * 2);
+            emit("1x256", 32, occ, 4, time_ms([&] { k_chain<1, 1, 4><<<blocks, 256>>>(t, bytes / 32, it, out); }, 3), th * it * 4);
+            emit("coop", 64, occ, 1, time_ms([&] { k_chain<2, 2, 1><<<blocks, 256>>>(t, bytes / 64, it, out); }, 3), th * it / 2);
+            emit("coop", 64, occ, 4, time_ms([&] { k_chain<2, 2, 4><<<blocks, 256>>>(t, bytes / 64, it, out); }, 3), th * it * 4 / 2);
+            emit("coop", 128, occ, 1, time_ms([&] { k_chain<2, 4, 1><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), th * it / 4);
+            emit("coop", 128, occ, 4, time_ms([&] { k_chain<2, 4, 4><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), th * it * 4 / 4);
+            emit("coop", 128, occ, 8, time_ms([&] { k_chain<2, 4, 8><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), th * it * 8 / 4);
         }
-        {
-            const int it = 256;
-            emit("chain", 32, occ, 1, time_ms([&] { k_chain<2><<<blocks, 256>>>(t, bytes / 32, it, out); }, 3), threads * it);
-            emit("chain", 64, occ, 1, time_ms([&] { k_chain<4><<<blocks, 256>>>(t, bytes / 64, it, out); }, 3), threads * it);
-            emit("chain", 128, occ, 1, time_ms([&] { k_chain<8><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), threads * it);
-        }
+        CK(cudaFree(t));
     }
     printf("\n]}\n");
     return 0;
