@@ -211,24 +211,32 @@ def ours_arm(args) -> None:
     n_mems = int(mo[-1])
     rb.close()
 
-    # ---- end-to-end leg through the C ABI with host buffers
-    out = (h_mo, h_mp, h_ml)
-    for _ in range(args.warmup):
-        ix.maxrimal_exact_matches(h_seqs, h_offs, out=out)
-    barrier()
-    e2e_ms, stage = 0.0, np.zeros(6)
-    t_wall = time.perf_counter()
-    for _ in range(args.steps):
-        ix.maxrimal_exact_matches(h_seqs, h_offs, out=out)
-        tt = ix.timing()
-        e2e_ms += tt["total_ms"]
-        stage += np.array([tt[k] for k in ("h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms")])
-    barrier()
-    wall_ms = (time.perf_counter() - t_wall) * 1e3
+    # ---- end-to-end leg through the C ABI with host buffers: moni_gpu_mems32 (32-bit record fields) is the headline,
+    # moni_gpu_mems (64-bit fields, twice the device->host bytes) is reported beside it
+    h_mp32 = m.pinned_empty(total, np.uint32)
+    h_ml32 = m.pinned_empty(total, np.uint32)
+
+    def e2e_leg(out):
+        for _ in range(args.warmup):
+            ix.maxrimal_exact_matches(h_seqs, h_offs, out=out)
+        barrier()
+        dev_sum, stage = 0.0, np.zeros(6)
+        t_wall = time.perf_counter()
+        for _ in range(args.steps):
+            ix.maxrimal_exact_matches(h_seqs, h_offs, out=out)
+            tt = ix.timing()
+            dev_sum += tt["total_ms"]
+            stage += np.array([tt[k] for k in ("h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms")])
+        barrier()
+        wall = (time.perf_counter() - t_wall) * 1e3
+        return max_over_ranks(dev_sum, dev), max_over_ranks(wall, dev), stage
+
+    e2e64_dev_ms, e2e64_wall_ms, stage64 = e2e_leg((h_mo, h_mp, h_ml))
+    same64 = bool(np.array_equal(h_mo, mo) and np.array_equal(h_mp[:n_mems], mp) and np.array_equal(h_ml[:n_mems], ml))
+    h_mo[:] = 0
+    e2e_dev_ms, e2e_wall_ms, stage = e2e_leg((h_mo, h_mp32, h_ml32))
     clocks = sampler.summary() if sampler else None
-    same = bool(np.array_equal(h_mo, mo) and np.array_equal(h_mp[:n_mems], mp) and np.array_equal(h_ml[:n_mems], ml))
-    e2e_dev_ms = max_over_ranks(e2e_ms, dev)
-    e2e_wall_ms = max_over_ranks(wall_ms, dev)
+    same = bool(same64 and np.array_equal(h_mo, mo) and np.array_equal(h_mp32[:n_mems], mp) and np.array_equal(h_ml32[:n_mems], ml))
     all_reads = sum_over_ranks(float(n_reads), dev)
     if rank != 0:
         if world > 1:
@@ -277,10 +285,14 @@ def ours_arm(args) -> None:
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg[dom], "algorithmic_bytes_per_base": alg[dom] / max(cnt["bases"], 1)},
         "counters_per_step": cnt,
-        "e2e": {"value": e2e_value, "unit": "reads/s", "h2d_bytes_per_step": int(total + 8 * (n_reads + 1)),
-                "d2h_bytes_per_step": int(8 * (n_reads + 1) + 16 * n_mems), "ms_per_step_wall": e2e_wall_ms / args.steps,
+        "e2e": {"value": e2e_value, "unit": "reads/s", "api": "moni_gpu_mems32", "h2d_bytes_per_step": int(total + 8 * (n_reads + 1)),
+                "d2h_bytes_per_step": int(8 * (n_reads + 1) + 8 * n_mems), "ms_per_step_wall": e2e_wall_ms / args.steps,
                 "ms_per_step_device": e2e_dev_ms / args.steps, "same_bits_as_resident_run": same,
-                "stage_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage / args.steps).tolist()))},
+                "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage / args.steps).tolist()))},
+        "e2e_u64": {"value": all_reads * args.steps / (e2e64_wall_ms / 1e3), "unit": "reads/s", "api": "moni_gpu_mems",
+                    "d2h_bytes_per_step": int(8 * (n_reads + 1) + 16 * n_mems), "ms_per_step_wall": e2e64_wall_ms / args.steps,
+                    "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage64 / args.steps).tolist()))},
+        "mem_records_per_step": n_mems,
         "gpu_launches": int(launches), "options": args.opt, "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
     }
     print(json.dumps(line), flush=True)

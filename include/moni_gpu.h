@@ -61,6 +61,11 @@ int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, 
 int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
                   uint64_t* mem_offsets, uint64_t* mem_pos, uint64_t* mem_len, uint64_t mem_capacity);
 
+/* Same records with 32-bit fields: a query offset and a match length are both smaller than the read length
+ * (< 2^32, enforced), so this halves the device->host traffic of the call, which is what bounds it. */
+int moni_gpu_mems32(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
+                    uint64_t* mem_offsets, uint32_t* mem_pos, uint32_t* mem_len, uint64_t mem_capacity);
+
 /* Event counters accumulated over all calls since the last reset, when counting is enabled
  * (moni_gpu_set_option("count", "1"); off by default, it costs a few percent):
  * c[0]=bases, c[1]=threshold jumps (ms_pointers.hpp:482-505 taken), c[2]=LCE restarts,
@@ -75,9 +80,9 @@ int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset);
  * t[4]=device->host copies, t[5]=whole call (first copy to last copy). */
 int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
 
-/* Options ("leaf_len", "max_scan", "chunk_bases" apply to indexes loaded afterwards; "count" and "verbose" apply at once): "leaf_len" (grammar literal block length, default 128),
+/* Options ("leaf_len", "max_scan", "chunk_bases" apply to indexes loaded afterwards; "count" and "verbose" apply at once): "leaf_len" (grammar literal block length; default 0 = auto: the whole text as one literal block if it fits "text_budget" bytes, default 64 GiB, else 128),
  * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
- * "chunk_bases" (bases per device chunk, default 2^26). */
+ * "chunk_bases" (bases per device chunk, default 2^24), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
 int moni_gpu_set_option(const char* key, const char* value);
 
 /* Pinned host memory for batch buffers (cudaHostAlloc / cudaFreeHost). */

@@ -36,7 +36,7 @@ class MoniGpuError(RuntimeError):
 
 
 EXPORTS = [
-    "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems",
+    "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems", "moni_gpu_mems32",
     "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
@@ -60,6 +60,7 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_index_info.argtypes = [vp, _u64p, _u64p, _u64p, _u64p]
     L.moni_gpu_ms.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, _u64p]
     L.moni_gpu_mems.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, _u64p, _u64p, ctypes.c_uint64]
+    L.moni_gpu_mems32.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, ctypes.c_uint64]
     L.moni_gpu_counters.argtypes = [vp, _u64p, ci]
     L.moni_gpu_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.moni_gpu_set_option.argtypes = [cc, cc]
@@ -182,20 +183,25 @@ class MoniIndex:
         _check(self._L.moni_gpu_ms(self._h, _ptr(seqs), _u64(offsets), nr, _u64(ptr), _u64(ln)))
         return ptr[:total], ln[:total]
 
-    def maxrimal_exact_matches(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
+    def maxrimal_exact_matches(self, seqs: np.ndarray, offsets: np.ndarray, out=None, dtype=np.uint64):
         """(mem_offsets uint64[n+1], mem_pos, mem_len) -- mems_c::maxrimal_exact_matches for every read;
-        read r owns records mem_offsets[r]:mem_offsets[r+1], each (query offset, length)."""
+        read r owns records mem_offsets[r]:mem_offsets[r+1], each (query offset, length).  dtype=np.uint32 (or uint32
+        `out` arrays) selects moni_gpu_mems32: same records, half the device->host bytes."""
         seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
         offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
         total = int(offsets[-1])
         nr = offsets.shape[0] - 1
         if out is None:
             mo = np.empty(nr + 1, dtype=np.uint64)
-            mp = np.empty(max(total, 1), dtype=np.uint64)
-            ml = np.empty(max(total, 1), dtype=np.uint64)
+            mp = np.empty(max(total, 1), dtype=dtype)
+            ml = np.empty(max(total, 1), dtype=dtype)
         else:
             mo, mp, ml = out
-        _check(self._L.moni_gpu_mems(self._h, _ptr(seqs), _u64(offsets), nr, _u64(mo), _u64(mp), _u64(ml), mp.shape[0]))
+        if mp.dtype == np.uint32:
+            assert ml.dtype == np.uint32
+            _check(self._L.moni_gpu_mems32(self._h, _ptr(seqs), _u64(offsets), nr, _u64(mo), _ptr(mp), _ptr(ml), mp.shape[0]))
+        else:
+            _check(self._L.moni_gpu_mems(self._h, _ptr(seqs), _u64(offsets), nr, _u64(mo), _u64(mp), _u64(ml), mp.shape[0]))
         k = int(mo[nr])
         return mo, mp[:k], ml[:k]
 

@@ -166,16 +166,17 @@ __global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_
 }
 
 // MEM compaction: one warp per read copies its packed records to their final place.
+template <typename OutT>
 __global__ void __launch_bounds__(kBlock) k_mem_gather(const uint64_t* __restrict__ rec, const uint64_t* __restrict__ offs,
                                                        uint64_t base, uint32_t n_reads, const uint64_t* __restrict__ moff,
-                                                       uint64_t* __restrict__ mem_pos, uint64_t* __restrict__ mem_len) {
+                                                       OutT* __restrict__ mem_pos, OutT* __restrict__ mem_len) {
     const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (r >= n_reads) return;
     const uint64_t o = offs[r] - base, a = moff[r], cnt = moff[r + 1] - a;
     for (uint64_t k = lane; k < cnt; k += 32) {
         const uint64_t x = rec[o + k];
-        mem_pos[a + k] = x >> 32;
-        mem_len[a + k] = x & 0xFFFFFFFFull;
+        mem_pos[a + k] = (OutT)(x >> 32);
+        mem_len[a + k] = (OutT)(x & 0xFFFFFFFFull);
     }
 }
 
@@ -195,10 +196,11 @@ std::atomic<uint64_t> g_launches{0};
 std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
-    uint64_t leaf_len = 128;
+    uint64_t leaf_len = 0;                    // 0 = auto: the whole text as one literal block when it fits text_budget, else 128
+    uint64_t text_budget = 64ull << 30;       // bytes of HBM the plain text may take per GPU
     uint32_t max_scan = 8;
     bool verbose = false, count = false;
-    uint64_t chunk_bases = 1ull << 26;
+    uint64_t chunk_bases = 1ull << 24;
     uint32_t l2_fetch = 0;          // 0 = leave the device default
 };
 Options g_opt;
@@ -274,7 +276,7 @@ struct Scratch {   // device buffers of one chunk
     }
 };
 
-constexpr int kLanes = 2;        // chunks in flight per GPU: copies of one overlap the kernels of the other
+constexpr int kLanes = 3;        // chunks in flight per GPU: copies of one overlap the kernels of the other
 constexpr int kEv = 6;           // events per chunk: start, h2d done, pass 1 done, pass 2 done, compaction done, d2h done
 
 struct Lane {
@@ -409,7 +411,7 @@ void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, bool mems, cudaStr
 }
 
 // counts -> exclusive offsets (n + 1 entries) -> gather.  mem_pos/mem_len hold `bases` entries.
-void launch_compact(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
+void launch_compact(Scratch& S, const ChunkPlan& p, bool narrow, cudaStream_t st) {
     if (!p.n) return;
     const uint32_t n = (uint32_t)p.n;
     uint64_t* wide = S.moff.as<uint64_t>() + (n + 1);          // second half of moff: widened counts
@@ -421,9 +423,13 @@ void launch_compact(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     CK(cub::DeviceScan::ExclusiveSum(S.cub.p, tmp, wide, S.moff.as<uint64_t>(), (int)(n + 1), st));
     g_launches += 2;
     const uint64_t threads = (uint64_t)n * 32;
-    k_mem_gather<<<(unsigned)((threads + kBlock - 1) / kBlock), kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n,
-                                                                                 S.moff.as<uint64_t>(), S.mem_pos.as<uint64_t>(),
-                                                                                 S.mem_len.as<uint64_t>());
+    const unsigned blocks = (unsigned)((threads + kBlock - 1) / kBlock);
+    if (narrow)
+        k_mem_gather<uint32_t><<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                          S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>());
+    else
+        k_mem_gather<uint64_t><<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                          S.mem_pos.as<uint64_t>(), S.mem_len.as<uint64_t>());
     g_launches++;
     CK(cudaGetLastError());
 }
@@ -434,16 +440,25 @@ float ev_ms(cudaEvent_t a, cudaEvent_t b) {
     return ms;
 }
 
-// Next chunk of reads [a, r1): as many reads as fit chunk_bases (at least one).
+struct BadBatch : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+// Next chunk of reads [a, r1): as many reads as fit chunk_bases (at least one).  Validates the offsets it
+// walks over (the only pass the host makes over them).
 ChunkPlan plan_chunk(const uint64_t* offsets, uint64_t a, uint64_t r1, uint64_t chunk_bases) {
     ChunkPlan p;
     p.first = a;
     p.base = offsets[a];
     uint64_t b = a, lo = ~0ull, hi = 0;
-    while (b < r1 && (b == a || offsets[b + 1] - offsets[a] <= chunk_bases) && b - a < 0x7FFFFFE0ull) {
-        const uint64_t m = offsets[b + 1] - offsets[b];
-        lo = std::min(lo, m);
-        hi = std::max(hi, m);
+    const uint64_t limit = chunk_bases > ~0ull - p.base ? ~0ull : p.base + chunk_bases;
+    while (b < r1 && b - a < 0x7FFFFFE0ull) {
+        const uint64_t s = offsets[b], e = offsets[b + 1];
+        if (e < s) throw BadBatch("offsets must be non-decreasing");
+        if (e - s >= 0x7FFFFFFFull) throw BadBatch("reads of 2^31 bases or more are not supported");
+        if (e > limit && b != a) break;
+        lo = std::min(lo, e - s);
+        hi = std::max(hi, e - s);
         ++b;
     }
     p.n = b - a;
@@ -463,8 +478,8 @@ __global__ void k_shift(uint64_t* __restrict__ a, uint64_t n, uint64_t by) {
 // mems: records go to rec_pos/rec_len (contiguous from index 0, capacity rec_cap) and per-read record
 // offsets (relative to this shard) to rec_off[0 .. r1-r0]; *needed receives the shard's record count.
 void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, const uint64_t* offsets, uint64_t r0, uint64_t r1,
-               uint64_t* pointers, uint64_t* lengths, uint64_t* rec_off, uint64_t* rec_pos, uint64_t* rec_len, uint64_t rec_cap,
-               uint64_t* needed) {
+               uint64_t* pointers, uint64_t* lengths, uint64_t* rec_off, void* rec_pos, void* rec_len, uint64_t rec_cap,
+               uint64_t* needed, int rec_bytes = 8) {
     std::lock_guard<std::mutex> lock(R.mu);
     CK(cudaSetDevice(R.dev));
     for (double& x : R.t) x = 0;
@@ -497,7 +512,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
         launch_pass2(R, S, p, mems, L.stream);
         CK(cudaEventRecord(e[3], L.stream));
         if (mems) {
-            launch_compact(S, p, L.stream);
+            launch_compact(S, p, rec_bytes == 4, L.stream);
             CK(cudaEventRecord(e[4], L.stream));
         } else {
             CK(cudaEventRecord(e[4], L.stream));
@@ -524,16 +539,17 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
         const bool last = c + 1 == nc;
         CK(cudaMemcpyAsync(rec_off + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
         if (rec_total + k <= rec_cap && k) {
-            CK(cudaMemcpyAsync(rec_pos + rec_total, S.mem_pos.p, k * 8, cudaMemcpyDeviceToHost, L.stream));
-            CK(cudaMemcpyAsync(rec_len + rec_total, S.mem_len.p, k * 8, cudaMemcpyDeviceToHost, L.stream));
+            CK(cudaMemcpyAsync((char*)rec_pos + rec_total * rec_bytes, S.mem_pos.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
+            CK(cudaMemcpyAsync((char*)rec_len + rec_total * rec_bytes, S.mem_len.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
         }
         CK(cudaEventRecord(e[5], L.stream));
         rec_total += k;
     };
 
-    if (nc) enqueue_front(0);
+    // keep kLanes - 1 chunks enqueued ahead of the one whose results are being sent home
+    size_t fronted = 0;
     for (size_t c = 0; c < nc; ++c) {
-        if (c + 1 < nc) enqueue_front(c + 1);
+        while (fronted < nc && fronted < c + kLanes) enqueue_front(fronted++);
         if (mems) finish_mems(c);
     }
     for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
@@ -558,14 +574,6 @@ void split_by_bases(const uint64_t* offsets, uint64_t n_reads, int parts, std::v
     }
 }
 
-int check_batch(const uint64_t* offsets, uint64_t n_reads) {
-    for (uint64_t r = 0; r < n_reads; ++r) {
-        if (offsets[r + 1] < offsets[r]) { g_err = "offsets must be non-decreasing"; return MONI_GPU_EINVAL; }
-        if (offsets[r + 1] - offsets[r] >= 0xFFFFFFFFull) { g_err = "reads of 2^32 bases or more are not supported"; return MONI_GPU_EINVAL; }
-    }
-    return 0;
-}
-
 template <typename F>
 int guarded(F&& f) {
     try {
@@ -573,6 +581,9 @@ int guarded(F&& f) {
     } catch (const CudaError& e) {
         g_err = e.what();
         return MONI_GPU_ECUDA;
+    } catch (const BadBatch& e) {
+        g_err = e.what();
+        return MONI_GPU_EINVAL;
     } catch (const std::bad_alloc&) {
         g_err = "out of host memory";
         return MONI_GPU_ENOMEM;
@@ -603,7 +614,8 @@ int moni_gpu_set_option(const char* key, const char* value) {
     std::lock_guard<std::mutex> lock(g_opt_mu);
     const std::string k(key);
     const long long v = atoll(value);
-    if (k == "leaf_len" && v >= 1 && v <= (1ll << 40)) g_opt.leaf_len = (uint64_t)v;
+    if (k == "leaf_len" && v >= 0 && v <= (1ll << 40)) g_opt.leaf_len = (uint64_t)v;
+    else if (k == "text_budget" && v >= 0) g_opt.text_budget = (uint64_t)v;
     else if (k == "max_scan" && v >= 2 && v <= 4096) g_opt.max_scan = (uint32_t)v;
     else if (k == "verbose") g_opt.verbose = v != 0;
     else if (k == "count") { g_opt.count = v != 0; g_count.store(v != 0); }
@@ -650,10 +662,12 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
         }
         {
             ExportOptions eo;
-            eo.leaf_len = idx->opt.leaf_len;
             eo.verbose = idx->opt.verbose;
             FlatSlp slp;
             read_plain_slp(std::string(prefix) + ".plain.slp", slp);
+            // B200 has the HBM to keep the text itself next to the move table (6 GB for a 6 Gbp pangenome): then an LCE
+            // restart is one random line instead of a root-to-leaf walk.  Larger texts keep the grammar with 128-byte leaves.
+            eo.leaf_len = idx->opt.leaf_len ? idx->opt.leaf_len : (slp.text_len <= idx->opt.text_budget ? std::max<uint64_t>(slp.text_len, 1) : 128);
             build_grammar_table(slp, eo, img);
         }
         idx->hdr = img.hdr;
@@ -707,7 +721,6 @@ int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, 
     if (!idx || !offsets || (!seqs && n_reads && offsets[n_reads] != offsets[0])) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
     if (n_reads == 0) return 0;
     if (!pointers || !lengths) { g_err = "null output"; return MONI_GPU_EINVAL; }
-    if (int e = check_batch(offsets, n_reads)) return e;
     return guarded([&]() -> int {
         const int G = (int)idx->reps.size();
         std::vector<uint64_t> cut;
@@ -733,24 +746,24 @@ int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, 
     });
 }
 
-int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
-                  uint64_t* mem_pos, uint64_t* mem_len, uint64_t mem_capacity) {
+static int mems_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
+                     void* mem_pos, void* mem_len, uint64_t mem_capacity, int rec_bytes) {
     if (!idx || !offsets || !mem_offsets) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
     if (n_reads == 0) { mem_offsets[0] = 0; return 0; }
     if (!seqs && offsets[n_reads] != offsets[0]) { g_err = "null seqs"; return MONI_GPU_EINVAL; }
     if ((!mem_pos || !mem_len) && mem_capacity) { g_err = "null output"; return MONI_GPU_EINVAL; }
-    if (int e = check_batch(offsets, n_reads)) return e;
     return guarded([&]() -> int {
         const int G = (int)idx->reps.size();
         std::vector<uint64_t> cut;
         split_by_bases(offsets, n_reads, G, cut);
         uint64_t needed = 0;
         if (G == 1) {
-            run_shard(idx, *idx->reps[0], true, seqs, offsets, 0, n_reads, nullptr, nullptr, mem_offsets, mem_pos, mem_len, mem_capacity, &needed);
+            run_shard(idx, *idx->reps[0], true, seqs, offsets, 0, n_reads, nullptr, nullptr, mem_offsets, mem_pos, mem_len, mem_capacity, &needed,
+                      rec_bytes);
             collect_times(idx);
         } else {
             // every shard fills private buffers; they are stitched together in input order afterwards
-            struct Part { std::vector<uint64_t> off, pos, len; uint64_t k = 0; int rc = 0; std::string err; };
+            struct Part { std::vector<uint64_t> off; std::vector<char> pos, len; uint64_t k = 0; int rc = 0; std::string err; };
             std::vector<Part> parts(G);
             std::vector<std::thread> th;
             for (int g = 0; g < G; ++g)
@@ -759,10 +772,10 @@ int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets
                     P.rc = guarded([&]() -> int {
                         const uint64_t nr = cut[g + 1] - cut[g], cap = offsets[cut[g + 1]] - offsets[cut[g]];
                         P.off.assign(nr + 1, 0);
-                        P.pos.resize(cap + 1);
-                        P.len.resize(cap + 1);
+                        P.pos.resize((cap + 1) * rec_bytes);
+                        P.len.resize((cap + 1) * rec_bytes);
                         if (nr) run_shard(idx, *idx->reps[g], true, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, P.off.data(), P.pos.data(),
-                                          P.len.data(), cap, &P.k);
+                                          P.len.data(), cap, &P.k, rec_bytes);
                         return 0;
                     });
                     if (P.rc) P.err = g_err;
@@ -775,8 +788,8 @@ int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets
                 const uint64_t nr = cut[g + 1] - cut[g];
                 for (uint64_t i = 0; i <= nr; ++i) mem_offsets[cut[g] + i] = needed + P.off[i];
                 if (needed + P.k <= mem_capacity && P.k) {
-                    memcpy(mem_pos + needed, P.pos.data(), P.k * 8);
-                    memcpy(mem_len + needed, P.len.data(), P.k * 8);
+                    memcpy((char*)mem_pos + needed * rec_bytes, P.pos.data(), P.k * rec_bytes);
+                    memcpy((char*)mem_len + needed * rec_bytes, P.len.data(), P.k * rec_bytes);
                 }
                 needed += P.k;
             }
@@ -787,6 +800,16 @@ int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets
         }
         return 0;
     });
+}
+
+int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
+                  uint64_t* mem_pos, uint64_t* mem_len, uint64_t mem_capacity) {
+    return mems_impl(idx, seqs, offsets, n_reads, mem_offsets, mem_pos, mem_len, mem_capacity, 8);
+}
+
+int moni_gpu_mems32(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
+                    uint32_t* mem_pos, uint32_t* mem_len, uint64_t mem_capacity) {
+    return mems_impl(idx, seqs, offsets, n_reads, mem_offsets, mem_pos, mem_len, mem_capacity, 4);
 }
 
 int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset) {
@@ -819,7 +842,6 @@ int moni_gpu_batch_create(moni_gpu_index* idx, int gpu_slot, const char* seqs, c
         g_err = "bad arguments";
         return MONI_GPU_EINVAL;
     }
-    if (int e = check_batch(offsets, n_reads)) return e;
     if (offsets[n_reads] - offsets[0] >= 0xFFFFFFFFull) { g_err = "a resident batch holds fewer than 2^32 bases"; return MONI_GPU_EINVAL; }
     *out = nullptr;
     return guarded([&]() -> int {
@@ -856,7 +878,7 @@ int moni_gpu_batch_run(moni_gpu_batch* b, int what, float kernel_ms[3]) {
         CK(cudaEventRecord(e[1], L.stream));
         launch_pass2(R, b->s, b->plan, what == 2, L.stream);
         CK(cudaEventRecord(e[2], L.stream));
-        if (what == 2) launch_compact(b->s, b->plan, L.stream);
+        if (what == 2) launch_compact(b->s, b->plan, false, L.stream);
         CK(cudaEventRecord(e[3], L.stream));
         CK(cudaStreamSynchronize(L.stream));
         b->last = what;

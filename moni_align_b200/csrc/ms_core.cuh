@@ -194,68 +194,138 @@ MONI_HD void scan_step(const ImageView& v, const uint8_t* tcode, uint8_t c, Scan
 }
 
 // ---- pass 2 -------------------------------------------------------------------------------------
-// Literal bytes of the text from position tp: returns a pointer to T[tp] inside the pool and sets
-// `rem` to how many consecutive text bytes are available there.  Replaces PlainSlp::charAt
-// (thirdparty/ShapedSlp/PlainSlp.hpp:101-126): one descent serves a whole literal block.
-MONI_HD const uint8_t* text_block(const ImageView& v, uint64_t tp, uint64_t& rem, Counters* cnt) {
-    uint32_t ref = v.hdr.root_ref;
-    uint64_t span = v.hdr.text_len, p = tp;
-    while (!(ref & kLeafBit)) {
+// Eight bytes from an arbitrary address (little endian).  May touch up to 15 bytes past p: every
+// buffer read this way (device read batches, the literal pool) carries that much slack.
+MONI_HD uint64_t load8(const uint8_t* p) {
 #if defined(__CUDA_ARCH__)
-        const uint4 q = __ldg(reinterpret_cast<const uint4*>(v.nodes + ref));
-        const uint32_t l = q.x, r = q.y;
-        const uint64_t ll = (uint64_t)q.z | ((uint64_t)q.w << 32);
+    const unsigned long long a = (unsigned long long)p;
+    const uint32_t sh = (uint32_t)(a & 7ull) * 8u;
+    const uint64_t* q = reinterpret_cast<const uint64_t*>(a & ~7ull);
+    const uint64_t lo = __ldg(q), hi = __ldg(q + 1);
+    return sh ? (lo >> sh) | (hi << (64u - sh)) : lo;
 #else
-        const uint32_t l = v.nodes[ref].left, r = v.nodes[ref].right;
-        const uint64_t ll = v.nodes[ref].left_len;
+    uint64_t x = 0;
+    for (int k = 7; k >= 0; --k) x = (x << 8) | p[k];
+    return x;
 #endif
-        if (p < ll) { ref = l; span = ll; } else { p -= ll; span -= ll; ref = r; }
-        if (cnt) cnt->restart_depth++;
-    }
-    rem = span - p;
-    if (cnt) cnt->descents++;
-    return v.pool + ((uint64_t)(ref & ~kLeafBit) << v.hdr.pool_shift) + p;
 }
 
-// The length loop for one read.  The pass-1 pointer of query offset i is ptr[i * ptr_stride] (the
-// kernels keep pointers warp-transposed, so the stride is -32 there; +1 on a plain array).  Writes
-// len[i] and ptr_out[i] when those are not null, and returns the number of MEM records; records are
-// written to mem_out (packed (i << 32) | len) when mem_out != nullptr.
+MONI_HD uint32_t first_diff_byte(uint64_t x) {      // x != 0
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)(__ffsll((long long)x) - 1) >> 3;
+#else
+    return (uint32_t)__builtin_ctzll(x) >> 3;
+#endif
+}
+
+// Pass 2 as a per-read state machine.  The reference's loop (src/matching_statistics.cpp:246-255) is
+//     for i: pos = ptr[i]; while (i+l < m && pos+l < N && restart(i) && read[i+l] == charAt(pos+l)) ++l; len[i] = l; l -= (l != 0)
+// with charAt = PlainSlp::charAt (thirdparty/ShapedSlp/PlainSlp.hpp:101-126), one root-to-leaf descent per
+// character.  Here one descent reaches a literal block that is compared eight bytes at a time, and the
+// work is cut into micro-steps -- ADVANCE to the next query offset, DESCEND to a literal block, COMPARE
+// one word -- so that the 32 reads of a warp each take whatever micro-step they need in the same
+// loop iteration instead of waiting for each other's inner loops.
+struct LenState {
+    enum : uint32_t { ADVANCE = 0, DESCEND = 1, COMPARE = 2 };
+    uint32_t i = 0, l = 0, prev_len = 0, n_mems = 0, mode = ADVANCE;
+    uint32_t ref = 0;               // DESCEND: current grammar reference
+    uint64_t pos = 0, prev_ptr = 0;
+    uint64_t span = 0, p = 0;       // DESCEND: expansion length of ref, offset inside it
+    const uint8_t* t = nullptr;     // COMPARE: next text byte
+    uint64_t rem = 0;               // COMPARE: text bytes left in the literal block
+};
+
+// One micro-step of read `seq[0..m)`.  The pointer of query offset i is ptr[i * ptr_stride] (the kernels
+// keep pointers warp-transposed: stride -32; +1 on a plain array).  When a query offset is finished,
+// writes ptr_out[i] / len[i] (if not null) and the MEM record (packed (i << 32) | len, if mem_out != null).
+// Call while st.i < m.  m < 2^31.
+template <typename LenT>
+MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, const uint64_t* ptr, int64_t ptr_stride,
+                          uint64_t* ptr_out, LenT* len, uint64_t* mem_out, LenState& st, Counters* cnt) {
+    const uint64_t N = v.hdr.text_len;
+    bool done = false;
+    if (st.mode == LenState::ADVANCE) {
+        st.pos = ptr[(int64_t)st.i * ptr_stride];
+        done = true;
+        if (st.i == 0 || st.pos != st.prev_ptr + 1) {            // otherwise the loop body never runs: l carries over
+            if (cnt) cnt->restarts++;
+            if (st.i + st.l < m && st.pos + st.l < N) {           // u64 add wraps exactly as in the reference
+                st.mode = LenState::DESCEND;
+                st.ref = v.hdr.root_ref;
+                st.span = N;
+                st.p = st.pos + st.l;
+                done = false;
+            }
+        }
+    }
+    if (st.mode == LenState::DESCEND) {
+        // tight loop on purpose: a level is ~10 instructions, far less than one trip through this function
+        while (!(st.ref & kLeafBit)) {
+#if defined(__CUDA_ARCH__)
+            const uint4 q = __ldg(reinterpret_cast<const uint4*>(v.nodes + st.ref));
+            const uint32_t lc = q.x, rc = q.y;
+            const uint64_t ll = (uint64_t)q.z | ((uint64_t)q.w << 32);
+#else
+            const uint32_t lc = v.nodes[st.ref].left, rc = v.nodes[st.ref].right;
+            const uint64_t ll = v.nodes[st.ref].left_len;
+#endif
+            if (st.p < ll) { st.ref = lc; st.span = ll; } else { st.p -= ll; st.span -= ll; st.ref = rc; }
+            if (cnt) cnt->restart_depth++;
+        }
+        st.t = v.pool + ((uint64_t)(st.ref & ~kLeafBit) << v.hdr.pool_shift) + st.p;
+        st.rem = st.span - st.p;                                 // > 0, and the block lies inside the text: pos + l < N holds in it
+        st.mode = LenState::COMPARE;
+        if (cnt) cnt->descents++;
+    }
+    if (st.mode == LenState::COMPARE) {
+        const uint32_t e = st.i + st.l;                          // < m
+        uint32_t lim = m - e;
+        if (lim > 8u) lim = 8u;
+        if ((uint64_t)lim > st.rem) lim = (uint32_t)st.rem;
+        const uint64_t x = load8(st.t) ^ load8(seq + e);
+        uint32_t k = x ? first_diff_byte(x) : 8u;
+        const bool mismatch = k < lim;
+        if (!mismatch) k = lim;
+        if (cnt) cnt->chars += k + (mismatch ? 1u : 0u);
+        st.l += k;
+        st.t += k;
+        st.rem -= k;
+        if (mismatch || e + k >= m) {
+            done = true;
+        } else if (st.rem == 0) {                                // block exhausted while still matching
+            if (st.pos + st.l < N) {
+                st.mode = LenState::DESCEND;
+                st.ref = v.hdr.root_ref;
+                st.span = N;
+                st.p = st.pos + st.l;
+            } else {
+                done = true;
+            }
+        }
+    }
+    if (done) {
+        const uint32_t i = st.i;
+        if (ptr_out) ptr_out[i] = st.pos;
+        if (len) len[i] = (LenT)st.l;
+        if (i == 0 || st.l >= st.prev_len) {                     // src/mems.cpp:257-258
+            if (mem_out) mem_out[st.n_mems] = ((uint64_t)i << 32) | st.l;
+            ++st.n_mems;
+        }
+        st.prev_len = st.l;
+        st.prev_ptr = st.pos;
+        st.l = st.l ? st.l - 1 : 0;
+        st.i = i + 1;
+        st.mode = LenState::ADVANCE;
+    }
+}
+
+// The whole length loop of one read (a single lane of the state machine).  Returns the number of MEM records.
 template <typename LenT>
 MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, int64_t ptr_stride,
                               uint64_t* ptr_out, LenT* len, uint64_t* mem_out, Counters* cnt) {
-    const uint64_t N = v.hdr.text_len;
-    uint64_t l = 0, prev_ptr = 0, prev_len = 0;
-    uint32_t n_mems = 0;
-    for (uint64_t i = 0; i < m; ++i) {
-        const uint64_t pos = ptr[(int64_t)i * ptr_stride];
-        if (i == 0 || pos != prev_ptr + 1) {
-            if (cnt) cnt->restarts++;
-            bool go = true;
-            while (go && i + l < m && pos + l < N) {             // u64 adds wrap exactly as in the reference
-                uint64_t rem;
-                const uint8_t* t = text_block(v, pos + l, rem, cnt);
-                uint64_t k = 0;
-                while (k < rem && i + l < m) {
-                    if (cnt) cnt->chars++;
-                    if (ld(t + k) != ld(seq + i + l)) { go = false; break; }
-                    ++k;
-                    ++l;
-                }
-                if (k < rem) go = false;                        // read exhausted or mismatch inside the block
-            }
-        }
-        if (ptr_out) ptr_out[i] = pos;
-        if (len) len[i] = (LenT)l;
-        if (i == 0 || l >= prev_len) {                           // src/mems.cpp:257-258
-            if (mem_out) mem_out[n_mems] = (i << 32) | l;
-            ++n_mems;
-        }
-        prev_len = l;
-        prev_ptr = pos;
-        l = l ? l - 1 : 0;
-    }
-    return n_mems;
+    LenState st;
+    while (st.i < (uint32_t)m) lengths_step(v, seq, (uint32_t)m, ptr, ptr_stride, ptr_out, len, mem_out, st, cnt);
+    return st.n_mems;
 }
 
 }  // namespace moni

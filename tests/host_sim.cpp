@@ -39,7 +39,7 @@ int main(int argc, char** argv) {
         if (fread(&nr, 8, 1, f) != 1) throw std::runtime_error("bad batch");
         std::vector<uint64_t> off(nr + 1);
         if (fread(off.data(), 8, nr + 1, f) != nr + 1) throw std::runtime_error("bad batch");
-        std::vector<uint8_t> seqs(off[nr] + 1);
+        std::vector<uint8_t> seqs(off[nr] + 16);   // load8 slack
         if (off[nr] && fread(seqs.data(), 1, off[nr], f) != off[nr]) throw std::runtime_error("bad batch");
         fclose(f);
 

@@ -105,6 +105,16 @@ def test_chunking_and_resident_batches_agree(m, oracle_mod):
     rb.close()
 
 
+def test_mems32_equals_mems(m, indexes):
+    """moni_gpu_mems32 returns the same records in 32-bit fields."""
+    names, seqs = read_fastq(os.path.join(GOLDEN, "pan4.fq"))
+    flat, offs = pack(seqs)
+    a = indexes["pan4"].maxrimal_exact_matches(flat, offs)
+    b = indexes["pan4"].maxrimal_exact_matches(flat, offs, dtype=np.uint32)
+    assert b[1].dtype == np.uint32 and b[2].dtype == np.uint32
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
 def test_mem_capacity_error(m, indexes):
     ix = indexes["pan4"]
     flat, offs = pack([b"ACGTACGTACGTTTTGACCA"] * 50)

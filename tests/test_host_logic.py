@@ -82,7 +82,7 @@ def test_library_exports_every_declared_symbol():
     import moni_align_b200 as m
     L = m.load_library()
     syms = _declared_symbols()
-    assert len(syms) >= 18
+    assert len(syms) >= 19
     for s in syms:
         assert hasattr(L, s), s
     assert sorted(m.EXPORTS) == syms

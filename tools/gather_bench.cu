@@ -55,8 +55,8 @@ __device__ __forceinline__ uint32_t ld2x128(const Sector* p) {
 }
 
 // MODE 0: 2x128 per thread, MODE 1: 1x256 per thread, MODE 2: coop (LANES lanes per granule, 1x256 each)
-template <int MODE, int LANES, int CHAINS>
-__global__ void __launch_bounds__(256) k_chain(const Sector* __restrict__ t, uint64_t n_gran, int iters, uint32_t* out) {
+template <int MODE, int LANES, int CHAINS, int BLOCK = 256>
+__global__ void __launch_bounds__(BLOCK) k_chain(const Sector* __restrict__ t, uint64_t n_gran, int iters, uint32_t* out) {
     const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     const uint32_t sub = threadIdx.x % LANES;
     uint64_t g[CHAINS];
@@ -117,9 +117,22 @@ int main(int argc, char** argv) {
     CK(cudaDeviceGetLimit(&fetch, cudaLimitMaxL2FetchGranularity));
     uint32_t* out;
     CK(cudaMalloc(&out, 4));
+    if (argc > 3) {   // probe mode for ncu: one 3 GiB table, one launch of each 32-byte shape and of the 128-byte cooperative shape
+        const uint64_t bytes = 3ull << 30;
+        Sector* t;
+        CK(cudaMalloc(&t, bytes));
+        k_fill<<<sms * 8, 256>>>((uint4*)t, bytes / 16);
+        const int blocks = sms * 8;
+        k_chain<1, 1, 1><<<blocks, 256>>>(t, bytes / 32, 64, out);
+        k_chain<0, 1, 1><<<blocks, 256>>>(t, bytes / 32, 64, out);
+        k_chain<2, 4, 1><<<blocks, 256>>>(t, bytes / 128, 64, out);
+        CK(cudaDeviceSynchronize());
+        printf("probe done, l2 fetch granularity %d\n", (int)fetch);
+        return 0;
+    }
     printf("{\"gpu\": \"%s\", \"sms\": %d, \"l2_fetch_granularity\": %d, \"results\": [", prop.name, sms, (int)fetch);
     bool first = true;
-    const double sizes[3] = {1.0, 3.0, max_gib};
+    const double sizes[4] = {0.03, 1.0, 3.0, max_gib};
     for (double gib : sizes) {
         const uint64_t bytes = (uint64_t)(gib * 1073741824.0) & ~127ULL;
         Sector* t;
@@ -146,6 +159,19 @@ int main(int argc, char** argv) {
             emit("coop", 128, occ, 1, time_ms([&] { k_chain<2, 4, 1><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), th * it / 4);
             emit("coop", 128, occ, 4, time_ms([&] { k_chain<2, 4, 4><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), th * it * 4 / 4);
             emit("coop", 128, occ, 8, time_ms([&] { k_chain<2, 4, 8><<<blocks, 256>>>(t, bytes / 128, it, out); }, 3), th * it * 8 / 4);
+        }
+        // Where is the ceiling?  One 1024-thread block per SM (forced by a 120 KB dynamic shared memory request) on
+        // all SMs, then on half of them: a per-SM limit halves the rate, a memory-side limit does not.
+        {
+            auto kern = k_chain<1, 1, 1, 1024>;
+            CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024));
+            for (int frac : {1, 2, 4}) {
+                const int blocks = sms / frac;
+                const double ms = time_ms([&] { kern<<<blocks, 1024, 120 * 1024>>>(t, bytes / 32, it, out); }, 3);
+                char shape[32];
+                snprintf(shape, sizeof shape, "1x256 on %d SMs", blocks);
+                emit(shape, 32, 1024, 1, ms, (double)blocks * 1024 * it);
+            }
         }
         CK(cudaFree(t));
     }
