@@ -245,9 +245,13 @@ def ours_arm(args) -> None:
 
     value = all_reads * args.steps / (dev_ms / 1e3)
     e2e_value = all_reads * args.steps / (e2e_wall_ms / 1e3)
-    # roofline of the dominant kernel: algorithmic bytes per SURVEY.md 8(d), 32 B x (5B + 6J) for pass 1 and
-    # 32 B x (D + 2C) for pass 2, with D = grammar nodes visited by this layout's descents
-    alg = {"pass1": 32.0 * (5 * cnt["bases"] + 6 * cnt["jumps"]), "pass2": 32.0 * (cnt["restart_depth"] + 2 * cnt["chars"])}
+    # roofline of the dominant kernel: B200 fetches one 128-byte DRAM line per random access, so
+    #   pass 1 = 137 B per base (row line 128 + pointer store 8 + read byte 1)
+    #   pass 2 = 128 B per LCE restart that touches text + 16 B per grammar node visited + 9 B per base + 8 B per MEM record
+    # SURVEY.md 8(d)'s layout-independent model is reported beside it.
+    alg = {"pass1": 137.0 * cnt["bases"],
+           "pass2": 128.0 * cnt["descents"] + 16.0 * cnt["restart_depth"] + 9.0 * cnt["bases"] + 8.0 * n_mems}
+    survey = {"pass1": 32.0 * (5 * cnt["bases"] + 6 * cnt["jumps"]), "pass2": 32.0 * (cnt["restart_depth"] + 2 * cnt["chars"])}
     per = {"pass1": k_ms[0] / args.steps, "pass2": k_ms[1] / args.steps}
     dom = "pass1" if per["pass1"] >= per["pass2"] else "pass2"
     peak, peak_src = measured_peak_gbs()
@@ -283,7 +287,10 @@ def ours_arm(args) -> None:
         "stage_ms_per_step": {"pass1": per["pass1"], "pass2": per["pass2"], "compact": k_ms[2] / args.steps},
         "roofline": {"bound": "hbm", "kernel": "k_ms_pointers" if dom == "pass1" else "k_ms_lengths", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": alg[dom], "algorithmic_bytes_per_base": alg[dom] / max(cnt["bases"], 1)},
+                     "algorithmic_bytes_per_launch": alg[dom], "algorithmic_bytes_per_base": alg[dom] / max(cnt["bases"], 1),
+                     "survey_model_bytes": survey[dom],
+                     "other_kernel": {"kernel": "k_ms_lengths" if dom == "pass1" else "k_ms_pointers",
+                                      "achieved": alg["pass2" if dom == "pass1" else "pass1"] / (per["pass2" if dom == "pass1" else "pass1"] / 1e3) / 1e9}},
         "counters_per_step": cnt,
         "e2e": {"value": e2e_value, "unit": "reads/s", "api": "moni_gpu_mems32", "h2d_bytes_per_step": int(total + 8 * (n_reads + 1)),
                 "d2h_bytes_per_step": int(8 * (n_reads + 1) + 8 * n_mems), "ms_per_step_wall": e2e_wall_ms / args.steps,

@@ -36,6 +36,29 @@ def test_ms_and_mems_equal_reference_files(case, m, indexes):
     assert m.format_mems(names, mo, mp, ml) == open(pre + ".mems", "rb").read()
 
 
+@pytest.fixture(scope="module")
+def grammar_indexes(m):
+    """The same indexes with the grammar kept (literal blocks of 16 bytes) instead of the whole text in HBM."""
+    m.set_option("leaf_len", 16)
+    try:
+        return {c: m.MoniIndex(os.path.join(GOLDEN, c + ".fa")) for c in CASES}
+    finally:
+        m.set_option("leaf_len", 0)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_grammar_mode_equals_reference_files(case, m, grammar_indexes):
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    ix = grammar_indexes[case]
+    ptr, ln = ix.matching_statistics(flat, offs)
+    assert m.format_ms(names, offs, ptr) == open(pre + ".pointers", "rb").read()
+    assert m.format_ms(names, offs, ln) == open(pre + ".lengths", "rb").read()
+    mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+    assert m.format_mems(names, mo, mp, ml) == open(pre + ".mems", "rb").read()
+
+
 @pytest.mark.parametrize("case", CASES)
 def test_random_reads_equal_oracle(case, m, indexes, oracle_mod):
     import synth
@@ -84,7 +107,7 @@ def test_chunking_and_resident_batches_agree(m, oracle_mod):
     try:
         small = m.MoniIndex(pre)
     finally:
-        m.set_option("chunk_bases", 1 << 26)
+        m.set_option("chunk_bases", 1 << 24)
     big = m.MoniIndex(pre)
     a = small.matching_statistics(flat, offs)
     b = big.matching_statistics(flat, offs)
