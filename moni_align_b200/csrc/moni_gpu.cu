@@ -202,6 +202,7 @@ struct Options {
     bool verbose = false, count = false;
     uint64_t chunk_bases = 1ull << 24;
     uint32_t l2_fetch = 0;          // 0 = leave the device default
+    uint32_t lanes = 4;
 };
 Options g_opt;
 std::mutex g_opt_mu;
@@ -276,7 +277,7 @@ struct Scratch {   // device buffers of one chunk
     }
 };
 
-constexpr int kLanes = 3;        // chunks in flight per GPU: copies of one overlap the kernels of the other
+constexpr int kMaxLanes = 8;     // chunks in flight per GPU (option "lanes"): copies of one overlap the kernels of the others
 constexpr int kEv = 6;           // events per chunk: start, h2d done, pass 1 done, pass 2 done, compaction done, d2h done
 
 struct Lane {
@@ -298,7 +299,7 @@ struct Lane {
 
 struct Replica {
     int dev = 0;
-    Lane lanes[kLanes];
+    std::vector<Lane> lanes;
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
     ImageView view;
     std::mutex mu;
@@ -488,7 +489,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
         plans.push_back(plan_chunk(offsets, a, r1, idx->opt.chunk_bases));
         a += plans.back().n;
     }
-    const size_t nc = plans.size();
+    const size_t nc = plans.size(), kLanes_ = R.lanes.size();
     for (Lane& L : R.lanes) L.used = 0;
     std::vector<size_t> ev_at(nc);
     uint64_t rec_total = 0;
@@ -496,7 +497,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
 
     auto enqueue_front = [&](size_t c) {
         const ChunkPlan& p = plans[c];
-        Lane& L = R.lanes[c % kLanes];
+        Lane& L = R.lanes[c % kLanes_];
         Scratch& S = L.scratch;
         S.reserve(p, !mems, mems);
         ev_at[c] = L.used;
@@ -526,7 +527,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
     // mems only: learn the chunk's record count, then send offsets (shifted to shard-relative) and records home
     auto finish_mems = [&](size_t c) {
         const ChunkPlan& p = plans[c];
-        Lane& L = R.lanes[c % kLanes];
+        Lane& L = R.lanes[c % kLanes_];
         Scratch& S = L.scratch;
         cudaEvent_t* e = L.events.data() + ev_at[c];
         uint64_t k = 0;
@@ -546,15 +547,15 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
         rec_total += k;
     };
 
-    // keep kLanes - 1 chunks enqueued ahead of the one whose results are being sent home
+    // keep lanes - 1 chunks enqueued ahead of the one whose results are being sent home
     size_t fronted = 0;
     for (size_t c = 0; c < nc; ++c) {
-        while (fronted < nc && fronted < c + kLanes) enqueue_front(fronted++);
+        while (fronted < nc && fronted < c + kLanes_) enqueue_front(fronted++);
         if (mems) finish_mems(c);
     }
     for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
     for (size_t c = 0; c < nc; ++c) {
-        cudaEvent_t* e = R.lanes[c % kLanes].events.data() + ev_at[c];
+        cudaEvent_t* e = R.lanes[c % kLanes_].events.data() + ev_at[c];
         for (int k = 0; k < 5; ++k) R.t[k] += ev_ms(e[k], e[k + 1]);
         cudaEvent_t* e0 = R.lanes[0].events.data() + ev_at[0];
         R.t[5] = std::max<double>(R.t[5], ev_ms(e0[0], e[5]));
@@ -620,6 +621,7 @@ int moni_gpu_set_option(const char* key, const char* value) {
     else if (k == "verbose") g_opt.verbose = v != 0;
     else if (k == "count") { g_opt.count = v != 0; g_count.store(v != 0); }
     else if (k == "chunk_bases" && v >= 1 && v <= (1ll << 31)) g_opt.chunk_bases = (uint64_t)v;
+    else if (k == "lanes" && v >= 1 && v <= kMaxLanes) g_opt.lanes = (uint32_t)v;
     else if (k == "l2_fetch" && (v == 0 || v == 32 || v == 64 || v == 128)) g_opt.l2_fetch = (uint32_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }
     return 0;
@@ -677,6 +679,7 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             R->dev = devs[g];
             CK(cudaSetDevice(R->dev));
             if (idx->opt.l2_fetch) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, idx->opt.l2_fetch));
+            R->lanes.resize(idx->opt.lanes);
             for (Lane& L : R->lanes) CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
             cudaStream_t st = R->stream();
             upload(R->rows, img.rows, st);
