@@ -34,6 +34,27 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 
+_REAL_STDOUT = None
+
+
+def capture_stdout() -> None:
+    """Send everything that writes to fd 1 (NCCL banners, child processes) to stderr, so that stdout carries exactly
+    the one JSON line emit() prints."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def log(*a):
     print("[bench]", *a, file=sys.stderr, flush=True)
 
@@ -99,7 +120,7 @@ def reference_arm(args) -> None:
     if rank != 0:
         return
     if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "mems")):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/bin/mems not built (needs /root/reference at build time)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/bin/mems not built (needs /root/reference at build time)"})
         return
     w = workloads.WORKLOADS[args.workload]
     prefix = workloads.ensure_index(args.workload)
@@ -127,7 +148,7 @@ def reference_arm(args) -> None:
             "cpu_baseline": {"value": value, "unit": "reads/s", "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ our arm
@@ -302,7 +323,7 @@ def ours_arm(args) -> None:
         "mem_records_per_step": n_mems,
         "gpu_launches": int(launches), "options": args.opt, "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -321,6 +342,7 @@ def main():
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (moni_gpu_set_option), repeatable")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    capture_stdout()
     if args.impl == "reference":
         reference_arm(args)
     else:

@@ -82,7 +82,7 @@ int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
 
 /* Options ("leaf_len", "max_scan", "chunk_bases" apply to indexes loaded afterwards; "count" and "verbose" apply at once): "leaf_len" (grammar literal block length; default 0 = auto: the whole text as one literal block if it fits "text_budget" bytes, default 64 GiB, else 128),
  * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
- * "chunk_bases" (bases per device chunk, default 2^24), "lanes" (chunks in flight per GPU, default 4), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
+ * "chunk_bases" (bases per device chunk, default 2^24) and "chunk_min_reads" (a chunk is not closed before it holds this many reads, default 98304; hard cap 2^29 bases), "lanes" (chunks in flight per GPU, default 4), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
 int moni_gpu_set_option(const char* key, const char* value);
 
 /* Pinned host memory for batch buffers (cudaHostAlloc / cudaFreeHost). */

@@ -12,6 +12,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -201,6 +202,7 @@ struct Options {
     uint32_t max_scan = 8;
     bool verbose = false, count = false;
     uint64_t chunk_bases = 1ull << 24;
+    uint64_t chunk_min_reads = 96 * 1024;
     uint32_t l2_fetch = 0;          // 0 = leave the device default
     uint32_t lanes = 4;
 };
@@ -301,6 +303,7 @@ struct Replica {
     int dev = 0;
     std::vector<Lane> lanes;
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
+    DevBuf shard_off, shard_pos, shard_len;   // multi-GPU mems: a shard's records wait here for their global offset
     ImageView view;
     std::mutex mu;
     double t[6] = {0, 0, 0, 0, 0, 0};
@@ -309,6 +312,7 @@ struct Replica {
         cudaSetDevice(dev);
         rows.release(); row_pos.release(); crun_row.release(); slots.release(); nodes.release(); pool.release();
         sym.release(); counters.release();
+        shard_off.release(); shard_pos.release(); shard_len.release();
         for (Lane& L : lanes) {
             L.scratch.release();
             for (auto& e : L.events) if (e) cudaEventDestroy(e);
@@ -445,19 +449,26 @@ struct BadBatch : std::runtime_error {
     using std::runtime_error::runtime_error;
 };
 
-// Next chunk of reads [a, r1): as many reads as fit chunk_bases (at least one).  Validates the offsets it
-// walks over (the only pass the host makes over them).
-ChunkPlan plan_chunk(const uint64_t* offsets, uint64_t a, uint64_t r1, uint64_t chunk_bases) {
+// Next chunk of reads [a, r1).  A chunk is closed once it holds chunk_bases bases AND min_reads reads (a kernel
+// needs ~10^5 independent reads in flight whatever their length), or when it reaches hard_cap bases (device scratch
+// is ~24 bytes per base per lane; chunk-relative offsets are 32-bit).  Always at least one read.  Validates the
+// offsets it walks over (the only pass the host makes over them).
+constexpr uint64_t kChunkHardCap = 1ull << 29;
+
+ChunkPlan plan_chunk(const uint64_t* offsets, uint64_t a, uint64_t r1, uint64_t chunk_bases, uint64_t min_reads,
+                     uint64_t hard_cap = kChunkHardCap) {
     ChunkPlan p;
     p.first = a;
     p.base = offsets[a];
     uint64_t b = a, lo = ~0ull, hi = 0;
-    const uint64_t limit = chunk_bases > ~0ull - p.base ? ~0ull : p.base + chunk_bases;
     while (b < r1 && b - a < 0x7FFFFFE0ull) {
         const uint64_t s = offsets[b], e = offsets[b + 1];
         if (e < s) throw BadBatch("offsets must be non-decreasing");
         if (e - s >= 0x7FFFFFFFull) throw BadBatch("reads of 2^31 bases or more are not supported");
-        if (e > limit && b != a) break;
+        if (b != a) {
+            const uint64_t with = e - p.base;
+            if (with > hard_cap || (with > chunk_bases && b - a >= min_reads)) break;
+        }
         lo = std::min(lo, e - s);
         hi = std::max(hi, e - s);
         ++b;
@@ -474,26 +485,55 @@ __global__ void k_shift(uint64_t* __restrict__ a, uint64_t n, uint64_t by) {
     if (i < n) a[i] += by;
 }
 
+// Multi-GPU mems: shard g may send its records home once the record totals of shards 0..g-1 are known.
+struct Rendezvous {
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<int64_t> total;      // -1 = not yet known, -2 = that shard failed
+    explicit Rendezvous(int parts) : total(parts, -1) {}
+    void publish(int g, int64_t t) {
+        { std::lock_guard<std::mutex> lock(mu); total[g] = t; }
+        cv.notify_all();
+    }
+    uint64_t base_of(int g) {
+        std::unique_lock<std::mutex> lock(mu);
+        uint64_t base = 0;
+        for (int h = 0; h < g; ++h) {
+            cv.wait(lock, [&] { return total[h] != -1; });
+            if (total[h] < 0) throw std::runtime_error("another GPU's shard failed");
+            base += (uint64_t)total[h];
+        }
+        return base;
+    }
+};
+
 // Processes reads [r0, r1) of a host batch on one replica.  Chunks alternate between the replica's
 // lanes (stream + scratch each), so the copies of one chunk overlap the kernels of the other.
 // mems: records go to rec_pos/rec_len (contiguous from index 0, capacity rec_cap) and per-read record
 // offsets (relative to this shard) to rec_off[0 .. r1-r0]; *needed receives the shard's record count.
 void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, const uint64_t* offsets, uint64_t r0, uint64_t r1,
                uint64_t* pointers, uint64_t* lengths, uint64_t* rec_off, void* rec_pos, void* rec_len, uint64_t rec_cap,
-               uint64_t* needed, int rec_bytes = 8) {
+               uint64_t* needed, int rec_bytes = 8, Rendezvous* rv = nullptr, int shard = 0) {
+    // rv != null: rec_off / rec_pos / rec_len are the CALLER's whole-batch arrays; this shard's records are kept on
+    // the device until the shards before it have published their totals, then copied to their final place.
     std::lock_guard<std::mutex> lock(R.mu);
     CK(cudaSetDevice(R.dev));
     for (double& x : R.t) x = 0;
     std::vector<ChunkPlan> plans;
     for (uint64_t a = r0; a < r1;) {
-        plans.push_back(plan_chunk(offsets, a, r1, idx->opt.chunk_bases));
+        plans.push_back(plan_chunk(offsets, a, r1, idx->opt.chunk_bases, idx->opt.chunk_min_reads));
         a += plans.back().n;
     }
     const size_t nc = plans.size(), kLanes_ = R.lanes.size();
     for (Lane& L : R.lanes) L.used = 0;
     std::vector<size_t> ev_at(nc);
     uint64_t rec_total = 0;
-    if (mems) rec_off[0] = 0;
+    if (mems && !rv) rec_off[0] = 0;
+    if (rv) {
+        R.shard_off.reserve((r1 - r0 + 1) * 8);
+        R.shard_pos.reserve((offsets[r1] - offsets[r0]) * rec_bytes + 16);
+        R.shard_len.reserve((offsets[r1] - offsets[r0]) * rec_bytes + 16);
+    }
 
     auto enqueue_front = [&](size_t c) {
         const ChunkPlan& p = plans[c];
@@ -538,10 +578,18 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
             g_launches++;
         }
         const bool last = c + 1 == nc;
-        CK(cudaMemcpyAsync(rec_off + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
-        if (rec_total + k <= rec_cap && k) {
-            CK(cudaMemcpyAsync((char*)rec_pos + rec_total * rec_bytes, S.mem_pos.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
-            CK(cudaMemcpyAsync((char*)rec_len + rec_total * rec_bytes, S.mem_len.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
+        if (rv) {
+            CK(cudaMemcpyAsync(R.shard_off.as<uint64_t>() + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToDevice, L.stream));
+            if (k) {
+                CK(cudaMemcpyAsync(R.shard_pos.as<char>() + rec_total * rec_bytes, S.mem_pos.p, k * rec_bytes, cudaMemcpyDeviceToDevice, L.stream));
+                CK(cudaMemcpyAsync(R.shard_len.as<char>() + rec_total * rec_bytes, S.mem_len.p, k * rec_bytes, cudaMemcpyDeviceToDevice, L.stream));
+            }
+        } else {
+            CK(cudaMemcpyAsync(rec_off + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
+            if (rec_total + k <= rec_cap && k) {
+                CK(cudaMemcpyAsync((char*)rec_pos + rec_total * rec_bytes, S.mem_pos.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
+                CK(cudaMemcpyAsync((char*)rec_len + rec_total * rec_bytes, S.mem_len.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
+            }
         }
         CK(cudaEventRecord(e[5], L.stream));
         rec_total += k;
@@ -559,6 +607,31 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
         for (int k = 0; k < 5; ++k) R.t[k] += ev_ms(e[k], e[k + 1]);
         cudaEvent_t* e0 = R.lanes[0].events.data() + ev_at[0];
         R.t[5] = std::max<double>(R.t[5], ev_ms(e0[0], e[5]));
+    }
+    if (rv) {
+        rv->publish(shard, (int64_t)rec_total);
+        const uint64_t gbase = rv->base_of(shard);
+        Lane& L = R.lanes[0];
+        const size_t at = L.used;
+        L.take();
+        cudaEvent_t* e = L.events.data() + at;
+        const uint64_t nr = r1 - r0;
+        const bool last_shard = shard + 1 == (int)rv->total.size();
+        CK(cudaEventRecord(e[0], L.stream));
+        if (gbase && nr) {
+            k_shift<<<(unsigned)((nr + 1 + 255) / 256), 256, 0, L.stream>>>(R.shard_off.as<uint64_t>(), nr + 1, gbase);
+            g_launches++;
+        }
+        CK(cudaMemcpyAsync(rec_off + r0, R.shard_off.p, (nr + (last_shard ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
+        if (gbase + rec_total <= rec_cap && rec_total) {
+            CK(cudaMemcpyAsync((char*)rec_pos + gbase * rec_bytes, R.shard_pos.p, rec_total * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
+            CK(cudaMemcpyAsync((char*)rec_len + gbase * rec_bytes, R.shard_len.p, rec_total * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
+        }
+        CK(cudaEventRecord(e[1], L.stream));
+        CK(cudaStreamSynchronize(L.stream));
+        const double ms = ev_ms(e[0], e[1]);
+        R.t[4] += ms;
+        R.t[5] += ms;
     }
     if (needed) *needed = rec_total;
 }
@@ -621,6 +694,7 @@ int moni_gpu_set_option(const char* key, const char* value) {
     else if (k == "verbose") g_opt.verbose = v != 0;
     else if (k == "count") { g_opt.count = v != 0; g_count.store(v != 0); }
     else if (k == "chunk_bases" && v >= 1 && v <= (1ll << 31)) g_opt.chunk_bases = (uint64_t)v;
+    else if (k == "chunk_min_reads" && v >= 0) g_opt.chunk_min_reads = (uint64_t)v;
     else if (k == "lanes" && v >= 1 && v <= kMaxLanes) g_opt.lanes = (uint32_t)v;
     else if (k == "l2_fetch" && (v == 0 || v == 32 || v == 64 || v == 128)) g_opt.l2_fetch = (uint32_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }
@@ -765,37 +839,32 @@ static int mems_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offs
                       rec_bytes);
             collect_times(idx);
         } else {
-            // every shard fills private buffers; they are stitched together in input order afterwards
-            struct Part { std::vector<uint64_t> off; std::vector<char> pos, len; uint64_t k = 0; int rc = 0; std::string err; };
-            std::vector<Part> parts(G);
+            // every shard keeps its records on its GPU until the totals of the shards before it are known, then copies
+            // them straight to their final place in the caller's arrays (input order, no host-side stitching)
+            Rendezvous rv(G);
+            std::vector<uint64_t> k(G, 0);
+            std::vector<int> rc(G, 0);
+            std::vector<std::string> errs(G);
             std::vector<std::thread> th;
             for (int g = 0; g < G; ++g)
                 th.emplace_back([&, g]() {
-                    Part& P = parts[g];
-                    P.rc = guarded([&]() -> int {
-                        const uint64_t nr = cut[g + 1] - cut[g], cap = offsets[cut[g + 1]] - offsets[cut[g]];
-                        P.off.assign(nr + 1, 0);
-                        P.pos.resize((cap + 1) * rec_bytes);
-                        P.len.resize((cap + 1) * rec_bytes);
-                        if (nr) run_shard(idx, *idx->reps[g], true, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, P.off.data(), P.pos.data(),
-                                          P.len.data(), cap, &P.k, rec_bytes);
+                    bool published = false;
+                    rc[g] = guarded([&]() -> int {
+                        if (cut[g + 1] > cut[g]) {
+                            run_shard(idx, *idx->reps[g], true, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, mem_offsets, mem_pos, mem_len,
+                                      mem_capacity, &k[g], rec_bytes, &rv, g);
+                            published = true;
+                        }
                         return 0;
                     });
-                    if (P.rc) P.err = g_err;
+                    if (rc[g]) errs[g] = g_err;
+                    if (!published) rv.publish(g, rc[g] ? -2 : 0);     // empty or failed shard: never leave the others waiting
                 });
             for (auto& t : th) t.join();
             collect_times(idx);
-            for (int g = 0; g < G; ++g) if (parts[g].rc) { g_err = parts[g].err; return parts[g].rc; }
-            for (int g = 0; g < G; ++g) {
-                const Part& P = parts[g];
-                const uint64_t nr = cut[g + 1] - cut[g];
-                for (uint64_t i = 0; i <= nr; ++i) mem_offsets[cut[g] + i] = needed + P.off[i];
-                if (needed + P.k <= mem_capacity && P.k) {
-                    memcpy((char*)mem_pos + needed * rec_bytes, P.pos.data(), P.k * rec_bytes);
-                    memcpy((char*)mem_len + needed * rec_bytes, P.len.data(), P.k * rec_bytes);
-                }
-                needed += P.k;
-            }
+            for (int g = 0; g < G; ++g) if (rc[g]) { g_err = errs[g]; return rc[g]; }
+            for (int g = 0; g < G; ++g) needed += k[g];
+            mem_offsets[n_reads] = needed;      // also covers trailing shards without reads
         }
         if (needed > mem_capacity) {
             g_err = "mem_capacity too small: " + std::to_string(needed) + " records needed";
@@ -854,7 +923,7 @@ int moni_gpu_batch_create(moni_gpu_index* idx, int gpu_slot, const char* seqs, c
         Replica& R = *b->rep;
         std::lock_guard<std::mutex> lock(R.mu);
         CK(cudaSetDevice(R.dev));
-        b->plan = plan_chunk(offsets, 0, n_reads, ~0ull);
+        b->plan = plan_chunk(offsets, 0, n_reads, ~0ull, 0, ~0ull);
         const ChunkPlan& p = b->plan;
         b->s.reserve(p, true, true);
         if (p.bases) CK(cudaMemcpyAsync(b->s.seqs.p, seqs + p.base, p.bases, cudaMemcpyHostToDevice, R.stream()));

@@ -104,10 +104,12 @@ def test_chunking_and_resident_batches_agree(m, oracle_mod):
     reads = synth.short_reads(text, 5000, 120, 9)
     flat, offs = m.pack_reads(reads)
     m.set_option("chunk_bases", 7001)
+    m.set_option("chunk_min_reads", 1)
     try:
         small = m.MoniIndex(pre)
     finally:
         m.set_option("chunk_bases", 1 << 24)
+        m.set_option("chunk_min_reads", 96 * 1024)
     big = m.MoniIndex(pre)
     a = small.matching_statistics(flat, offs)
     b = big.matching_statistics(flat, offs)
@@ -136,6 +138,32 @@ def test_mems32_equals_mems(m, indexes):
     b = indexes["pan4"].maxrimal_exact_matches(flat, offs, dtype=np.uint32)
     assert b[1].dtype == np.uint32 and b[2].dtype == np.uint32
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
+@pytest.mark.parametrize("case", ["pan4", "withN"])
+def test_sharded_over_replicas_keeps_input_order(case, m, indexes, oracle_mod):
+    """The multi-GPU path (one replica per listed device, reads split by bases, records copied to their global place once
+    the earlier shards' totals are known).  Listing device 0 three times runs it on a one-GPU box."""
+    import synth
+    pre = os.path.join(GOLDEN, case + ".fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = list(synth.short_reads(text, 2000, 90, 11, err=0.02)) + synth.long_reads(text, 30, 12, mean=900, sd=400, lo=50, hi=2500)
+    flat, offs = m.pack_reads(reads)
+    three = m.MoniIndex(pre, gpus=[0, 0, 0])
+    one = indexes[case]
+    a, b = one.matching_statistics(flat, offs), three.matching_statistics(flat, offs)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    for dt in (np.uint64, np.uint32):
+        am, bm = one.maxrimal_exact_matches(flat, offs, dtype=dt), three.maxrimal_exact_matches(flat, offs, dtype=dt)
+        assert all(np.array_equal(x, y) for x, y in zip(am, bm))
+    wmo, wmp, wml = orc.mems(flat, offs)
+    assert np.array_equal(bm[0], wmo) and np.array_equal(bm[1], wmp) and np.array_equal(bm[2], wml)
+    # fewer reads than shards: some shards are empty
+    f2, o2 = pack([b"ACGTTGCAAC", b""])
+    x, y = one.maxrimal_exact_matches(f2, o2), three.maxrimal_exact_matches(f2, o2)
+    assert all(np.array_equal(p, q) for p, q in zip(x, y))
+    three.close()
 
 
 def test_mem_capacity_error(m, indexes):
