@@ -285,7 +285,7 @@ def ours_arm(args) -> None:
         except Exception:
             traffic = None
     cpu = None
-    if not args.no_cpu_baseline and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "mems")):
+    if not args.no_cpu_baseline and world == 1 and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "mems")):
         try:
             pairs = max(1000, args.ref_reads // 2)
             sample = workloads.reads_of(args.workload, pairs=pairs)

@@ -519,14 +519,13 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
     std::lock_guard<std::mutex> lock(R.mu);
     CK(cudaSetDevice(R.dev));
     for (double& x : R.t) x = 0;
+    // chunks are planned (and their offsets validated) just before they are enqueued, so the host's pass over the
+    // offsets overlaps the GPU's work on earlier chunks
     std::vector<ChunkPlan> plans;
-    for (uint64_t a = r0; a < r1;) {
-        plans.push_back(plan_chunk(offsets, a, r1, idx->opt.chunk_bases, idx->opt.chunk_min_reads));
-        a += plans.back().n;
-    }
-    const size_t nc = plans.size(), kLanes_ = R.lanes.size();
+    uint64_t next_read = r0;
+    const size_t kLanes_ = R.lanes.size();
     for (Lane& L : R.lanes) L.used = 0;
-    std::vector<size_t> ev_at(nc);
+    std::vector<size_t> ev_at;
     uint64_t rec_total = 0;
     if (mems && !rv) rec_off[0] = 0;
     if (rv) {
@@ -540,7 +539,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
         Lane& L = R.lanes[c % kLanes_];
         Scratch& S = L.scratch;
         S.reserve(p, !mems, mems);
-        ev_at[c] = L.used;
+        ev_at.push_back(L.used);
         L.take();
         cudaEvent_t* e = L.events.data() + ev_at[c];
         CK(cudaEventRecord(e[0], L.stream));
@@ -577,7 +576,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
             k_shift<<<(unsigned)((p.n + 1 + 255) / 256), 256, 0, L.stream>>>(S.moff.as<uint64_t>(), p.n + 1, rec_total);
             g_launches++;
         }
-        const bool last = c + 1 == nc;
+        const bool last = p.first + p.n == r1;
         if (rv) {
             CK(cudaMemcpyAsync(R.shard_off.as<uint64_t>() + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToDevice, L.stream));
             if (k) {
@@ -597,11 +596,31 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
 
     // keep lanes - 1 chunks enqueued ahead of the one whose results are being sent home
     size_t fronted = 0;
-    for (size_t c = 0; c < nc; ++c) {
-        while (fronted < nc && fronted < c + kLanes_) enqueue_front(fronted++);
-        if (mems) finish_mems(c);
+    try {
+        for (size_t c = 0; c < fronted || next_read < r1; ++c) {
+            while (next_read < r1 && fronted < c + kLanes_) {
+                plans.push_back(plan_chunk(offsets, next_read, r1, idx->opt.chunk_bases, idx->opt.chunk_min_reads));
+                next_read += plans.back().n;
+                enqueue_front(fronted++);
+            }
+            if (mems) finish_mems(c);
+        }
+    } catch (...) {
+        // a bad offset found mid-batch (or a CUDA failure): nothing may still be writing the caller's buffers when we return
+        for (Lane& L : R.lanes) cudaStreamSynchronize(L.stream);
+        throw;
     }
+    const size_t nc = plans.size();
     for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
+    if (nc && getenv("MONI_GPU_TRACE")) {      // per-chunk timeline (ms since the first event): where the pipeline idles
+        cudaEvent_t* e0 = R.lanes[0].events.data() + ev_at[0];
+        for (size_t c = 0; c < nc; ++c) {
+            cudaEvent_t* e = R.lanes[c % kLanes_].events.data() + ev_at[c];
+            fprintf(stderr, "[moni-gpu trace] gpu %d chunk %zu lane %zu reads %llu:", R.dev, c, c % kLanes_, (unsigned long long)plans[c].n);
+            for (int k = 0; k < kEv; ++k) fprintf(stderr, " %.3f", ev_ms(e0[0], e[k]));
+            fprintf(stderr, "   (start h2d pass1 pass2 compact d2h)\n");
+        }
+    }
     for (size_t c = 0; c < nc; ++c) {
         cudaEvent_t* e = R.lanes[c % kLanes_].events.data() + ev_at[c];
         for (int k = 0; k < 5; ++k) R.t[k] += ev_ms(e[k], e[k + 1]);

@@ -230,6 +230,8 @@ struct LenState {
     uint32_t i = 0, l = 0, prev_len = 0, n_mems = 0, mode = ADVANCE;
     uint32_t ref = 0;               // DESCEND: current grammar reference
     uint64_t pos = 0, prev_ptr = 0;
+    uint64_t nxt = 0;               // pointer of query offset i, loaded one step ahead (valid once primed)
+    bool primed = false;
     uint64_t span = 0, p = 0;       // DESCEND: expansion length of ref, offset inside it
     const uint8_t* t = nullptr;     // COMPARE: next text byte
     uint64_t rem = 0;               // COMPARE: text bytes left in the literal block
@@ -245,7 +247,11 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
     const uint64_t N = v.hdr.text_len;
     bool done = false;
     if (st.mode == LenState::ADVANCE) {
-        st.pos = ptr[(int64_t)st.i * ptr_stride];
+        // the pointer of the NEXT offset is requested now and consumed one micro-step later, so its latency hides behind
+        // this offset's text access
+        if (!st.primed) { st.nxt = ld(ptr + (int64_t)st.i * ptr_stride); st.primed = true; }
+        st.pos = st.nxt;
+        if (st.i + 1 < m) st.nxt = ld(ptr + (int64_t)(st.i + 1) * ptr_stride);
         done = true;
         if (st.i == 0 || st.pos != st.prev_ptr + 1) {            // otherwise the loop body never runs: l carries over
             if (cnt) cnt->restarts++;
