@@ -238,13 +238,14 @@ def ours_arm(args) -> None:
     h_ml32 = m.pinned_empty(total, np.uint32)
 
     def e2e_leg(out):
+        call = ix.maxrimal_exact_matches if len(out) == 3 else ix.maxrimal_exact_matches_packed
         for _ in range(args.warmup):
-            ix.maxrimal_exact_matches(h_seqs, h_offs, out=out)
+            call(h_seqs, h_offs, out=out)
         barrier()
         dev_sum, stage = 0.0, np.zeros(6)
         t_wall = time.perf_counter()
         for _ in range(args.steps):
-            ix.maxrimal_exact_matches(h_seqs, h_offs, out=out)
+            call(h_seqs, h_offs, out=out)
             tt = ix.timing()
             dev_sum += tt["total_ms"]
             stage += np.array([tt[k] for k in ("h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms")])
@@ -255,9 +256,15 @@ def ours_arm(args) -> None:
     e2e64_dev_ms, e2e64_wall_ms, stage64 = e2e_leg((h_mo, h_mp, h_ml))
     same64 = bool(np.array_equal(h_mo, mo) and np.array_equal(h_mp[:n_mems], mp) and np.array_equal(h_ml[:n_mems], ml))
     h_mo[:] = 0
-    e2e_dev_ms, e2e_wall_ms, stage = e2e_leg((h_mo, h_mp32, h_ml32))
+    e2e32_dev_ms, e2e32_wall_ms, stage32 = e2e_leg((h_mo, h_mp32, h_ml32))
+    same32 = bool(np.array_equal(h_mo, mo) and np.array_equal(h_mp32[:n_mems], mp) and np.array_equal(h_ml32[:n_mems], ml))
+    # headline: one packed 32-bit word per record (reads are shorter than 65536 bases)
+    h_mo[:] = 0
+    h_rec = h_mp32
+    e2e_dev_ms, e2e_wall_ms, stage = e2e_leg((h_mo, h_rec))
     clocks = sampler.summary() if sampler else None
-    same = bool(same64 and np.array_equal(h_mo, mo) and np.array_equal(h_mp32[:n_mems], mp) and np.array_equal(h_ml32[:n_mems], ml))
+    same = bool(same64 and same32 and np.array_equal(h_mo, mo) and np.array_equal(h_rec[:n_mems] >> 16, mp)
+                and np.array_equal(h_rec[:n_mems] & 0xFFFF, ml))
     all_reads = sum_over_ranks(float(n_reads), dev)
     if rank != 0:
         if world > 1:
@@ -313,10 +320,13 @@ def ours_arm(args) -> None:
                      "other_kernel": {"kernel": "k_ms_lengths" if dom == "pass1" else "k_ms_pointers",
                                       "achieved": alg["pass2" if dom == "pass1" else "pass1"] / (per["pass2" if dom == "pass1" else "pass1"] / 1e3) / 1e9}},
         "counters_per_step": cnt,
-        "e2e": {"value": e2e_value, "unit": "reads/s", "api": "moni_gpu_mems32", "h2d_bytes_per_step": int(total + 8 * (n_reads + 1)),
-                "d2h_bytes_per_step": int(8 * (n_reads + 1) + 8 * n_mems), "ms_per_step_wall": e2e_wall_ms / args.steps,
+        "e2e": {"value": e2e_value, "unit": "reads/s", "api": "moni_gpu_mems_packed", "h2d_bytes_per_step": int(total + 8 * (n_reads + 1)),
+                "d2h_bytes_per_step": int(8 * (n_reads + 1) + 4 * n_mems), "ms_per_step_wall": e2e_wall_ms / args.steps,
                 "ms_per_step_device": e2e_dev_ms / args.steps, "same_bits_as_resident_run": same,
                 "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage / args.steps).tolist()))},
+        "e2e_u32": {"value": all_reads * args.steps / (e2e32_wall_ms / 1e3), "unit": "reads/s", "api": "moni_gpu_mems32",
+                    "d2h_bytes_per_step": int(8 * (n_reads + 1) + 8 * n_mems), "ms_per_step_wall": e2e32_wall_ms / args.steps,
+                    "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage32 / args.steps).tolist()))},
         "e2e_u64": {"value": all_reads * args.steps / (e2e64_wall_ms / 1e3), "unit": "reads/s", "api": "moni_gpu_mems",
                     "d2h_bytes_per_step": int(8 * (n_reads + 1) + 16 * n_mems), "ms_per_step_wall": e2e64_wall_ms / args.steps,
                     "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage64 / args.steps).tolist()))},

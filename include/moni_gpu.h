@@ -39,7 +39,10 @@ typedef struct moni_gpu_batch moni_gpu_batch; /* opaque: a read batch resident i
 /* Replaces ms_c<slp_t>::ms_c(std::string) / mems_c::mems_c  (src/matching_statistics.cpp:195-228,
  * src/mems.cpp:195-228): reads `<prefix>.thrbv.ms` (ms_pointers::load, include/ms/ms_pointers.hpp:307-320)
  * and `<prefix>.plain.slp` (PlainSlp::load, thirdparty/ShapedSlp/PlainSlp.hpp:305-319), flattens them
- * and uploads one replica to every listed CUDA device.  gpus == NULL: devices 0..n_gpus-1. */
+ * and uploads one replica to every listed CUDA device.  gpus == NULL: devices 0..n_gpus-1.
+ * If `<prefix>.thrbv.ms` does not exist, the `moni align` index `<prefix>.thrbv.full.ms` (ms_pointers<>::load,
+ * include/ms/moni.hpp:392-409) or `<prefix>.thrbv.full.lcp.ms` (moni_lcp<>::load, include/aligner/moni_lcp.hpp:208-225) is
+ * read instead: same query structures, the Phi / LCP members are skipped. */
 int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gpu_index** out);
 void moni_gpu_index_free(moni_gpu_index* idx);
 
@@ -65,6 +68,20 @@ int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets
  * (< 2^32, enforced), so this halves the device->host traffic of the call, which is what bounds it. */
 int moni_gpu_mems32(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
                     uint64_t* mem_offsets, uint32_t* mem_pos, uint32_t* mem_len, uint64_t mem_capacity);
+
+/* Same records as one 32-bit word each, (query offset << 16) | length: for batches whose reads are all shorter than
+ * 65536 bases (else MONI_GPU_EINVAL).  Halves the device->host bytes of moni_gpu_mems32 again (4 bytes per record). */
+int moni_gpu_mems_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
+                         uint64_t* mem_offsets, uint32_t* mem_rec, uint64_t mem_capacity);
+
+/* Replaces seed_finder<slp_t, ms_t>::find_mems(const kseq_t*, std::vector<mem_t>&, r_offset, mate)
+ * (include/aligner/seed_finder.hpp:126-166), the seed stage of `moni align`, for a whole batch: same two passes, with the
+ * record rule of :148 -- l >= pl and n_Ns < l and l >= min_len (n_Ns = the run of 'N' ending the characters matched so
+ * far, :139-143).  Record k of read r, k in [seed_offsets[r], seed_offsets[r+1]): mem_t.pos = seed_ref[k] (= pointers[i]),
+ * mem_t.len = seed_len[k], mem_t.idx = seed_qpos[k]; mem_t.rpos = r_offset + idx + len - 1 and mem_t.mate are the caller's.
+ * Works on any of the three index files (moni_gpu_index_load).  Capacity rule as for moni_gpu_mems. */
+int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t min_len,
+                   uint64_t* seed_offsets, uint64_t* seed_ref, uint32_t* seed_qpos, uint32_t* seed_len, uint64_t seed_capacity);
 
 /* Event counters accumulated over all calls since the last reset, when counting is enabled
  * (moni_gpu_set_option("count", "1"); off by default, it costs a few percent):

@@ -8,6 +8,7 @@ Host-side mirror of the reference's two call sites for this path, over the C ABI
     ms_c<slp_t>::ms_c(prefix)      src/matching_statistics.cpp:195   MoniIndex(prefix, gpus=[...])
     ms_c::matching_statistics      src/matching_statistics.cpp:242   MoniIndex.matching_statistics
     mems_c::maxrimal_exact_matches src/mems.cpp:241                  MoniIndex.maxrimal_exact_matches
+    seed_finder::find_mems         include/aligner/seed_finder.hpp:126   MoniIndex.find_mems
 
 The method names (including the reference's spelling of "maxrimal") and the meaning of the results
 are the reference's; the unit of work is a batch of reads instead of one kseq record.  There is no
@@ -37,6 +38,7 @@ class MoniGpuError(RuntimeError):
 
 EXPORTS = [
     "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems", "moni_gpu_mems32",
+    "moni_gpu_mems_packed", "moni_gpu_seeds",
     "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
@@ -61,6 +63,8 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_ms.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, _u64p]
     L.moni_gpu_mems.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, _u64p, _u64p, ctypes.c_uint64]
     L.moni_gpu_mems32.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, ctypes.c_uint64]
+    L.moni_gpu_mems_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, ctypes.c_uint64]
+    L.moni_gpu_seeds.argtypes = [vp, vp, _u64p, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, vp, vp, ctypes.c_uint64]
     L.moni_gpu_counters.argtypes = [vp, _u64p, ci]
     L.moni_gpu_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.moni_gpu_set_option.argtypes = [cc, cc]
@@ -205,6 +209,39 @@ class MoniIndex:
         k = int(mo[nr])
         return mo, mp[:k], ml[:k]
 
+    def maxrimal_exact_matches_packed(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
+        """(mem_offsets uint64[n+1], mem_rec uint32[k]) with mem_rec = (query offset << 16) | length -- moni_gpu_mems_packed;
+        every read must be shorter than 65536 bases."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        nr = offsets.shape[0] - 1
+        if out is None:
+            mo = np.empty(nr + 1, dtype=np.uint64)
+            rec = np.empty(max(int(offsets[-1]), 1), dtype=np.uint32)
+        else:
+            mo, rec = out
+        _check(self._L.moni_gpu_mems_packed(self._h, _ptr(seqs), _u64(offsets), nr, _u64(mo), _ptr(rec), rec.shape[0]))
+        return mo, rec[:int(mo[nr])]
+
+    def find_mems(self, seqs: np.ndarray, offsets: np.ndarray, min_len: int = 0, out=None):
+        """(seed_offsets uint64[n+1], seed_ref uint64[k], seed_qpos uint32[k], seed_len uint32[k]) -- seed_finder::find_mems
+        (include/aligner/seed_finder.hpp:126-166) for every read: mem_t.pos, mem_t.idx, mem_t.len."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        nr = offsets.shape[0] - 1
+        if out is None:
+            so = np.empty(nr + 1, dtype=np.uint64)
+            ref = np.empty(max(total, 1), dtype=np.uint64)
+            qp = np.empty(max(total, 1), dtype=np.uint32)
+            ln = np.empty(max(total, 1), dtype=np.uint32)
+        else:
+            so, ref, qp, ln = out
+        _check(self._L.moni_gpu_seeds(self._h, _ptr(seqs), _u64(offsets), nr, int(min_len), _u64(so), _u64(ref), _ptr(qp), _ptr(ln),
+                                      ref.shape[0]))
+        k = int(so[nr])
+        return so, ref[:k], qp[:k], ln[:k]
+
     # -- instrumentation -----------------------------------------------------------------------
     def counters(self, reset: bool = True) -> dict:
         c = (ctypes.c_uint64 * 8)()
@@ -281,4 +318,13 @@ def format_mems(names: Iterable[bytes], mem_offsets, mem_pos, mem_len) -> bytes:
     for r, nm in enumerate(names):
         a, b = int(mem_offsets[r]), int(mem_offsets[r + 1])
         out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d) " % (int(mem_pos[t]), int(mem_len[t])) for t in range(a, b)) + b"\n")
+    return b"".join(out)
+
+
+def format_seeds(names: Iterable[bytes], seed_offsets, seed_ref, seed_len, seed_qpos) -> bytes:
+    """Seeds as '(' pos ',' len ',' idx ') ' tokens per read (mem_t.pos, .len, .idx; include/aligner/mems.hpp:30-35)."""
+    out = []
+    for r, nm in enumerate(names):
+        a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
+        out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d,%d) " % (int(seed_ref[t]), int(seed_len[t]), int(seed_qpos[t])) for t in range(a, b)) + b"\n")
     return b"".join(out)

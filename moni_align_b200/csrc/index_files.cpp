@@ -188,7 +188,11 @@ void read_wt_huff(Cursor& c, std::vector<uint8_t>& seq) {
 
 }  // namespace
 
-void read_thrbv_ms(const std::string& path, FlatRlbwt& o) {
+// `full`: the `moni align` index (include/ms/moni.hpp:359-382 / include/aligner/moni_lcp.hpp:208-225): the same members
+// in the same order with the Phi structures in between -- after the BWT: pred (sparse_sd_vector) and pred_to_run
+// (int_vector<>), after the thresholds: pred_start and pred_start_to_run -- and, in the .lcp variant, one trailing
+// int_vector<> slcp.  The matching-statistics query (moni.hpp:568-626) reads none of them; they are parsed and skipped.
+void read_thrbv_ms(const std::string& path, FlatRlbwt& o, bool full) {
     MappedFile mf(path);
     Cursor c{mf.p, mf.size, 0, path};
     o.terminator_position = c.u64("terminator_position");
@@ -238,13 +242,28 @@ void read_thrbv_ms(const std::string& path, FlatRlbwt& o) {
     }
     per_letter.clear();
     per_letter.shrink_to_fit();
+    if (full) {
+        std::vector<uint64_t> pred;
+        read_sparse_sd(c, pred, "pred");
+        if (read_int_vector(c, 0, "pred_to_run").size() != o.R || pred.size() != o.R)
+            throw std::runtime_error(path + ": Phi structures (pred) do not have R entries");
+    }
     unpack(read_int_vector(c, 0, "samples_last"), o.samples_last);
     for (int s = 0; s < 256; ++s) {
         read_sparse_sd(c, o.thr[s], "thresholds_per_letter");
         for (size_t i = 1; i < o.thr[s].size(); ++i)
             if (o.thr[s][i] <= o.thr[s][i - 1]) throw std::runtime_error(path + ": thresholds not increasing");
     }
+    if (full) {
+        std::vector<uint64_t> pred;
+        read_sparse_sd(c, pred, "pred_start");
+        if (read_int_vector(c, 0, "pred_start_to_run").size() != o.R || pred.size() != o.R)
+            throw std::runtime_error(path + ": Phi structures (pred_start) do not have R entries");
+    }
     unpack(read_int_vector(c, 0, "samples_start"), o.samples_start);
+    if (full && c.off != c.size) {                    // .thrbv.full.lcp.ms: sampled LCP values, one per run
+        if (read_int_vector(c, 0, "slcp").size() != o.R) throw std::runtime_error(path + ": slcp does not have R entries");
+    }
     if (o.samples_last.size() != o.R || o.samples_start.size() != o.R)
         throw std::runtime_error(path + ": sample arrays do not have R entries");
     if (c.off != c.size) throw std::runtime_error(path + ": " + std::to_string(c.size - c.off) + " trailing bytes");

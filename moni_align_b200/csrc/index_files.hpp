@@ -37,7 +37,7 @@ struct FlatSlp {
 };
 
 // Both throw std::runtime_error with a message naming the file and the failing field.
-void read_thrbv_ms(const std::string& path, FlatRlbwt& out);
+void read_thrbv_ms(const std::string& path, FlatRlbwt& out, bool full = false);
 void read_plain_slp(const std::string& path, FlatSlp& out);
 
 }  // namespace moni

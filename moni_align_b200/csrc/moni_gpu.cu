@@ -9,6 +9,7 @@
 // contiguous 256-byte line.  The per-read arithmetic lives in ms_core.cuh.
 // No tensor cores, no CPU fallback: without a device every entry point fails.
 #include <cuda_runtime.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <atomic>
@@ -143,26 +144,28 @@ __global__ void __launch_bounds__(kBlock) k_ms_pointers(ImageView v, const uint8
     if (COUNT) { c.bases = m; flush_counters(c, g); }
 }
 
-// ---- pass 2: MS lengths / MEM records --------------------------------------------------------------
-// MEMS == false: ptr_out[] and len_out[] (u64, laid out like seqs).  MEMS == true: the read's MEM
-// records, packed (i << 32) | len, go to rec[] at the read's own offset (at most one per base) and
-// counts[read] receives their number.
-template <bool MEMS, bool COUNT>
+// ---- pass 2: MS lengths / MEM records / seeds --------------------------------------------------------
+// MODE 0 (ms): ptr_out[] and len_out[] (u64, laid out like seqs).  MODE 1 (mems): the read's MEM records, packed
+// (i << 32) | len, go to rec[] at the read's own offset (at most one per base) and counts[read] receives their number.
+// MODE 2 (seeds): same with seed_finder::find_mems' rule (minimum length, N filter) and rec_ref[] = pointers[i].
+template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
                                                        const uint64_t* __restrict__ ptr_t, uint64_t* __restrict__ ptr_out,
                                                        uint64_t* __restrict__ len_out, uint64_t* __restrict__ rec,
-                                                       uint32_t* __restrict__ counts, Counters* g) {
+                                                       uint32_t* __restrict__ counts, Counters* g,
+                                                       uint64_t* __restrict__ rec_ref, uint32_t min_len) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
     if (slot >= cm.n_reads) return;
     const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
     const uint64_t a = __ldg(cm.offs + r);
     const uint64_t o = a - cm.base, m = __ldg(cm.offs + r + 1) - a;
-    if (m == 0) { if (MEMS) counts[r] = 0; return; }
+    if (m == 0) { if (MODE) counts[r] = 0; return; }
     const uint64_t* in = ptr_t + warp_base(cm, w) + lane + (m - 1) * 32u;     // query offset 0 = last step
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
-    const uint32_t k = lengths_read<uint64_t>(v, seqs + o, m, in, -32, MEMS ? nullptr : ptr_out + o, MEMS ? nullptr : len_out + o,
-                                              MEMS ? rec + o : nullptr, COUNT ? &c : nullptr);
-    if (MEMS) counts[r] = k;
+    const uint32_t k = lengths_read<uint64_t, MODE == 2>(v, seqs + o, m, in, -32, MODE ? nullptr : ptr_out + o, MODE ? nullptr : len_out + o,
+                                                         MODE ? rec + o : nullptr, COUNT ? &c : nullptr,
+                                                         MODE == 2 ? rec_ref + o : nullptr, min_len);
+    if (MODE) counts[r] = k;
     if (COUNT) flush_counters(c, g);
 }
 
@@ -178,6 +181,35 @@ __global__ void __launch_bounds__(kBlock) k_mem_gather(const uint64_t* __restric
         const uint64_t x = rec[o + k];
         mem_pos[a + k] = (OutT)(x >> 32);
         mem_len[a + k] = (OutT)(x & 0xFFFFFFFFull);
+    }
+}
+
+// Seeds: (query offset, length) as u32 and the text position as u64.
+__global__ void __launch_bounds__(kBlock) k_seed_gather(const uint64_t* __restrict__ rec, const uint64_t* __restrict__ rec_ref,
+                                                        const uint64_t* __restrict__ offs, uint64_t base, uint32_t n_reads,
+                                                        const uint64_t* __restrict__ moff, uint32_t* __restrict__ qpos,
+                                                        uint32_t* __restrict__ len, uint64_t* __restrict__ ref) {
+    const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (r >= n_reads) return;
+    const uint64_t o = offs[r] - base, a = moff[r], cnt = moff[r + 1] - a;
+    for (uint64_t k = lane; k < cnt; k += 32) {
+        const uint64_t x = rec[o + k];
+        qpos[a + k] = (uint32_t)(x >> 32);
+        len[a + k] = (uint32_t)(x & 0xFFFFFFFFull);
+        ref[a + k] = rec_ref[o + k];
+    }
+}
+
+// Same, one 32-bit word per record: (query offset << 16) | length.  Only for chunks whose reads are shorter than 2^16.
+__global__ void __launch_bounds__(kBlock) k_mem_gather_packed(const uint64_t* __restrict__ rec, const uint64_t* __restrict__ offs,
+                                                              uint64_t base, uint32_t n_reads, const uint64_t* __restrict__ moff,
+                                                              uint32_t* __restrict__ mem_rec) {
+    const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (r >= n_reads) return;
+    const uint64_t o = offs[r] - base, a = moff[r], cnt = moff[r + 1] - a;
+    for (uint64_t k = lane; k < cnt; k += 32) {
+        const uint64_t x = rec[o + k];
+        mem_rec[a + k] = ((uint32_t)(x >> 32) << 16) | (uint32_t)(x & 0xFFFFu);
     }
 }
 
@@ -255,12 +287,14 @@ struct ChunkPlan {
 
 struct Scratch {   // device buffers of one chunk
     DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, wbase, ptr_t, out_ptr, out_len, rec, counts, moff, mem_pos, mem_len, cub;
+    DevBuf rec_ref, mem_ref;     // seeds only
     void release() {
         for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &wbase, &ptr_t, &out_ptr, &out_len, &rec, &counts, &moff,
-                          &mem_pos, &mem_len, &cub})
+                          &mem_pos, &mem_len, &cub, &rec_ref, &mem_ref})
             b->release();
     }
-    void reserve(const ChunkPlan& p, bool ms, bool mems) {
+    void reserve(const ChunkPlan& p, bool ms, bool mems, bool seeds = false) {
+        if (seeds) { rec_ref.reserve(p.bases * 8 + 16); mem_ref.reserve(p.bases * 8 + 16); }
         seqs.reserve(p.bases + 16);
         offs.reserve((p.n + 1) * 8);
         ptr_t.reserve(p.ptr_entries() * 8);
@@ -303,7 +337,7 @@ struct Replica {
     int dev = 0;
     std::vector<Lane> lanes;
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
-    DevBuf shard_off, shard_pos, shard_len;   // multi-GPU mems: a shard's records wait here for their global offset
+    DevBuf shard_off, shard_pos, shard_len, shard_ref;   // multi-GPU mems: a shard's records wait here for their global offset
     ImageView view;
     std::mutex mu;
     double t[6] = {0, 0, 0, 0, 0, 0};
@@ -312,7 +346,7 @@ struct Replica {
         cudaSetDevice(dev);
         rows.release(); row_pos.release(); crun_row.release(); slots.release(); nodes.release(); pool.release();
         sym.release(); counters.release();
-        shard_off.release(); shard_pos.release(); shard_len.release();
+        shard_off.release(); shard_pos.release(); shard_len.release(); shard_ref.release();
         for (Lane& L : lanes) {
             L.scratch.release();
             for (auto& e : L.events) if (e) cudaEventDestroy(e);
@@ -397,26 +431,34 @@ void launch_pass1(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     CK(cudaGetLastError());
 }
 
-void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, bool mems, cudaStream_t st) {
+// mode: 0 = ms, 1 = mems, 2 = seeds
+void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, int mode, cudaStream_t st, uint32_t min_len = 0) {
     if (!p.n) return;
     const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
     const ChunkMap cm = chunk_map(S, p);
     Counters* g = g_count.load() ? R.counters.as<Counters>() : nullptr;
     const uint8_t* sq = S.seqs.as<uint8_t>();
     const uint64_t* pt = S.ptr_t.as<uint64_t>();
-    if (mems) {
-        if (g) k_ms_lengths<true, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, S.rec.as<uint64_t>(), S.counts.as<uint32_t>(), g);
-        else k_ms_lengths<true, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, S.rec.as<uint64_t>(), S.counts.as<uint32_t>(), nullptr);
+    uint64_t* rec = S.rec.as<uint64_t>();
+    uint32_t* cnt = S.counts.as<uint32_t>();
+    if (mode == 2) {
+        if (g) k_ms_lengths<2, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, g, S.rec_ref.as<uint64_t>(), min_len);
+        else k_ms_lengths<2, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, nullptr, S.rec_ref.as<uint64_t>(), min_len);
+    } else if (mode == 1) {
+        if (g) k_ms_lengths<1, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, g, nullptr, 0);
+        else k_ms_lengths<1, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, nullptr, nullptr, 0);
     } else {
-        if (g) k_ms_lengths<false, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, g);
-        else k_ms_lengths<false, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, nullptr);
+        if (g) k_ms_lengths<0, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, g, nullptr, 0);
+        else k_ms_lengths<0, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, nullptr, nullptr, 0);
     }
     g_launches++;
     CK(cudaGetLastError());
 }
 
 // counts -> exclusive offsets (n + 1 entries) -> gather.  mem_pos/mem_len hold `bases` entries.
-void launch_compact(Scratch& S, const ChunkPlan& p, bool narrow, cudaStream_t st) {
+// rec_bytes: 8 = two u64 arrays, 4 = two u32 arrays, 2 = one u32 array of packed (offset:16, length:16) records,
+// 12 = seeds (u32 query offset, u32 length, u64 text position)
+void launch_compact(Scratch& S, const ChunkPlan& p, int rec_bytes, cudaStream_t st) {
     if (!p.n) return;
     const uint32_t n = (uint32_t)p.n;
     uint64_t* wide = S.moff.as<uint64_t>() + (n + 1);          // second half of moff: widened counts
@@ -429,7 +471,13 @@ void launch_compact(Scratch& S, const ChunkPlan& p, bool narrow, cudaStream_t st
     g_launches += 2;
     const uint64_t threads = (uint64_t)n * 32;
     const unsigned blocks = (unsigned)((threads + kBlock - 1) / kBlock);
-    if (narrow)
+    if (rec_bytes == 12)
+        k_seed_gather<<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.rec_ref.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                 S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>(), S.mem_ref.as<uint64_t>());
+    else if (rec_bytes == 2)
+        k_mem_gather_packed<<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                       S.mem_pos.as<uint32_t>());
+    else if (rec_bytes == 4)
         k_mem_gather<uint32_t><<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
                                                           S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>());
     else
@@ -507,15 +555,28 @@ struct Rendezvous {
     }
 };
 
+// Where a mems / seeds call wants its records: up to three host columns of `width` bytes per record.
+struct RecOut {
+    uint64_t* off = nullptr;                     // per-read record offsets
+    void* col[3] = {nullptr, nullptr, nullptr};
+    int width[3] = {0, 0, 0};
+    int ncol = 0;
+    uint64_t cap = 0;                            // records the columns can hold
+    int fmt = 8;                                 // launch_compact format
+    uint32_t min_len = 0;                        // seeds
+};
+
 // Processes reads [r0, r1) of a host batch on one replica.  Chunks alternate between the replica's
 // lanes (stream + scratch each), so the copies of one chunk overlap the kernels of the other.
-// mems: records go to rec_pos/rec_len (contiguous from index 0, capacity rec_cap) and per-read record
-// offsets (relative to this shard) to rec_off[0 .. r1-r0]; *needed receives the shard's record count.
-void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, const uint64_t* offsets, uint64_t r0, uint64_t r1,
-               uint64_t* pointers, uint64_t* lengths, uint64_t* rec_off, void* rec_pos, void* rec_len, uint64_t rec_cap,
-               uint64_t* needed, int rec_bytes = 8, Rendezvous* rv = nullptr, int shard = 0) {
-    // rv != null: rec_off / rec_pos / rec_len are the CALLER's whole-batch arrays; this shard's records are kept on
+// mode 0 = ms, 1 = mems, 2 = seeds.  mems / seeds: records go to out.col[] (contiguous from index 0, capacity out.cap)
+// and per-read record offsets (relative to this shard) to out.off[0 .. r1-r0]; *needed receives the shard's record count.
+void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, const uint64_t* offsets, uint64_t r0, uint64_t r1,
+               uint64_t* pointers, uint64_t* lengths, const RecOut& out, uint64_t* needed, Rendezvous* rv = nullptr, int shard = 0) {
+    // rv != null: out.off / out.col are the CALLER's whole-batch arrays; this shard's records are kept on
     // the device until the shards before it have published their totals, then copied to their final place.
+    const bool mems = mode != 0;
+    uint64_t* const rec_off = out.off;
+    const uint64_t rec_cap = out.cap;
     std::lock_guard<std::mutex> lock(R.mu);
     CK(cudaSetDevice(R.dev));
     for (double& x : R.t) x = 0;
@@ -528,17 +589,17 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
     std::vector<size_t> ev_at;
     uint64_t rec_total = 0;
     if (mems && !rv) rec_off[0] = 0;
+    DevBuf* const shard_col[3] = {&R.shard_pos, &R.shard_len, &R.shard_ref};
     if (rv) {
         R.shard_off.reserve((r1 - r0 + 1) * 8);
-        R.shard_pos.reserve((offsets[r1] - offsets[r0]) * rec_bytes + 16);
-        R.shard_len.reserve((offsets[r1] - offsets[r0]) * rec_bytes + 16);
+        for (int k = 0; k < out.ncol; ++k) shard_col[k]->reserve((offsets[r1] - offsets[r0]) * out.width[k] + 16);
     }
 
     auto enqueue_front = [&](size_t c) {
         const ChunkPlan& p = plans[c];
         Lane& L = R.lanes[c % kLanes_];
         Scratch& S = L.scratch;
-        S.reserve(p, !mems, mems);
+        S.reserve(p, !mems, mems, mode == 2);
         ev_at.push_back(L.used);
         L.take();
         cudaEvent_t* e = L.events.data() + ev_at[c];
@@ -549,10 +610,11 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
         launch_prepare(S, p, L.stream);
         launch_pass1(R, S, p, L.stream);
         CK(cudaEventRecord(e[2], L.stream));
-        launch_pass2(R, S, p, mems, L.stream);
+        if (out.fmt == 2 && mems && p.max_len > 0xFFFFull) throw BadBatch("packed MEM records need reads shorter than 65536 bases");
+        launch_pass2(R, S, p, mode, L.stream, out.min_len);
         CK(cudaEventRecord(e[3], L.stream));
         if (mems) {
-            launch_compact(S, p, rec_bytes == 4, L.stream);
+            launch_compact(S, p, out.fmt, L.stream);
             CK(cudaEventRecord(e[4], L.stream));
         } else {
             CK(cudaEventRecord(e[4], L.stream));
@@ -577,18 +639,15 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
             g_launches++;
         }
         const bool last = p.first + p.n == r1;
+        DevBuf* const chunk_col[3] = {&S.mem_pos, &S.mem_len, &S.mem_ref};
         if (rv) {
             CK(cudaMemcpyAsync(R.shard_off.as<uint64_t>() + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToDevice, L.stream));
-            if (k) {
-                CK(cudaMemcpyAsync(R.shard_pos.as<char>() + rec_total * rec_bytes, S.mem_pos.p, k * rec_bytes, cudaMemcpyDeviceToDevice, L.stream));
-                CK(cudaMemcpyAsync(R.shard_len.as<char>() + rec_total * rec_bytes, S.mem_len.p, k * rec_bytes, cudaMemcpyDeviceToDevice, L.stream));
-            }
+            for (int q = 0; q < out.ncol && k; ++q)
+                CK(cudaMemcpyAsync(shard_col[q]->as<char>() + rec_total * out.width[q], chunk_col[q]->p, k * out.width[q], cudaMemcpyDeviceToDevice, L.stream));
         } else {
             CK(cudaMemcpyAsync(rec_off + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
-            if (rec_total + k <= rec_cap && k) {
-                CK(cudaMemcpyAsync((char*)rec_pos + rec_total * rec_bytes, S.mem_pos.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
-                CK(cudaMemcpyAsync((char*)rec_len + rec_total * rec_bytes, S.mem_len.p, k * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
-            }
+            for (int q = 0; q < out.ncol && k && rec_total + k <= rec_cap; ++q)
+                CK(cudaMemcpyAsync((char*)out.col[q] + rec_total * out.width[q], chunk_col[q]->p, k * out.width[q], cudaMemcpyDeviceToHost, L.stream));
         }
         CK(cudaEventRecord(e[5], L.stream));
         rec_total += k;
@@ -642,10 +701,8 @@ void run_shard(moni_gpu_index* idx, Replica& R, bool mems, const char* seqs, con
             g_launches++;
         }
         CK(cudaMemcpyAsync(rec_off + r0, R.shard_off.p, (nr + (last_shard ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
-        if (gbase + rec_total <= rec_cap && rec_total) {
-            CK(cudaMemcpyAsync((char*)rec_pos + gbase * rec_bytes, R.shard_pos.p, rec_total * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
-            CK(cudaMemcpyAsync((char*)rec_len + gbase * rec_bytes, R.shard_len.p, rec_total * rec_bytes, cudaMemcpyDeviceToHost, L.stream));
-        }
+        for (int q = 0; q < out.ncol && rec_total && gbase + rec_total <= rec_cap; ++q)
+            CK(cudaMemcpyAsync((char*)out.col[q] + gbase * out.width[q], shard_col[q]->p, rec_total * out.width[q], cudaMemcpyDeviceToHost, L.stream));
         CK(cudaEventRecord(e[1], L.stream));
         CK(cudaStreamSynchronize(L.stream));
         const double ms = ev_ms(e[0], e[1]);
@@ -699,7 +756,7 @@ void collect_times(moni_gpu_index* idx) {
 extern "C" {
 
 const char* moni_gpu_last_error(void) { return g_err.c_str(); }
-const char* moni_gpu_version(void) { return "moni-gpu 0.2 (sm_100a)"; }
+const char* moni_gpu_version(void) { return "moni-gpu 0.3 (sm_100a)"; }
 uint64_t moni_gpu_launch_count(void) { return g_launches.load(); }
 
 int moni_gpu_set_option(const char* key, const char* value) {
@@ -752,7 +809,13 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             eo.max_scan = idx->opt.max_scan;
             eo.verbose = idx->opt.verbose;
             FlatRlbwt bwt;
-            read_thrbv_ms(std::string(prefix) + ".thrbv.ms", bwt);
+            // `ms`/`mems` index first; else the `moni align` index (same query structures + Phi, include/ms/moni.hpp:384-387,
+            // include/aligner/moni_lcp.hpp:200-203)
+            const char* exts[3] = {".thrbv.ms", ".thrbv.full.ms", ".thrbv.full.lcp.ms"};
+            int which = 0;
+            for (int k = 0; k < 3; ++k)
+                if (access((std::string(prefix) + exts[k]).c_str(), R_OK) == 0) { which = k; break; }
+            read_thrbv_ms(std::string(prefix) + exts[which], bwt, which != 0);
             build_move_table(bwt, eo, img);
         }
         {
@@ -825,7 +888,7 @@ int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, 
         std::vector<int> rc(G, 0);
         auto work = [&](int g) {
             rc[g] = guarded([&]() -> int {
-                run_shard(idx, *idx->reps[g], false, seqs, offsets, cut[g], cut[g + 1], pointers, lengths, nullptr, nullptr, nullptr, 0, nullptr);
+                run_shard(idx, *idx->reps[g], 0, seqs, offsets, cut[g], cut[g + 1], pointers, lengths, RecOut(), nullptr);
                 return 0;
             });
             if (rc[g]) errs[g] = g_err;
@@ -842,20 +905,20 @@ int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, 
     });
 }
 
-static int mems_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
-                     void* mem_pos, void* mem_len, uint64_t mem_capacity, int rec_bytes) {
+static int mems_impl(moni_gpu_index* idx, int mode, const char* seqs, const uint64_t* offsets, uint64_t n_reads, RecOut out) {
+    uint64_t* const mem_offsets = out.off;
     if (!idx || !offsets || !mem_offsets) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
     if (n_reads == 0) { mem_offsets[0] = 0; return 0; }
     if (!seqs && offsets[n_reads] != offsets[0]) { g_err = "null seqs"; return MONI_GPU_EINVAL; }
-    if ((!mem_pos || !mem_len) && mem_capacity) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    for (int q = 0; q < out.ncol; ++q)
+        if (!out.col[q] && out.cap) { g_err = "null output"; return MONI_GPU_EINVAL; }
     return guarded([&]() -> int {
         const int G = (int)idx->reps.size();
         std::vector<uint64_t> cut;
         split_by_bases(offsets, n_reads, G, cut);
         uint64_t needed = 0;
         if (G == 1) {
-            run_shard(idx, *idx->reps[0], true, seqs, offsets, 0, n_reads, nullptr, nullptr, mem_offsets, mem_pos, mem_len, mem_capacity, &needed,
-                      rec_bytes);
+            run_shard(idx, *idx->reps[0], mode, seqs, offsets, 0, n_reads, nullptr, nullptr, out, &needed);
             collect_times(idx);
         } else {
             // every shard keeps its records on its GPU until the totals of the shards before it are known, then copies
@@ -870,8 +933,7 @@ static int mems_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offs
                     bool published = false;
                     rc[g] = guarded([&]() -> int {
                         if (cut[g + 1] > cut[g]) {
-                            run_shard(idx, *idx->reps[g], true, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, mem_offsets, mem_pos, mem_len,
-                                      mem_capacity, &k[g], rec_bytes, &rv, g);
+                            run_shard(idx, *idx->reps[g], mode, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, out, &k[g], &rv, g);
                             published = true;
                         }
                         return 0;
@@ -885,7 +947,7 @@ static int mems_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offs
             for (int g = 0; g < G; ++g) needed += k[g];
             mem_offsets[n_reads] = needed;      // also covers trailing shards without reads
         }
-        if (needed > mem_capacity) {
+        if (needed > out.cap) {
             g_err = "mem_capacity too small: " + std::to_string(needed) + " records needed";
             return MONI_GPU_ENOMEM;
         }
@@ -893,14 +955,38 @@ static int mems_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offs
     });
 }
 
+static RecOut rec_out(uint64_t* off, void* a, int wa, void* b, int wb, void* c, int wc, uint64_t cap, int fmt, uint32_t min_len = 0) {
+    RecOut o;
+    o.off = off;
+    o.col[0] = a; o.width[0] = wa;
+    o.col[1] = b; o.width[1] = wb;
+    o.col[2] = c; o.width[2] = wc;
+    o.ncol = wc ? 3 : (wb ? 2 : 1);
+    o.cap = cap;
+    o.fmt = fmt;
+    o.min_len = min_len;
+    return o;
+}
+
 int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
                   uint64_t* mem_pos, uint64_t* mem_len, uint64_t mem_capacity) {
-    return mems_impl(idx, seqs, offsets, n_reads, mem_offsets, mem_pos, mem_len, mem_capacity, 8);
+    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_pos, 8, mem_len, 8, nullptr, 0, mem_capacity, 8));
 }
 
 int moni_gpu_mems32(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
                     uint32_t* mem_pos, uint32_t* mem_len, uint64_t mem_capacity) {
-    return mems_impl(idx, seqs, offsets, n_reads, mem_offsets, mem_pos, mem_len, mem_capacity, 4);
+    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_pos, 4, mem_len, 4, nullptr, 0, mem_capacity, 4));
+}
+
+int moni_gpu_mems_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
+                         uint32_t* mem_rec, uint64_t mem_capacity) {
+    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_rec, 4, nullptr, 0, nullptr, 0, mem_capacity, 2));
+}
+
+int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t min_len,
+                   uint64_t* seed_offsets, uint64_t* seed_ref, uint32_t* seed_qpos, uint32_t* seed_len, uint64_t seed_capacity) {
+    const uint32_t ml = min_len > 0x7FFFFFFFull ? 0x7FFFFFFFu : (uint32_t)min_len;     // reads are shorter than 2^31
+    return mems_impl(idx, 2, seqs, offsets, n_reads, rec_out(seed_offsets, seed_qpos, 4, seed_len, 4, seed_ref, 8, seed_capacity, 12, ml));
 }
 
 int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset) {
@@ -967,9 +1053,9 @@ int moni_gpu_batch_run(moni_gpu_batch* b, int what, float kernel_ms[3]) {
         launch_prepare(b->s, b->plan, L.stream);
         launch_pass1(R, b->s, b->plan, L.stream);
         CK(cudaEventRecord(e[1], L.stream));
-        launch_pass2(R, b->s, b->plan, what == 2, L.stream);
+        launch_pass2(R, b->s, b->plan, what == 2 ? 1 : 0, L.stream);
         CK(cudaEventRecord(e[2], L.stream));
-        if (what == 2) launch_compact(b->s, b->plan, false, L.stream);
+        if (what == 2) launch_compact(b->s, b->plan, 8, L.stream);
         CK(cudaEventRecord(e[3], L.stream));
         CK(cudaStreamSynchronize(L.stream));
         b->last = what;

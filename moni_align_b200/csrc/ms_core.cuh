@@ -8,6 +8,7 @@
 //   pass 1  ms_pointers<>::_query                      include/ms/ms_pointers.hpp:455-511
 //   pass 2  ms_c::matching_statistics length loop      src/matching_statistics.cpp:246-255
 //           mems_c::maxrimal_exact_matches MEM rule    src/mems.cpp:247-259
+//           seed_finder::find_mems seed rule           include/aligner/seed_finder.hpp:126-166
 #pragma once
 #include <cstdint>
 
@@ -228,6 +229,7 @@ MONI_HD uint32_t first_diff_byte(uint64_t x) {      // x != 0
 struct LenState {
     enum : uint32_t { ADVANCE = 0, DESCEND = 1, COMPARE = 2 };
     uint32_t i = 0, l = 0, prev_len = 0, n_mems = 0, mode = ADVANCE;
+    uint32_t n_Ns = 0;              // seeds only: length of the run of 'N' that ends the characters compared so far
     uint32_t ref = 0;               // DESCEND: current grammar reference
     uint64_t pos = 0, prev_ptr = 0;
     uint64_t nxt = 0;               // pointer of query offset i, loaded one step ahead (valid once primed)
@@ -240,10 +242,14 @@ struct LenState {
 // One micro-step of read `seq[0..m)`.  The pointer of query offset i is ptr[i * ptr_stride] (the kernels
 // keep pointers warp-transposed: stride -32; +1 on a plain array).  When a query offset is finished,
 // writes ptr_out[i] / len[i] (if not null) and the MEM record (packed (i << 32) | len, if mem_out != null).
+// SEEDS: the record rule is seed_finder::find_mems' (include/aligner/seed_finder.hpp:148): l >= pl and n_Ns < l and
+// l >= min_len, where n_Ns counts the consecutive 'N' at the end of the characters matched so far (:139-143; it is
+// only touched when a character is compared and matches); ref_out[k] receives the record's text position pointers[i].
 // Call while st.i < m.  m < 2^31.
-template <typename LenT>
+template <typename LenT, bool SEEDS = false>
 MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, const uint64_t* ptr, int64_t ptr_stride,
-                          uint64_t* ptr_out, LenT* len, uint64_t* mem_out, LenState& st, Counters* cnt) {
+                          uint64_t* ptr_out, LenT* len, uint64_t* mem_out, LenState& st, Counters* cnt,
+                          uint64_t* ref_out = nullptr, uint32_t min_len = 0) {
     const uint64_t N = v.hdr.text_len;
     bool done = false;
     if (st.mode == LenState::ADVANCE) {
@@ -288,10 +294,26 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
         uint32_t lim = m - e;
         if (lim > 8u) lim = 8u;
         if ((uint64_t)lim > st.rem) lim = (uint32_t)st.rem;
-        const uint64_t x = load8(st.t) ^ load8(seq + e);
+        const uint64_t rd = load8(seq + e);
+        const uint64_t x = load8(st.t) ^ rd;
         uint32_t k = x ? first_diff_byte(x) : 8u;
         const bool mismatch = k < lim;
         if (!mismatch) k = lim;
+        if (SEEDS && k) {
+            // bit 7 of every byte of the read word that is NOT 'N', restricted to the k matched bytes
+            const uint64_t z = rd ^ 0x4E4E4E4E4E4E4E4Eull;
+            uint64_t nz = ((((z & 0x7F7F7F7F7F7F7F7Full) + 0x7F7F7F7F7F7F7F7Full) | z) & 0x8080808080808080ull);
+            if (k < 8u) nz &= (1ull << (8u * k)) - 1ull;
+            if (nz == 0) st.n_Ns += k;                               // all k are 'N': the run grows
+            else {
+#if defined(__CUDA_ARCH__)
+                const uint32_t h = (uint32_t)(63 - __clzll((long long)nz)) >> 3;
+#else
+                const uint32_t h = (uint32_t)(63 - __builtin_clzll(nz)) >> 3;
+#endif
+                st.n_Ns = k - 1u - h;                                // 'N's after the last other character
+            }
+        }
         if (cnt) cnt->chars += k + (mismatch ? 1u : 0u);
         st.l += k;
         st.t += k;
@@ -313,8 +335,11 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
         const uint32_t i = st.i;
         if (ptr_out) ptr_out[i] = st.pos;
         if (len) len[i] = (LenT)st.l;
-        if (i == 0 || st.l >= st.prev_len) {                     // src/mems.cpp:257-258
+        const bool emit = SEEDS ? (st.l >= st.prev_len && st.n_Ns < st.l && st.l >= min_len)    // seed_finder.hpp:148 (pl starts at 0)
+                                : (i == 0 || st.l >= st.prev_len);                               // src/mems.cpp:257-258
+        if (emit) {
             if (mem_out) mem_out[st.n_mems] = ((uint64_t)i << 32) | st.l;
+            if (SEEDS && ref_out) ref_out[st.n_mems] = st.pos;
             ++st.n_mems;
         }
         st.prev_len = st.l;
@@ -326,11 +351,13 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
 }
 
 // The whole length loop of one read (a single lane of the state machine).  Returns the number of MEM records.
-template <typename LenT>
+template <typename LenT, bool SEEDS = false>
 MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, int64_t ptr_stride,
-                              uint64_t* ptr_out, LenT* len, uint64_t* mem_out, Counters* cnt) {
+                              uint64_t* ptr_out, LenT* len, uint64_t* mem_out, Counters* cnt, uint64_t* ref_out = nullptr,
+                              uint32_t min_len = 0) {
     LenState st;
-    while (st.i < (uint32_t)m) lengths_step(v, seq, (uint32_t)m, ptr, ptr_stride, ptr_out, len, mem_out, st, cnt);
+    while (st.i < (uint32_t)m)
+        lengths_step<LenT, SEEDS>(v, seq, (uint32_t)m, ptr, ptr_stride, ptr_out, len, mem_out, st, cnt, ref_out, min_len);
     return st.n_mems;
 }
 

@@ -20,6 +20,8 @@
  *   PlainSlp::charAt                                   thirdparty/ShapedSlp/PlainSlp.hpp:101-126
  *   ms_c::matching_statistics length loop              src/matching_statistics.cpp:246-255
  *   mems_c::maxrimal_exact_matches                     src/mems.cpp:247-259
+ *   seed_finder::find_mems                             include/aligner/seed_finder.hpp:126-166  (pinned against
+ *       oracle/_ref/bin/ref_seeds, the reference header driven by oracle/ref_seeds_harness.cpp: tests/golden/*.seeds*)
  */
 #include <stdint.h>
 #include <stdlib.h>
@@ -228,4 +230,46 @@ void oracle_mems_batch(oracle_index* ix, const u8* seqs, const u64* offsets, u64
     }
     mem_offsets[n_reads] = total;
     free(ptr); free(len); free(rec);
+}
+
+/* seed_finder<slp_t, ms_t>::find_mems (include/aligner/seed_finder.hpp:126-166), statement by statement: the same
+ * pointers (ms.query, include/ms/moni.hpp:568-626 == ms_pointers.hpp:455-511), the same extension loop with the
+ * trailing-N counter (:139-143), and the record rule of :148.  rec receives (pointers[i], l, i) triples. */
+void oracle_find_mems(oracle_index* ix, const u8* seq, u64 m, const u64* pointers, u64 min_len, u64* rec, u64* n_rec) {
+    const u64 n = ix->text_len;                                         /* seed_finder::n = ra.getLen() (:91) */
+    u64 l = 0, pl = 0, n_Ns = 0, q = 0;
+    u64 prev_pos_plus_one = n + 1;
+    for (u64 i = 0; i < m; ++i) {
+        const u64 pos = pointers[i];
+        while (pos != prev_pos_plus_one && (i + l) < m && (pos + l) < n && seq[i + l] == char_at(ix, pos + l, NULL)) {
+            if (seq[i + l] == 'N') n_Ns++;
+            else n_Ns = 0;
+            ++l;
+        }
+        if (l >= pl && n_Ns < l && l >= min_len) { rec[3 * q] = pointers[i]; rec[3 * q + 1] = l; rec[3 * q + 2] = i; ++q; }
+        pl = l;
+        l = (l == 0 ? 0 : (l - 1));
+        prev_pos_plus_one = pos + 1;
+    }
+    *n_rec = q;
+}
+
+/* seed_ref/seed_qpos/seed_len need offsets[n_reads] entries (upper bound); seed_offsets has n_reads + 1 entries. */
+void oracle_seeds_batch(oracle_index* ix, const u8* seqs, const u64* offsets, u64 n_reads, u64 min_len, u64* seed_offsets,
+                        u64* seed_ref, u64* seed_qpos, u64* seed_len) {
+    u64 total = 0, cap = 0;
+    for (u64 r = 0; r < n_reads; ++r) { u64 m = offsets[r + 1] - offsets[r]; if (m > cap) cap = m; }
+    u64* ptr = (u64*)malloc((cap + 1) * sizeof(u64));
+    u64* rec = (u64*)malloc((3 * cap + 3) * sizeof(u64));
+    for (u64 r = 0; r < n_reads; ++r) {
+        const u64 o = offsets[r], m = offsets[r + 1] - o;
+        u64 q = 0;
+        oracle_ms_pointers(ix, seqs + o, m, ptr);
+        oracle_find_mems(ix, seqs + o, m, ptr, min_len, rec, &q);
+        seed_offsets[r] = total;
+        for (u64 t = 0; t < q; ++t) { seed_ref[total + t] = rec[3 * t]; seed_len[total + t] = rec[3 * t + 1]; seed_qpos[total + t] = rec[3 * t + 2]; }
+        total += q;
+    }
+    seed_offsets[n_reads] = total;
+    free(ptr); free(rec);
 }

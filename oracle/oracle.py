@@ -155,7 +155,9 @@ def _wt_huff(c: _Cur) -> np.ndarray:
     return decode(0, size) if size else np.zeros(0, dtype=np.uint8)
 
 
-def read_thrbv_ms(path: str) -> dict:
+def read_thrbv_ms(path: str, full: bool = False) -> dict:
+    """`full`: the `moni align` index (.thrbv.full.ms, include/ms/moni.hpp:359-382; .thrbv.full.lcp.ms adds a trailing
+    slcp vector, include/aligner/moni_lcp.hpp:208-225): same members with the Phi structures in between."""
     c = _Cur(path)
     d: dict = {"terminator_position": c.u64()}
     if c.u64() != 256:
@@ -181,12 +183,20 @@ def read_thrbv_ms(path: str) -> dict:
     if int(starts[-1]) != n:
         raise ValueError("run lengths do not sum to n")
     d.update(heads=heads, lens=lens, starts=starts, count=count)
+    if full:
+        d["pred"] = _sparse_sd(c)[1]
+        d["pred_to_run"] = _unpack(*_int_vector(c)).astype(np.uint64)
     d["samples_last"] = _unpack(*_int_vector(c)).astype(np.uint64)
     thr = []
     for s in range(256):
         thr.append(_sparse_sd(c)[1])
     d["thr"] = thr
+    if full:
+        d["pred_start"] = _sparse_sd(c)[1]
+        d["pred_start_to_run"] = _unpack(*_int_vector(c)).astype(np.uint64)
     d["samples_start"] = _unpack(*_int_vector(c)).astype(np.uint64)
+    if full and c.off != c.buf.shape[0]:
+        d["slcp"] = _unpack(*_int_vector(c)).astype(np.uint64)
     if c.off != c.buf.shape[0]:
         raise ValueError(f"{path}: {c.buf.shape[0] - c.off} trailing bytes")
     return d
@@ -225,7 +235,10 @@ class OracleIndex:
         L.oracle_counters.argtypes = [ctypes.c_void_p, u64p, ctypes.c_int]
         L.oracle_char_at.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
         L.oracle_char_at.restype = ctypes.c_uint8
-        self.bwt = read_thrbv_ms(prefix + ".thrbv.ms")
+        L.oracle_seeds_batch.argtypes = [ctypes.c_void_p, u8p, u64p, ctypes.c_uint64, ctypes.c_uint64, u64p, u64p, u64p, u64p]
+        import os as _os
+        ext = next((e for e in (".thrbv.ms", ".thrbv.full.ms", ".thrbv.full.lcp.ms") if _os.path.exists(prefix + e)), ".thrbv.ms")
+        self.bwt = read_thrbv_ms(prefix + ext, full=ext != ".thrbv.ms")
         self.slp = read_plain_slp(prefix + ".plain.slp")
         b, s = self.bwt, self.slp
         self._keep = dict(
@@ -284,6 +297,20 @@ class OracleIndex:
         k = int(mo[-1])
         return mo, mp[:k], ml[:k]
 
+    def seeds(self, seqs: np.ndarray, offsets: np.ndarray, min_len: int = 0):
+        """(seed_offsets, seed_ref, seed_qpos, seed_len): seed_finder::find_mems for every read."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        nr = offsets.shape[0] - 1
+        so = np.zeros(nr + 1, dtype=np.uint64)
+        cols = [np.zeros(max(total, 1), dtype=np.uint64) for _ in range(3)]
+        sq = seqs if seqs.shape[0] else np.zeros(1, dtype=np.uint8)
+        self.lib.oracle_seeds_batch(self.h, _p(sq, ctypes.c_uint8), _p(offsets, ctypes.c_uint64), nr, int(min_len),
+                                    _p(so, ctypes.c_uint64), *[_p(c, ctypes.c_uint64) for c in cols])
+        k = int(so[-1])
+        return so, cols[0][:k], cols[1][:k], cols[2][:k]
+
     def counters(self, reset: bool = True) -> dict:
         out = np.zeros(5, dtype=np.uint64)
         self.lib.oracle_counters(self.h, _p(out, ctypes.c_uint64), 1 if reset else 0)
@@ -310,4 +337,13 @@ def format_mems(names, mem_offsets, mem_pos, mem_len) -> bytes:
     for r, nm in enumerate(names):
         a, b = int(mem_offsets[r]), int(mem_offsets[r + 1])
         out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d) " % (int(mem_pos[t]), int(mem_len[t])) for t in range(a, b)) + b"\n")
+    return b"".join(out)
+
+
+def format_seeds(names, seed_offsets, seed_ref, seed_len, seed_qpos) -> bytes:
+    """The text oracle/ref_seeds_harness.cpp prints for the reference's find_mems: '(' pos ',' len ',' idx ') ' tokens."""
+    out = []
+    for r, nm in enumerate(names):
+        a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
+        out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d,%d) " % (int(seed_ref[t]), int(seed_len[t]), int(seed_qpos[t])) for t in range(a, b)) + b"\n")
     return b"".join(out)

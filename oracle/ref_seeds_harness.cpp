@@ -1,0 +1,41 @@
+// TEST INFRASTRUCTURE -- drives the UNMODIFIED reference seed_finder<plain_slp_t, ms_pointers<>>::find_mems
+// (include/aligner/seed_finder.hpp:126-166 of the reference checkout) over a FASTQ and prints, per read,
+//     >name\n(pos,len,idx) (pos,len,idx) ...\n
+// where pos = pointers[i] (text position), len = seed length, idx = query offset i.  Built by oracle/build_ref.sh
+// into oracle/_ref/bin/ref_seeds; the reference headers are compiled where they lie, nothing is copied.
+// The only thing replaced is the lift-over index member (class liftidx, levioSAM + htslib), which find_mems never
+// touches: oracle/build_ref.sh generates a three-method stand-in under oracle/_ref/shim/liftstub/liftidx.hpp that
+// shadows include/aligner/liftidx.hpp on the include path.
+//
+// usage: ref_seeds <index-prefix> <reads.fq> <min_len> <out.seeds>
+//   needs <prefix>.thrbv.full.ms (reference rlebwt_ms_full_build -n), <prefix>.plain.slp and an (empty) <prefix>.ldx
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+
+#include <seed_finder.hpp>
+
+#include <zlib.h>
+// kseq's KSEQ_INIT(gzFile, gzread) is already instantiated by the reference headers (seqidx.hpp / common.hpp)
+
+int main(int argc, char** argv) {
+    if (argc != 5) { fprintf(stderr, "usage: ref_seeds prefix reads.fq min_len out\n"); return 2; }
+    const size_t min_len = (size_t)atoll(argv[3]);
+    seed_finder<plain_slp_t, ms_pointers<>> sf(argv[1], min_len, false, 5000);
+    gzFile fp = gzopen(argv[2], "r");
+    if (!fp) { fprintf(stderr, "cannot open %s\n", argv[2]); return 1; }
+    FILE* out = fopen(argv[4], "w");
+    if (!out) { fprintf(stderr, "cannot open %s\n", argv[4]); return 1; }
+    kseq_t* seq = kseq_init(fp);
+    while (kseq_read(seq) >= 0) {
+        std::vector<mem_t> mems;
+        sf.find_mems(seq, mems);
+        fprintf(out, ">%s\n", seq->name.s);
+        for (const mem_t& m : mems) fprintf(out, "(%zu,%zu,%zu) ", m.pos, m.len, m.idx);
+        fprintf(out, "\n");
+    }
+    kseq_destroy(seq);
+    gzclose(fp);
+    fclose(out);
+    return 0;
+}

@@ -65,7 +65,23 @@ def run_host_sim(exe, prefix, flat, offs, tmpdir, extra=()):
     mo = raw[2 * total:2 * total + nr + 1]
     k = int(mo[-1])
     base = 2 * total + nr + 1
-    return p, l, mo, raw[base:base + k], raw[base + k:base + 2 * k], raw[base + 2 * k:base + 2 * k + 8]
+    res = (p, l, mo, raw[base:base + k], raw[base + k:base + 2 * k], raw[base + 2 * k:base + 2 * k + 8])
+    if len(extra) < 3:
+        return res
+    at = base + 2 * k + 8              # seeds: offsets, ref, len, qpos
+    so = raw[at:at + nr + 1]
+    ks = int(so[-1]) if nr >= 0 and so.shape[0] else 0
+    at += nr + 1
+    return res + (so, raw[at:at + ks], raw[at + ks:at + 2 * ks], raw[at + 2 * ks:at + 3 * ks])
+
+
+def full_only_prefix(case, tmpdir):
+    """A prefix under tmpdir that holds ONLY the `moni align` index of a golden case (+ the grammar)."""
+    import shutil
+    pre = os.path.join(str(tmpdir), case + "_full.fa")
+    shutil.copy(os.path.join(GOLDEN, case + ".fa.thrbv.full.ms"), pre + ".thrbv.full.ms")
+    shutil.copy(os.path.join(GOLDEN, case + ".fa.plain.slp"), pre + ".plain.slp")
+    return pre
 
 
 @pytest.fixture(scope="session")

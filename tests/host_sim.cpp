@@ -2,9 +2,11 @@
 // and runs them over the host copy of the HBM image, so the exporter and the kernel arithmetic can
 // be checked against the oracle on a machine without a GPU.  Never linked into the library.
 //
-// usage: host_sim <index-prefix> <batch.bin> <out.bin> [leaf_len] [max_scan]
+// usage: host_sim <index-prefix> <batch.bin> <out.bin> [leaf_len] [max_scan] [seed_min_len]
 //   batch.bin : u64 n_reads, u64 offsets[n_reads+1], u8 seqs[offsets[n_reads]]
 //   out.bin   : u64 ptr[total], u64 len[total], u64 mem_offsets[n_reads+1], u64 mem_pos[k], u64 mem_len[k], u64 counters[8]
+//               and, when seed_min_len is given: u64 seed_offsets[n_reads+1], u64 seed_ref[s], u64 seed_len[s], u64 seed_qpos[s]
+// If <prefix>.thrbv.ms does not exist, <prefix>.thrbv.full.ms (the `moni align` index) is read.
 #include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
@@ -20,12 +22,23 @@ int main(int argc, char** argv) {
     try {
         FlatRlbwt bwt;
         FlatSlp slp;
-        read_thrbv_ms(std::string(argv[1]) + ".thrbv.ms", bwt);
+        {
+            const std::string plain = std::string(argv[1]) + ".thrbv.ms", full = std::string(argv[1]) + ".thrbv.full.ms";
+            FILE* probe = fopen(plain.c_str(), "rb");
+            FILE* probe2 = probe ? nullptr : fopen(full.c_str(), "rb");
+            if (probe) fclose(probe);
+            if (probe2) fclose(probe2);
+            if (!probe && probe2) read_thrbv_ms(full, bwt, true);
+            else read_thrbv_ms(plain, bwt);
+        }
         read_plain_slp(std::string(argv[1]) + ".plain.slp", slp);
         ExportOptions opt;
         opt.verbose = true;
         if (argc > 4) opt.leaf_len = (uint64_t)atoll(argv[4]);
         if (argc > 5) opt.max_scan = (uint32_t)atoi(argv[5]);
+        const bool want_seeds = argc > 6;
+        const uint32_t seed_min_len = want_seeds ? (uint32_t)atoll(argv[6]) : 0;
+        std::vector<uint64_t> so, s_ref, s_len, s_qpos;
         HostImage img;
         build_move_table(bwt, opt, img);
         build_grammar_table(slp, opt, img);
@@ -60,7 +73,15 @@ int main(int argc, char** argv) {
             const uint32_t k = lengths_read(v, seqs.data() + o, m, ptr.data() + o, 1, (uint64_t*)nullptr, len.data() + o, rec.data(), &cnt);
             mo[r] = mems.size();
             mems.insert(mems.end(), rec.begin(), rec.begin() + k);
+            if (want_seeds) {
+                std::vector<uint64_t> ref(m + 1);
+                const uint32_t ks = lengths_read<uint32_t, true>(v, seqs.data() + o, m, ptr.data() + o, 1, (uint64_t*)nullptr, (uint32_t*)nullptr,
+                                                                 rec.data(), nullptr, ref.data(), seed_min_len);
+                so.push_back(s_ref.size());
+                for (uint32_t t = 0; t < ks; ++t) { s_ref.push_back(ref[t]); s_len.push_back(rec[t] & 0xFFFFFFFFu); s_qpos.push_back(rec[t] >> 32); }
+            }
         }
+        if (want_seeds) so.push_back(s_ref.size());
         mo[nr] = mems.size();
         for (uint64_t i = 0; i < total; ++i) len64[i] = len[i];
         std::vector<uint64_t> mp(mems.size() + 1), ml(mems.size() + 1);
@@ -74,6 +95,12 @@ int main(int argc, char** argv) {
         fwrite(ml.data(), 8, mems.size(), f);
         unsigned long long c8[8] = {cnt.bases, cnt.jumps, cnt.restarts, cnt.restart_depth, cnt.chars, cnt.scan_rows, cnt.general_steps, cnt.descents};
         fwrite(c8, 8, 8, f);
+        if (want_seeds) {
+            fwrite(so.data(), 8, so.size(), f);
+            fwrite(s_ref.data(), 8, s_ref.size(), f);
+            fwrite(s_len.data(), 8, s_len.size(), f);
+            fwrite(s_qpos.data(), 8, s_qpos.size(), f);
+        }
         fclose(f);
         fprintf(stderr, "host_sim: bases %llu jumps %llu restarts %llu depth %llu chars %llu scan_rows %llu general %llu descents %llu; image %.1f MB\n",
                 c8[0], c8[1], c8[2], c8[3], c8[4], c8[5], c8[6], c8[7], (double)img.bytes() / 1e6);

@@ -283,3 +283,88 @@ def test_cli_reads_gzip_and_fasta(tmp_path):
     r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", "mems"), pre + ".fa", "-p", str(fa), "-o", out], capture_output=True)
     assert r.returncode == 0, r.stderr
     assert open(out + ".mems", "rb").read() == open(pre + ".mems", "rb").read()
+
+
+# ------------------------------------------------------------------------------ packed records, `moni align` front end
+def test_mems_packed_equals_mems(m, indexes):
+    """moni_gpu_mems_packed: the same records as (query offset << 16) | length; refuses reads of 65536 bases or more."""
+    for case in CASES:
+        names, seqs = read_fastq(os.path.join(GOLDEN, case + ".fq"))
+        flat, offs = pack(seqs)
+        a = indexes[case].maxrimal_exact_matches(flat, offs)
+        mo, rec = indexes[case].maxrimal_exact_matches_packed(flat, offs)
+        assert rec.dtype == np.uint32
+        assert np.array_equal(a[0], mo) and np.array_equal(a[1], rec >> 16) and np.array_equal(a[2], rec & 0xFFFF)
+    three = m.MoniIndex(os.path.join(GOLDEN, "pan4.fa"), gpus=[0, 0, 0])
+    names, seqs = read_fastq(os.path.join(GOLDEN, "pan4.fq"))
+    flat, offs = pack(seqs)
+    mo1, rec1 = indexes["pan4"].maxrimal_exact_matches_packed(flat, offs)
+    mo3, rec3 = three.maxrimal_exact_matches_packed(flat, offs)
+    assert np.array_equal(mo1, mo3) and np.array_equal(rec1, rec3)
+    long_flat, long_offs = pack([b"ACGT" * 16384, b"ACGTTG"])
+    with pytest.raises(m.MoniGpuError) as e:
+        indexes["pan4"].maxrimal_exact_matches_packed(long_flat, long_offs)
+    assert e.value.code == -1
+    three.close()
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("min_len", [0, 25])
+def test_seeds_equal_reference_find_mems(case, min_len, m, indexes):
+    """moni_gpu_seeds == the reference's seed_finder::find_mems (tests/golden/<case>.seeds<min_len>, produced by the
+    reference header on the reference's own .thrbv.full.ms)."""
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    so, ref, qpos, ln = indexes[case].find_mems(flat, offs, min_len)
+    assert m.format_seeds(names, so, ref, ln, qpos) == open(pre + f".seeds{min_len}", "rb").read()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_align_index_file_gives_identical_results(case, m, indexes, tmp_path):
+    """A prefix that only has the `moni align` index (.thrbv.full.ms): ms, mems and seeds are the reference's."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    ix = m.MoniIndex(full_only_prefix(case, tmp_path))
+    assert (ix.n, ix.r) == (indexes[case].n, indexes[case].r)
+    ptr, ln = ix.matching_statistics(flat, offs)
+    assert m.format_ms(names, offs, ptr) == open(pre + ".pointers", "rb").read()
+    assert m.format_ms(names, offs, ln) == open(pre + ".lengths", "rb").read()
+    mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+    assert m.format_mems(names, mo, mp, ml) == open(pre + ".mems", "rb").read()
+    so, ref, qpos, sl = ix.find_mems(flat, offs, 25)
+    assert m.format_seeds(names, so, ref, sl, qpos) == open(pre + ".seeds25", "rb").read()
+    ix.close()
+
+
+def test_seeds_random_reads_chunked_and_sharded(m, oracle_mod):
+    """Seeds on N-rich random reads vs the oracle: one call, small chunks (ragged, many launches) and three replicas."""
+    import synth
+    pre = os.path.join(GOLDEN, "withN.fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = [r for r in synth.short_reads(text, 3000, 100, 41, err=0.02)]
+    reads += synth.long_reads(text, 30, 42, mean=1200, sd=500, lo=80, hi=3000)
+    rng = np.random.default_rng(9)
+    for r in reads[::3]:
+        q = int(rng.integers(0, len(r)))
+        r[q:q + int(rng.integers(1, 14))] = ord("N")
+    flat, offs = m.pack_reads(reads)
+    m.set_option("chunk_bases", 9001)
+    m.set_option("chunk_min_reads", 1)
+    try:
+        small = m.MoniIndex(pre)
+    finally:
+        m.set_option("chunk_bases", 1 << 24)
+        m.set_option("chunk_min_reads", 96 * 1024)
+    one, three = m.MoniIndex(pre), m.MoniIndex(pre, gpus=[0, 0, 0])
+    for min_len in (0, 12):
+        want = orc.seeds(flat, offs, min_len)
+        for ix in (one, small, three):
+            got = ix.find_mems(flat, offs, min_len)
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+            assert np.array_equal(got[2], want[2]) and np.array_equal(got[3], want[3])
+    for ix in (one, small, three):
+        ix.close()

@@ -105,3 +105,41 @@ def test_missing_index_file_is_an_error_not_a_crash(host_sim, tmp_path):
     (tmp_path / "b.bin").write_bytes(np.zeros(2, dtype=np.uint64).tobytes())
     r = subprocess.run([host_sim, str(tmp_path / "nope"), str(tmp_path / "b.bin"), str(tmp_path / "o.bin")], capture_output=True)
     assert r.returncode == 1 and b"cannot open" in r.stderr
+
+
+# ------------------------------------------------------------------------------ `moni align` front end
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("min_len,opts", [(0, (0, 8)), (25, (0, 8)), (0, (16, 3)), (25, (64, 4))])
+def test_seed_core_matches_reference_find_mems(case, min_len, opts, host_sim, oracle_mod, tmp_path):
+    """The kernels' per-read core in seeds mode (8-byte compares, trailing-N counter by bit tricks), on the image exported
+    from the `moni align` index file alone, == the reference's seed_finder::find_mems output."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    res = run_host_sim(host_sim, full_only_prefix(case, tmp_path), flat, offs, tmp_path, (*opts, min_len))
+    assert oracle_mod.format_ms(names, offs, res[0]) == open(pre + ".pointers", "rb").read()
+    so, ref, ln, qpos = res[6:10]
+    assert oracle_mod.format_seeds(names, so, ref, ln, qpos) == open(pre + f".seeds{min_len}", "rb").read()
+
+
+def test_seed_core_on_N_rich_reads(host_sim, oracle_mod, tmp_path):
+    """Random reads over {A,C,G,T,N} with long N stretches against the N-rich text: the trailing-N counter must agree with
+    the oracle's character-by-character restatement at every 8-byte compare boundary."""
+    pre = os.path.join(GOLDEN, "withN")
+    ix = oracle_mod.OracleIndex(pre + ".fa")
+    text = bytes(ix.char_at(i) for i in range(ix.text_len))
+    rng = np.random.default_rng(5)
+    seqs = []
+    for _ in range(200):
+        a = int(rng.integers(0, len(text) - 200))
+        s = bytearray(text[a:a + int(rng.integers(1, 200))])
+        for _ in range(int(rng.integers(0, 4))):
+            q = int(rng.integers(0, len(s)))
+            s[q:q + int(rng.integers(1, 12))] = b"N" * min(int(rng.integers(1, 12)), len(s) - q)
+        seqs.append(bytes(s))
+    flat, offs = pack(seqs)
+    for min_len in (0, 3, 20):
+        res = run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path, (0, 8, min_len))
+        so, ref, qpos, ln = ix.seeds(flat, offs, min_len)
+        assert np.array_equal(res[6], so) and np.array_equal(res[7], ref) and np.array_equal(res[8], ln) and np.array_equal(res[9], qpos)

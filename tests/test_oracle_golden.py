@@ -78,3 +78,45 @@ def test_oracle_lengths_are_true_matching_statistics(oracle_mod):
             p, l = int(ptr[int(offs[r]) + i]), int(ln[int(offs[r]) + i])
             assert text[p:p + l] == s[i:i + l]
             assert s[i:i + l + 1] not in text or i + l == len(s)
+
+
+# ---------------------------------------------------------------------------- `moni align` front end
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("min_len", [0, 25])
+def test_oracle_seeds_equal_reference_find_mems(case, min_len, oracle_mod):
+    """oracle_find_mems == the reference's seed_finder::find_mems (run through oracle/ref_seeds_harness.cpp on the
+    reference's own .thrbv.full.ms; committed as tests/golden/<case>.seeds<min_len>)."""
+    pre = os.path.join(GOLDEN, case)
+    ix = oracle_mod.OracleIndex(pre + ".fa")
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    so, ref, qpos, ln = ix.seeds(flat, offs, min_len)
+    assert oracle_mod.format_seeds(names, so, ref, ln, qpos) == open(pre + f".seeds{min_len}", "rb").read()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_full_index_file_holds_the_same_query_structures(case, oracle_mod):
+    """.thrbv.full.ms (rlebwt_ms_full_build -n) == .thrbv.ms (rlebwt_ms_build) on everything the MS query reads."""
+    pre = os.path.join(GOLDEN, case + ".fa")
+    a = oracle_mod.read_thrbv_ms(pre + ".thrbv.ms")
+    b = oracle_mod.read_thrbv_ms(pre + ".thrbv.full.ms", full=True)
+    for key in ("n", "R", "terminator_position"):
+        assert a[key] == b[key]
+    for key in ("F", "heads", "starts", "samples_start", "samples_last", "count"):
+        assert np.array_equal(a[key], b[key]), key
+    for c in range(256):
+        assert np.array_equal(a["thr"][c], b["thr"][c])
+    assert b["pred"].shape[0] == b["R"] and b["pred_start"].shape[0] == b["R"]
+
+
+def test_seed_rule_drops_all_N_matches(oracle_mod):
+    """The N filter of seed_finder.hpp:148 is exercised by the fixtures: withN has reads whose only matches are N runs."""
+    pre = os.path.join(GOLDEN, "withN")
+    ix = oracle_mod.OracleIndex(pre + ".fa")
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    so, ref, qpos, ln = ix.seeds(flat, offs, 0)
+    mo, mp, ml = ix.mems(flat, offs)
+    r = seqs.index(b"NNNNNNNNNNNNNNNNNNNN")
+    assert int(mo[r + 1] - mo[r]) > 0 and int(ml[int(mo[r])]) > 0      # `mems` reports the N match ...
+    assert int(so[r + 1] - so[r]) == 0                                  # ... the seed rule drops it
