@@ -331,6 +331,10 @@ def main():
         return out
     long_reads()
     print(json.dumps(RES))
+    bad = [k for k, v in RES.items() if isinstance(v, dict) and "error" in v]
+    if bad:
+        log("stages with errors:", bad)
+        sys.exit(1)
 
 
 if __name__ == "__main__":
