@@ -191,7 +191,8 @@ void read_wt_huff(Cursor& c, std::vector<uint8_t>& seq) {
 // `full`: the `moni align` index (include/ms/moni.hpp:359-382 / include/aligner/moni_lcp.hpp:208-225): the same members
 // in the same order with the Phi structures in between -- after the BWT: pred (sparse_sd_vector) and pred_to_run
 // (int_vector<>), after the thresholds: pred_start and pred_start_to_run -- and, in the .lcp variant, one trailing
-// int_vector<> slcp.  The matching-statistics query (moni.hpp:568-626) reads none of them; they are parsed and skipped.
+// int_vector<> slcp.  The matching-statistics query (moni.hpp:568-626) reads none of them; the Phi members are kept for
+// occurrence enumeration, slcp is parsed and skipped.
 void read_thrbv_ms(const std::string& path, FlatRlbwt& o, bool full) {
     MappedFile mf(path);
     Cursor c{mf.p, mf.size, 0, path};
@@ -243,9 +244,9 @@ void read_thrbv_ms(const std::string& path, FlatRlbwt& o, bool full) {
     per_letter.clear();
     per_letter.shrink_to_fit();
     if (full) {
-        std::vector<uint64_t> pred;
-        read_sparse_sd(c, pred, "pred");
-        if (read_int_vector(c, 0, "pred_to_run").size() != o.R || pred.size() != o.R)
+        read_sparse_sd(c, o.pred, "pred");
+        unpack(read_int_vector(c, 0, "pred_to_run"), o.pred_to_run);
+        if (o.pred_to_run.size() != o.R || o.pred.size() != o.R)
             throw std::runtime_error(path + ": Phi structures (pred) do not have R entries");
     }
     unpack(read_int_vector(c, 0, "samples_last"), o.samples_last);
@@ -255,9 +256,9 @@ void read_thrbv_ms(const std::string& path, FlatRlbwt& o, bool full) {
             if (o.thr[s][i] <= o.thr[s][i - 1]) throw std::runtime_error(path + ": thresholds not increasing");
     }
     if (full) {
-        std::vector<uint64_t> pred;
-        read_sparse_sd(c, pred, "pred_start");
-        if (read_int_vector(c, 0, "pred_start_to_run").size() != o.R || pred.size() != o.R)
+        read_sparse_sd(c, o.pred_start, "pred_start");
+        unpack(read_int_vector(c, 0, "pred_start_to_run"), o.pred_start_to_run);
+        if (o.pred_start_to_run.size() != o.R || o.pred_start.size() != o.R)
             throw std::runtime_error(path + ": Phi structures (pred_start) do not have R entries");
     }
     unpack(read_int_vector(c, 0, "samples_start"), o.samples_start);

@@ -24,6 +24,9 @@ struct FlatRlbwt {
     std::vector<uint64_t> samples_start;  // R   text position of the BWT char at the run's first row
     std::vector<uint64_t> samples_last;   // R   ... at the run's last row
     std::vector<uint64_t> thr[256];    // per letter: the stored (non-zero) threshold positions, increasing
+    // `moni align` index only (.thrbv.full[.lcp].ms): the Phi / Phi^-1 structures, else empty
+    std::vector<uint64_t> pred, pred_to_run;              // r_index::pred (set bits, increasing), pred_to_run   (R each)
+    std::vector<uint64_t> pred_start, pred_start_to_run;  // ms_pointers::pred_start, pred_start_to_run          (R each)
 };
 
 struct FlatSlp {

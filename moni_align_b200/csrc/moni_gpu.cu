@@ -145,14 +145,15 @@ __global__ void __launch_bounds__(kBlock) k_ms_pointers(ImageView v, const uint8
 }
 
 // ---- pass 2: MS lengths / MEM records / seeds --------------------------------------------------------
-// MODE 0 (ms): ptr_out[] and len_out[] (u64, laid out like seqs).  MODE 1 (mems): the read's MEM records, packed
-// (i << 32) | len, go to rec[] at the read's own offset (at most one per base) and counts[read] receives their number.
-// MODE 2 (seeds): same with seed_finder::find_mems' rule (minimum length, N filter) and rec_ref[] = pointers[i].
+// MODE 0 (ms): the length of query offset i goes to len_t[] next to its pointer (same warp-transposed place, u32), so the
+// 32 lanes of a warp write into the same lines; k_ms_untranspose then produces the caller's layout with coalesced
+// accesses on both sides.  MODE 1 (mems): the read's MEM records, packed (i << 32) | len, go to rec[] at the read's own
+// offset (at most one per base) and counts[read] receives their number.  MODE 2 (seeds): same with
+// seed_finder::find_mems' rule (minimum length, N filter) and rec_ref[] = pointers[i].
 template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
-                                                       const uint64_t* __restrict__ ptr_t, uint64_t* __restrict__ ptr_out,
-                                                       uint64_t* __restrict__ len_out, uint64_t* __restrict__ rec,
-                                                       uint32_t* __restrict__ counts, Counters* g,
+                                                       const uint64_t* __restrict__ ptr_t, uint32_t* __restrict__ len_t,
+                                                       uint64_t* __restrict__ rec, uint32_t* __restrict__ counts, Counters* g,
                                                        uint64_t* __restrict__ rec_ref, uint32_t min_len) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
     if (slot >= cm.n_reads) return;
@@ -160,13 +161,58 @@ __global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_
     const uint64_t a = __ldg(cm.offs + r);
     const uint64_t o = a - cm.base, m = __ldg(cm.offs + r + 1) - a;
     if (m == 0) { if (MODE) counts[r] = 0; return; }
-    const uint64_t* in = ptr_t + warp_base(cm, w) + lane + (m - 1) * 32u;     // query offset 0 = last step
+    const uint64_t at = warp_base(cm, w) + lane + (m - 1) * 32u;              // query offset 0 = last step
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
-    const uint32_t k = lengths_read<uint64_t, MODE == 2>(v, seqs + o, m, in, -32, MODE ? nullptr : ptr_out + o, MODE ? nullptr : len_out + o,
+    const uint32_t k = lengths_read<uint32_t, MODE == 2>(v, seqs + o, m, ptr_t + at, -32, nullptr, MODE ? nullptr : len_t + at,
                                                          MODE ? rec + o : nullptr, COUNT ? &c : nullptr,
-                                                         MODE == 2 ? rec_ref + o : nullptr, min_len);
+                                                         MODE == 2 ? rec_ref + o : nullptr, min_len, -32);
     if (MODE) counts[r] = k;
     if (COUNT) flush_counters(c, g);
+}
+
+// ms: warp-transposed (pointer, length) -> the caller's layout (u64 each, laid out like seqs).  One warp per 32 reads,
+// 32 steps at a time through shared memory: 256-byte loads along the lanes, 256-byte stores along each read.
+constexpr int kUtBlock = 64;
+__global__ void __launch_bounds__(kUtBlock) k_ms_untranspose(ChunkMap cm, const uint64_t* __restrict__ ptr_t,
+                                                             const uint32_t* __restrict__ len_t, uint64_t* __restrict__ ptr_out,
+                                                             uint64_t* __restrict__ len_out) {
+    __shared__ uint64_t tp[kUtBlock / 32][32 * 33];
+    __shared__ uint32_t tl[kUtBlock / 32][32 * 33];
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
+    if ((w << 5) >= cm.n_reads) return;                       // warp-uniform
+    uint64_t* P = tp[threadIdx.x >> 5];
+    uint32_t* Q = tl[threadIdx.x >> 5];
+    uint64_t o = 0;
+    uint32_t m = 0;
+    if (slot < cm.n_reads) {
+        const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
+        const uint64_t a = __ldg(cm.offs + r);
+        o = a - cm.base;
+        m = (uint32_t)(__ldg(cm.offs + r + 1) - a);
+    }
+    const uint32_t mw = warp_max(m);
+    const uint64_t base = warp_base(cm, w) + lane;
+    for (uint32_t t0 = 0; t0 < mw; t0 += 32) {
+        const uint32_t lim = min(32u, mw - t0);
+#pragma unroll 8
+        for (uint32_t t = 0; t < lim; ++t) {                  // entries of lanes whose read is shorter are never stored below
+            P[t * 33 + lane] = __ldg(ptr_t + base + (uint64_t)(t0 + t) * 32u);
+            Q[t * 33 + lane] = __ldg(len_t + base + (uint64_t)(t0 + t) * 32u);
+        }
+        __syncwarp();
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+            const uint64_t o_r = __shfl_sync(0xFFFFFFFFu, o, rr);
+            const uint32_t m_r = __shfl_sync(0xFFFFFFFFu, m, rr);
+            const uint32_t step = t0 + lane;
+            if (step < m_r) {
+                const uint64_t at = o_r + (m_r - 1 - step);
+                ptr_out[at] = P[lane * 33 + rr];
+                len_out[at] = Q[lane * 33 + rr];
+            }
+        }
+        __syncwarp();
+    }
 }
 
 // MEM compaction: one warp per read copies its packed records to their final place.
@@ -288,9 +334,10 @@ struct ChunkPlan {
 struct Scratch {   // device buffers of one chunk
     DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, wbase, ptr_t, out_ptr, out_len, rec, counts, moff, mem_pos, mem_len, cub;
     DevBuf rec_ref, mem_ref;     // seeds only
+    DevBuf len_t;                // ms only: lengths, warp-transposed like ptr_t
     void release() {
         for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &wbase, &ptr_t, &out_ptr, &out_len, &rec, &counts, &moff,
-                          &mem_pos, &mem_len, &cub, &rec_ref, &mem_ref})
+                          &mem_pos, &mem_len, &cub, &rec_ref, &mem_ref, &len_t})
             b->release();
     }
     void reserve(const ChunkPlan& p, bool ms, bool mems, bool seeds = false) {
@@ -302,7 +349,7 @@ struct Scratch {   // device buffers of one chunk
             keys_in.reserve(p.n * 4); keys_out.reserve(p.n * 4); vals_in.reserve(p.n * 4); perm.reserve(p.n * 4);
             wbase.reserve((p.n_warps() + 1) * 8);
         }
-        if (ms) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); }
+        if (ms) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); len_t.reserve(p.ptr_entries() * 4); }
         if (mems) {
             rec.reserve(p.bases * 8 + 16);
             counts.reserve((p.n + 1) * 4);
@@ -442,15 +489,25 @@ void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, int mode, cudaStre
     uint64_t* rec = S.rec.as<uint64_t>();
     uint32_t* cnt = S.counts.as<uint32_t>();
     if (mode == 2) {
-        if (g) k_ms_lengths<2, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, g, S.rec_ref.as<uint64_t>(), min_len);
-        else k_ms_lengths<2, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, nullptr, S.rec_ref.as<uint64_t>(), min_len);
+        if (g) k_ms_lengths<2, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, g, S.rec_ref.as<uint64_t>(), min_len);
+        else k_ms_lengths<2, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, nullptr, S.rec_ref.as<uint64_t>(), min_len);
     } else if (mode == 1) {
-        if (g) k_ms_lengths<1, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, g, nullptr, 0);
-        else k_ms_lengths<1, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, nullptr, rec, cnt, nullptr, nullptr, 0);
+        if (g) k_ms_lengths<1, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, g, nullptr, 0);
+        else k_ms_lengths<1, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, nullptr, nullptr, 0);
     } else {
-        if (g) k_ms_lengths<0, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, g, nullptr, 0);
-        else k_ms_lengths<0, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, nullptr, nullptr, 0);
+        if (g) k_ms_lengths<0, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.len_t.as<uint32_t>(), nullptr, nullptr, g, nullptr, 0);
+        else k_ms_lengths<0, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.len_t.as<uint32_t>(), nullptr, nullptr, nullptr, nullptr, 0);
     }
+    g_launches++;
+    CK(cudaGetLastError());
+}
+
+// ms: pointers and lengths from the warp-transposed buffers to the caller's layout
+void launch_untranspose(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
+    if (!p.n) return;
+    const dim3 grid((unsigned)((p.n_warps() * 32 + kUtBlock - 1) / kUtBlock));
+    k_ms_untranspose<<<grid, kUtBlock, 0, st>>>(chunk_map(S, p), S.ptr_t.as<uint64_t>(), S.len_t.as<uint32_t>(), S.out_ptr.as<uint64_t>(),
+                                                S.out_len.as<uint64_t>());
     g_launches++;
     CK(cudaGetLastError());
 }
@@ -617,6 +674,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
             launch_compact(S, p, out.fmt, L.stream);
             CK(cudaEventRecord(e[4], L.stream));
         } else {
+            launch_untranspose(S, p, L.stream);
             CK(cudaEventRecord(e[4], L.stream));
             if (p.bases) {
                 CK(cudaMemcpyAsync(pointers + p.base, S.out_ptr.p, p.bases * 8, cudaMemcpyDeviceToHost, L.stream));
@@ -804,7 +862,23 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
         std::unique_ptr<moni_gpu_index> idx(new moni_gpu_index);
         { std::lock_guard<std::mutex> lock(g_opt_mu); idx->opt = g_opt; }
         HostImage img;
-        {
+        // the two files are decoded and exported side by side (they fill disjoint members of the image)
+        std::exception_ptr slp_err;
+        std::thread slp_thread([&]() {
+            try {
+                ExportOptions eo;
+                eo.verbose = idx->opt.verbose;
+                FlatSlp slp;
+                read_plain_slp(std::string(prefix) + ".plain.slp", slp);
+                // B200 has the HBM to keep the text itself next to the move table (6 GB for a 6 Gbp pangenome): then an LCE
+                // restart is one random line instead of a root-to-leaf walk.  Larger texts keep the grammar with 128-byte leaves.
+                eo.leaf_len = idx->opt.leaf_len ? idx->opt.leaf_len : (slp.text_len <= idx->opt.text_budget ? std::max<uint64_t>(slp.text_len, 1) : 128);
+                build_grammar_table(slp, eo, img);
+            } catch (...) {
+                slp_err = std::current_exception();
+            }
+        });
+        try {
             ExportOptions eo;
             eo.max_scan = idx->opt.max_scan;
             eo.verbose = idx->opt.verbose;
@@ -817,17 +891,12 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
                 if (access((std::string(prefix) + exts[k]).c_str(), R_OK) == 0) { which = k; break; }
             read_thrbv_ms(std::string(prefix) + exts[which], bwt, which != 0);
             build_move_table(bwt, eo, img);
+        } catch (...) {
+            slp_thread.join();
+            throw;
         }
-        {
-            ExportOptions eo;
-            eo.verbose = idx->opt.verbose;
-            FlatSlp slp;
-            read_plain_slp(std::string(prefix) + ".plain.slp", slp);
-            // B200 has the HBM to keep the text itself next to the move table (6 GB for a 6 Gbp pangenome): then an LCE
-            // restart is one random line instead of a root-to-leaf walk.  Larger texts keep the grammar with 128-byte leaves.
-            eo.leaf_len = idx->opt.leaf_len ? idx->opt.leaf_len : (slp.text_len <= idx->opt.text_budget ? std::max<uint64_t>(slp.text_len, 1) : 128);
-            build_grammar_table(slp, eo, img);
-        }
+        slp_thread.join();
+        if (slp_err) std::rethrow_exception(slp_err);
         idx->hdr = img.hdr;
         idx->device_bytes = img.bytes() + sizeof(SymbolTables);
         for (int g = 0; g < n_gpus; ++g) {
@@ -1056,6 +1125,7 @@ int moni_gpu_batch_run(moni_gpu_batch* b, int what, float kernel_ms[3]) {
         launch_pass2(R, b->s, b->plan, what == 2 ? 1 : 0, L.stream);
         CK(cudaEventRecord(e[2], L.stream));
         if (what == 2) launch_compact(b->s, b->plan, 8, L.stream);
+        else launch_untranspose(b->s, b->plan, L.stream);
         CK(cudaEventRecord(e[3], L.stream));
         CK(cudaStreamSynchronize(L.stream));
         b->last = what;

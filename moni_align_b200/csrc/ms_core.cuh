@@ -241,7 +241,7 @@ struct LenState {
 
 // One micro-step of read `seq[0..m)`.  The pointer of query offset i is ptr[i * ptr_stride] (the kernels
 // keep pointers warp-transposed: stride -32; +1 on a plain array).  When a query offset is finished,
-// writes ptr_out[i] / len[i] (if not null) and the MEM record (packed (i << 32) | len, if mem_out != null).
+// writes ptr_out[i] / len[i * len_stride] (if not null) and the MEM record (packed (i << 32) | len, if mem_out != null).
 // SEEDS: the record rule is seed_finder::find_mems' (include/aligner/seed_finder.hpp:148): l >= pl and n_Ns < l and
 // l >= min_len, where n_Ns counts the consecutive 'N' at the end of the characters matched so far (:139-143; it is
 // only touched when a character is compared and matches); ref_out[k] receives the record's text position pointers[i].
@@ -249,7 +249,7 @@ struct LenState {
 template <typename LenT, bool SEEDS = false>
 MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, const uint64_t* ptr, int64_t ptr_stride,
                           uint64_t* ptr_out, LenT* len, uint64_t* mem_out, LenState& st, Counters* cnt,
-                          uint64_t* ref_out = nullptr, uint32_t min_len = 0) {
+                          uint64_t* ref_out = nullptr, uint32_t min_len = 0, int64_t len_stride = 1) {
     const uint64_t N = v.hdr.text_len;
     bool done = false;
     if (st.mode == LenState::ADVANCE) {
@@ -334,7 +334,7 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
     if (done) {
         const uint32_t i = st.i;
         if (ptr_out) ptr_out[i] = st.pos;
-        if (len) len[i] = (LenT)st.l;
+        if (len) len[(int64_t)i * len_stride] = (LenT)st.l;
         const bool emit = SEEDS ? (st.l >= st.prev_len && st.n_Ns < st.l && st.l >= min_len)    // seed_finder.hpp:148 (pl starts at 0)
                                 : (i == 0 || st.l >= st.prev_len);                               // src/mems.cpp:257-258
         if (emit) {
@@ -354,10 +354,10 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
 template <typename LenT, bool SEEDS = false>
 MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, int64_t ptr_stride,
                               uint64_t* ptr_out, LenT* len, uint64_t* mem_out, Counters* cnt, uint64_t* ref_out = nullptr,
-                              uint32_t min_len = 0) {
+                              uint32_t min_len = 0, int64_t len_stride = 1) {
     LenState st;
     while (st.i < (uint32_t)m)
-        lengths_step<LenT, SEEDS>(v, seq, (uint32_t)m, ptr, ptr_stride, ptr_out, len, mem_out, st, cnt, ref_out, min_len);
+        lengths_step<LenT, SEEDS>(v, seq, (uint32_t)m, ptr, ptr_stride, ptr_out, len, mem_out, st, cnt, ref_out, min_len, len_stride);
     return st.n_mems;
 }
 

@@ -7,7 +7,11 @@
 // touches: oracle/build_ref.sh generates a three-method stand-in under oracle/_ref/shim/liftstub/liftidx.hpp that
 // shadows include/aligner/liftidx.hpp on the include path.
 //
-// usage: ref_seeds <index-prefix> <reads.fq> <min_len> <out.seeds>
+// With a fifth argument "occs" every seed is followed by its occurrence list as the reference enumerates it with
+// seed_finder::find_MEM_occs (:239-251: the seed's own position, then Phi steps upwards and Phi^-1 steps downwards while
+// the bounded LCE reaches the seed length; no seed filtering):   (pos,len,idx:occ,occ,...)
+//
+// usage: ref_seeds <index-prefix> <reads.fq> <min_len> <out.seeds> [occs]
 //   needs <prefix>.thrbv.full.ms (reference rlebwt_ms_full_build -n), <prefix>.plain.slp and an (empty) <prefix>.ldx
 #include <cstdio>
 #include <cstdlib>
@@ -19,7 +23,8 @@
 // kseq's KSEQ_INIT(gzFile, gzread) is already instantiated by the reference headers (seqidx.hpp / common.hpp)
 
 int main(int argc, char** argv) {
-    if (argc != 5) { fprintf(stderr, "usage: ref_seeds prefix reads.fq min_len out\n"); return 2; }
+    if (argc != 5 && argc != 6) { fprintf(stderr, "usage: ref_seeds prefix reads.fq min_len out [occs]\n"); return 2; }
+    const bool with_occs = argc == 6;
     const size_t min_len = (size_t)atoll(argv[3]);
     seed_finder<plain_slp_t, ms_pointers<>> sf(argv[1], min_len, false, 5000);
     gzFile fp = gzopen(argv[2], "r");
@@ -31,7 +36,13 @@ int main(int argc, char** argv) {
         std::vector<mem_t> mems;
         sf.find_mems(seq, mems);
         fprintf(out, ">%s\n", seq->name.s);
-        for (const mem_t& m : mems) fprintf(out, "(%zu,%zu,%zu) ", m.pos, m.len, m.idx);
+        for (mem_t& m : mems) {
+            if (!with_occs) { fprintf(out, "(%zu,%zu,%zu) ", m.pos, m.len, m.idx); continue; }
+            sf.find_MEM_occs(m);
+            fprintf(out, "(%zu,%zu,%zu:", m.pos, m.len, m.idx);
+            for (size_t k = 0; k < m.occs.size(); ++k) fprintf(out, k ? ",%zu" : "%zu", m.occs[k]);
+            fprintf(out, ") ");
+        }
         fprintf(out, "\n");
     }
     kseq_destroy(seq);

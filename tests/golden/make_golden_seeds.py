@@ -7,6 +7,8 @@ For each case already under tests/golden/ (its builder intermediates .bwt.heads/
   <case>.fa.thrbv.full.ms   reference rlebwt_ms_full_build -n   (src/align/rlebwt_ms_full_build.cpp: the align index)
   <case>.seeds0 / .seeds25  reference seed_finder<plain_slp_t, ms_pointers<>>::find_mems with min_len 0 / 25, loaded from
                             that .thrbv.full.ms, printed per read as '(pos,len,idx) ' by oracle/ref_seeds_harness.cpp
+  <case>.occs12             the same with min_len 12 and every seed followed by its occurrences (seed_finder::find_MEM_occs,
+                            unfiltered): '(pos,len,idx:occ,occ,...) '
 """
 import os
 import shutil
@@ -31,9 +33,12 @@ def main():
                 subprocess.run([os.path.join(BIN, "ref_seeds"), fa, os.path.join(td, case + ".fq"), str(ml),
                                 os.path.join(td, f"{case}.seeds{ml}")], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
                 shutil.copy(os.path.join(td, f"{case}.seeds{ml}"), HERE)
+            subprocess.run([os.path.join(BIN, "ref_seeds"), fa, os.path.join(td, case + ".fq"), "12", os.path.join(td, f"{case}.occs12"), "occs"],
+                           check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            shutil.copy(os.path.join(td, f"{case}.occs12"), HERE)
             shutil.copy(fa + ".thrbv.full.ms", HERE)
 
 
 if __name__ == "__main__":
     main()
-    print(sorted(f for f in os.listdir(HERE) if "seeds" in f or "full" in f))
+    print(sorted(f for f in os.listdir(HERE) if "seeds" in f or "full" in f or "occs" in f))

@@ -126,6 +126,8 @@ def main():
     ap.add_argument("--seed-check-reads", type=int, default=20_000)
     ap.add_argument("--long-reads", type=int, default=20_000)
     ap.add_argument("--long-parity-reads", type=int, default=2_000)
+    ap.add_argument("--ms-reads", type=int, default=10_000_000, help="reads of the batch that go through moni_gpu_ms (16 B of results per base)")
+    ap.add_argument("--max-kernel-slices", type=int, default=8)
     args = ap.parse_args()
     OUT = args.out
     import moni_align_b200 as m
@@ -168,8 +170,13 @@ def main():
         agg = np.zeros(3)
         agg_ms = np.zeros(2)
         cnt_all: dict = {}
-        for s in range(0, n_reads, args.slice_reads):
+        starts = list(range(0, n_reads, args.slice_reads))
+        if len(starts) > args.max_kernel_slices:      # spread the measured slices over the batch (R1 half and R2 half)
+            starts = [starts[int(j * (len(starts) - 1) / (args.max_kernel_slices - 1))] for j in range(args.max_kernel_slices)]
+        measured = 0
+        for s in starts:
             e = min(n_reads, s + args.slice_reads)
+            measured += e - s
             offs = (h_offs[s:e + 1] - h_offs[s]).copy()
             rb = ix.resident_batch(h_seqs[s * L:e * L], offs)
             ix.counters(reset=True)
@@ -191,18 +198,22 @@ def main():
         m.set_option("count", 0)
         out["mems_kernel_ms_total"] = dict(zip(["pass1", "pass2", "compact"], agg.tolist()))
         out["ms_kernel_ms_total"] = dict(zip(["pass1", "pass2"], agg_ms.tolist()))
-        out["mems_reads_per_s_kernels"] = n_reads / (agg.sum() / 1e3)
-        out["ms_reads_per_s_kernels"] = n_reads / (agg_ms.sum() / 1e3)
+        out["reads_measured"] = int(measured)
+        out["mems_reads_per_s_kernels"] = measured / (agg.sum() / 1e3)
+        out["ms_reads_per_s_kernels"] = measured / (agg_ms.sum() / 1e3)
         out["counters"] = cnt_all
-        out["pass1_GBps_at_137B_per_base"] = 137.0 * total / (agg[0] / 1e3) / 1e9
+        out["pass1_GBps_at_137B_per_base"] = 137.0 * measured * L / (agg[0] / 1e3) / 1e9
         return out
     kernels()
 
     @stage("e2e")
     def e2e():
         out = {}
+        big = total > (1 << 32)
+        cap = total // 2 if big else total           # records per base stay well below 1/2 on these workloads
+        scap = total // 16 if big else total
         mo = m.pinned_empty(n_reads + 1, np.uint64)
-        rec = m.pinned_empty(total, np.uint32)
+        rec = m.pinned_empty(cap, np.uint32)
         ix.maxrimal_exact_matches_packed(h_seqs, h_offs, out=(mo, rec))
         t = time.perf_counter()
         mo_, rec_ = ix.maxrimal_exact_matches_packed(h_seqs, h_offs, out=(mo, rec))
@@ -211,33 +222,36 @@ def main():
                               "timing": ix.timing(), "hash": hash64(mo_, rec_ >> 16, rec_ & 0xFFFF)}
         e2e.mems_hash = out["mems_packed"]["hash"]
         # seeds, min_len 25
-        ref = m.pinned_empty(total, np.uint64)
-        ln = m.pinned_empty(total, np.uint32)
-        ix.find_mems(h_seqs, h_offs, 25, out=(mo, ref, rec, ln))
+        ref = m.pinned_empty(scap, np.uint64)
+        ln = m.pinned_empty(scap, np.uint32)
+        ix.find_mems(h_seqs, h_offs, 25, out=(mo, ref, rec[:scap], ln))
         t = time.perf_counter()
-        so, sr, sq, sl = ix.find_mems(h_seqs, h_offs, 25, out=(mo, ref, rec, ln))
+        so, sr, sq, sl = ix.find_mems(h_seqs, h_offs, 25, out=(mo, ref, rec[:scap], ln))
         dt = time.perf_counter() - t
         out["seeds_min25"] = {"wall_ms": dt * 1e3, "reads_per_s": n_reads / dt, "records": int(so[n_reads]), "timing": ix.timing(),
                               "hash": hash64(so, sr, sq, sl)}
         # ms: 16 bytes of results per base
-        ptr = m.pinned_empty(total, np.uint64)
-        ix.matching_statistics(h_seqs, h_offs, out=(ptr, ref))
+        k_ms = min(n_reads, args.ms_reads)
+        t_ms = k_ms * L
+        ptr = m.pinned_empty(t_ms, np.uint64)
+        lnb = m.pinned_empty(t_ms, np.uint64)
+        ix.matching_statistics(h_seqs[:t_ms], h_offs[:k_ms + 1], out=(ptr, lnb))
         t = time.perf_counter()
-        p_, l_ = ix.matching_statistics(h_seqs, h_offs, out=(ptr, ref))
+        p_, l_ = ix.matching_statistics(h_seqs[:t_ms], h_offs[:k_ms + 1], out=(ptr, lnb))
         dt = time.perf_counter() - t
-        out["ms"] = {"wall_ms": dt * 1e3, "reads_per_s": n_reads / dt, "bases_per_s": total / dt, "d2h_bytes": 16 * total,
+        out["ms"] = {"reads": int(k_ms), "wall_ms": dt * 1e3, "reads_per_s": k_ms / dt, "bases_per_s": t_ms / dt, "d2h_bytes": 16 * t_ms,
                      "timing": ix.timing(), "hash": hash64(p_, l_)}
         # properties of the complete result: lengths are matching statistics of the pointers
         Lm = l_.reshape(-1, L)
         ok1 = ok2 = True
         cap = (L - np.arange(L)).astype(np.uint64)[None, :]
-        for s in range(0, n_reads, 1 << 20):
+        for s in range(0, k_ms, 1 << 20):
             blk = Lm[s:s + (1 << 20)]
             ok1 = ok1 and bool((blk[:, 1:] + np.uint64(1) >= blk[:, :-1]).all())
             ok2 = ok2 and bool((blk <= cap).all())
         out["ms"]["len_drops_by_at_most_one"] = ok1
         out["ms"]["len_within_read"] = ok2
-        sel = np.random.default_rng(1).integers(0, n_reads, size=200_000)
+        sel = np.random.default_rng(1).integers(0, k_ms, size=200_000)
         P = p_.reshape(-1, L)[sel].astype(np.int64)
         Ls = Lm[sel].astype(np.int64)
         rr = reads[sel]

@@ -35,6 +35,12 @@ WORKLOADS = {
     "cfg3": dict(base_len=40_000_000, haplotypes=32, seed=301, snp=1e-3, indel=1e-4, read_seed=302, read_len=150,
                  pairs=5_000_000, insert=(400, 50), err=0.01,
                  desc="cfg3: 40 Mbp x 32 haplotypes (SNP 1e-3, indel 1e-4), 10M x 150 bp reads, 1% substitutions"),
+    # BASELINE.json configs[3]/[4]: "synthetic 128-haplotype human-chromosome-scale pangenome (~6 Gbp text), 100M reads" and
+    # "same index, 10 kbp ONT-like reads".  A 6 Gbp index takes the reference's CPU builder hours and ~100 GB of RAM, so the
+    # haplotype count and the read counts are kept and the chromosome is scaled down: 128 x 4 Mbp = 512 Mbp.
+    "cfg4s": dict(base_len=4_000_000, haplotypes=128, seed=401, snp=1e-3, indel=1e-4, read_seed=402, read_len=150,
+                  pairs=50_000_000, insert=(400, 50), err=0.01,
+                  desc="cfg4 scaled: 4 Mbp x 128 haplotypes (SNP 1e-3, indel 1e-4), 100M x 150 bp reads, 1% substitutions"),
     "small": dict(base_len=2_000_000, haplotypes=4, seed=5, snp=2e-3, indel=2e-4, read_seed=6, read_len=150,
                   pairs=100_000, insert=(400, 50), err=0.01, desc="functional check: 2 Mbp x 4 haplotypes"),
 }
