@@ -83,6 +83,18 @@ int moni_gpu_mems_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* 
 int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t min_len,
                    uint64_t* seed_offsets, uint64_t* seed_ref, uint32_t* seed_qpos, uint32_t* seed_len, uint64_t seed_capacity);
 
+/* Replaces seed_finder::find_MEM_occs(mem_t&) (include/aligner/seed_finder.hpp:239-251) with seed filtering off, for a batch
+ * of seeds (e.g. the records moni_gpu_seeds returned): for seed s the text positions occs[k], k in [occ_offsets[s],
+ * occ_offsets[s+1]), are mem_t::occs in the reference's order -- the seed's own position, then the suffixes above it
+ * (find_MEM_above :169-197, r_index::Phi, thirdparty/r-index/internal/r_index.hpp:225-243) and below it (find_MEM_below
+ * :201-229, ms_pointers::Phi_inv, include/ms/moni.hpp:338-354) whose common prefix with their neighbour reaches the seed
+ * length (get_prev/next_occ_with_lcp :346-370; the bounded LCE of thirdparty/ShapedSlp/Common.hpp:250-295 is a direct
+ * compare of the text in HBM).  Needs an index loaded from `<prefix>.thrbv.full.ms` (the Phi structures) with the text
+ * resident.  max_per_direction bounds each walk (the reference's is unbounded); *truncated (may be NULL) is set to 1 if a
+ * walk hit it.  Runs on the index's first GPU.  Capacity rule as for moni_gpu_mems. */
+int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
+                       uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity, int* truncated);
+
 /* Event counters accumulated over all calls since the last reset, when counting is enabled
  * (moni_gpu_set_option("count", "1"); off by default, it costs a few percent):
  * c[0]=bases, c[1]=threshold jumps (ms_pointers.hpp:482-505 taken), c[2]=LCE restarts,

@@ -9,6 +9,7 @@ Host-side mirror of the reference's two call sites for this path, over the C ABI
     ms_c::matching_statistics      src/matching_statistics.cpp:242   MoniIndex.matching_statistics
     mems_c::maxrimal_exact_matches src/mems.cpp:241                  MoniIndex.maxrimal_exact_matches
     seed_finder::find_mems         include/aligner/seed_finder.hpp:126   MoniIndex.find_mems
+    seed_finder::find_MEM_occs     include/aligner/seed_finder.hpp:239   MoniIndex.find_MEM_occs
 
 The method names (including the reference's spelling of "maxrimal") and the meaning of the results
 are the reference's; the unit of work is a batch of reads instead of one kseq record.  There is no
@@ -38,7 +39,7 @@ class MoniGpuError(RuntimeError):
 
 EXPORTS = [
     "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems", "moni_gpu_mems32",
-    "moni_gpu_mems_packed", "moni_gpu_seeds",
+    "moni_gpu_mems_packed", "moni_gpu_seeds", "moni_gpu_seed_occs",
     "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
@@ -65,6 +66,7 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_mems32.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, ctypes.c_uint64]
     L.moni_gpu_mems_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, ctypes.c_uint64]
     L.moni_gpu_seeds.argtypes = [vp, vp, _u64p, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, vp, vp, ctypes.c_uint64]
+    L.moni_gpu_seed_occs.argtypes = [vp, _u64p, vp, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, ctypes.c_uint64, ctypes.POINTER(ci)]
     L.moni_gpu_counters.argtypes = [vp, _u64p, ci]
     L.moni_gpu_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.moni_gpu_set_option.argtypes = [cc, cc]
@@ -241,6 +243,26 @@ class MoniIndex:
                                       ref.shape[0]))
         k = int(so[nr])
         return so, ref[:k], qp[:k], ln[:k]
+
+    def find_MEM_occs(self, seed_ref: np.ndarray, seed_len: np.ndarray, max_per_direction: int = 1 << 20, capacity: int | None = None):
+        """(occ_offsets uint64[n+1], occs uint64[k], truncated) -- seed_finder::find_MEM_occs (unfiltered) for every seed:
+        its own position, then the occurrences above and below it in suffix-array order."""
+        seed_ref = np.ascontiguousarray(seed_ref, dtype=np.uint64)
+        seed_len = np.ascontiguousarray(seed_len, dtype=np.uint32)
+        n = seed_ref.shape[0]
+        off = np.empty(n + 1, dtype=np.uint64)
+        tr = ctypes.c_int(0)
+        cap = max(4 * n, 1) if capacity is None else int(capacity)
+        occs = np.empty(max(cap, 1), dtype=np.uint64)
+        rc = self._L.moni_gpu_seed_occs(self._h, _u64(seed_ref), _ptr(seed_len), n, int(max_per_direction), _u64(off), _u64(occs), cap,
+                                        ctypes.byref(tr))
+        if rc == -4 and capacity is None and n:      # capacity was a guess: the needed size is in off[n]
+            cap = int(off[n])
+            occs = np.empty(cap, dtype=np.uint64)
+            rc = self._L.moni_gpu_seed_occs(self._h, _u64(seed_ref), _ptr(seed_len), n, int(max_per_direction), _u64(off), _u64(occs), cap,
+                                            ctypes.byref(tr))
+        _check(rc)
+        return off, occs[:int(off[n])], bool(tr.value)
 
     # -- instrumentation -----------------------------------------------------------------------
     def counters(self, reset: bool = True) -> dict:

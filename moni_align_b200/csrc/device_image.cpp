@@ -239,6 +239,30 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
                 worst, now_s() - t0);
 }
 
+void build_phi_tables(const FlatRlbwt& b, HostImage& img) {
+    img.phi.clear();
+    img.phi_inv.clear();
+    img.hdr.phi_n = 0;
+    img.hdr.first_run_sample = b.R ? (b.samples_start[0] + 1) % b.n : 0;
+    if (b.pred.empty() || b.pred_start.empty()) return;
+    const uint64_t R = b.R;
+    if (b.pred.size() != R || b.pred_to_run.size() != R || b.pred_start.size() != R || b.pred_start_to_run.size() != R)
+        throw std::runtime_error("exporter: Phi structures do not have R entries");
+    img.phi.resize(R);
+    img.phi_inv.resize(R);
+    for (uint64_t j = 0; j < R; ++j) {
+        if (j && (b.pred[j] <= b.pred[j - 1] || b.pred_start[j] <= b.pred_start[j - 1]))
+            throw std::runtime_error("exporter: Phi keys not increasing");
+        const uint64_t run = b.pred_to_run[j], run_s = b.pred_start_to_run[j];
+        if (run >= R || run_s >= R) throw std::runtime_error("exporter: Phi run index out of range");
+        img.phi[j].key = b.pred[j];
+        img.phi[j].val = run > 0 ? b.samples_last[run - 1] : kPhiNone;
+        img.phi_inv[j].key = b.pred_start[j];
+        img.phi_inv[j].val = run_s + 1 < R ? b.samples_start[run_s + 1] : kPhiNone;
+    }
+    img.hdr.phi_n = R;
+}
+
 void build_grammar_table(const FlatSlp& g, const ExportOptions& opt, HostImage& img) {
     const double t0 = now_s();
     const uint64_t A = g.alph_size, NR = g.num_rules;

@@ -67,6 +67,17 @@ struct alignas(16) SlpNode {
 static_assert(sizeof(SlpNode) == 16, "SlpNode must be 16 bytes");
 constexpr uint32_t kLeafBit = 0x80000000u;
 
+// One entry of a Phi / Phi^-1 table (`moni align` indexes only): the key is a text position marked in r_index::pred
+// (resp. ms_pointers::pred_start), the value is the sample the reference adds the distance to --
+//   Phi      (thirdparty/r-index/internal/r_index.hpp:225-243):  samples_last [pred_to_run[jr] - 1]
+//   Phi^-1   (include/ms/moni.hpp:338-354):                       samples_start[pred_start_to_run[jr] + 1]
+// so a step is one predecessor search over the keys plus arithmetic.
+struct alignas(16) PhiEntry {
+    uint64_t key;
+    uint64_t val;           // kPhiNone where the reference would index outside its arrays (Phi of SA[0], Phi^-1 of SA[n-1])
+};
+constexpr uint64_t kPhiNone = ~0ULL;
+
 // Per-symbol constants (device: __constant__ memory).
 struct SymbolTables {
     uint64_t F[256];
@@ -89,6 +100,8 @@ struct ImageHeader {
     uint32_t n_table_syms = 0;
     uint32_t slp_depth_max = 0;
     uint32_t init_row = 0, init_off = 0;         // pos = n - 1 as (row, offset)
+    uint64_t phi_n = 0;                          // entries of each Phi table (R), 0 without the `moni align` index
+    uint64_t first_run_sample = 0;               // (samples_start[0] + 1) % n   (include/ms/moni.hpp:330-332)
 };
 
 // Host copy of the image.
@@ -101,9 +114,11 @@ struct HostImage {
     std::vector<GapSlot> slots;         // R + (#symbols)
     std::vector<SlpNode> nodes;
     std::vector<uint8_t> pool;
+    std::vector<PhiEntry> phi, phi_inv; // R each, keys increasing (empty without the `moni align` index)
     uint64_t bytes() const {
         return rows.size() * sizeof(MoveRow) + row_pos.size() * 8 + crun_row.size() * 4 +
-               slots.size() * sizeof(GapSlot) + nodes.size() * sizeof(SlpNode) + pool.size();
+               slots.size() * sizeof(GapSlot) + nodes.size() * sizeof(SlpNode) + pool.size() +
+               (phi.size() + phi_inv.size()) * sizeof(PhiEntry);
     }
 };
 
@@ -120,5 +135,6 @@ struct ExportOptions {
 // Throws std::runtime_error on anything the image cannot represent.
 void build_move_table(const FlatRlbwt& bwt, const ExportOptions& opt, HostImage& img);
 void build_grammar_table(const FlatSlp& slp, const ExportOptions& opt, HostImage& img);
+void build_phi_tables(const FlatRlbwt& bwt, HostImage& img);     // no-op when the index has no Phi structures
 
 }  // namespace moni

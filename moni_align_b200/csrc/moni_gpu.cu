@@ -259,6 +259,26 @@ __global__ void __launch_bounds__(kBlock) k_mem_gather_packed(const uint64_t* __
     }
 }
 
+// ---- occurrence enumeration: one seed per thread, Phi / Phi^-1 walks with a bounded LCE on the text in HBM -------------
+__global__ void __launch_bounds__(kBlock) k_occ_count(ImageView v, const uint64_t* __restrict__ ref, const uint32_t* __restrict__ len,
+                                                      uint64_t n_seeds, uint64_t cap, uint64_t* __restrict__ counts,
+                                                      uint32_t* __restrict__ truncated) {
+    const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (i > n_seeds) return;
+    if (i == n_seeds) { counts[i] = 0; return; }
+    bool tr = false;
+    counts[i] = occ_walk(v, ref[i], len[i], cap, nullptr, &tr);
+    if (tr) atomicOr(truncated, 1u);
+}
+
+__global__ void __launch_bounds__(kBlock) k_occ_fill(ImageView v, const uint64_t* __restrict__ ref, const uint32_t* __restrict__ len,
+                                                     uint64_t n_seeds, uint64_t cap, const uint64_t* __restrict__ off,
+                                                     uint64_t* __restrict__ occs) {
+    const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (i >= n_seeds) return;
+    occ_walk(v, ref[i], len[i], cap, occs + off[i], nullptr);
+}
+
 __global__ void k_widen_counts(const uint32_t* __restrict__ c, uint64_t* __restrict__ out, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = c[i];
@@ -384,6 +404,8 @@ struct Replica {
     int dev = 0;
     std::vector<Lane> lanes;
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
+    DevBuf phi, phi_inv;                                  // `moni align` indexes only
+    DevBuf occ_ref, occ_len, occ_off, occ_out, occ_flag, occ_cub;   // moni_gpu_seed_occs scratch
     DevBuf shard_off, shard_pos, shard_len, shard_ref;   // multi-GPU mems: a shard's records wait here for their global offset
     ImageView view;
     std::mutex mu;
@@ -393,6 +415,8 @@ struct Replica {
         cudaSetDevice(dev);
         rows.release(); row_pos.release(); crun_row.release(); slots.release(); nodes.release(); pool.release();
         sym.release(); counters.release();
+        phi.release(); phi_inv.release();
+        occ_ref.release(); occ_len.release(); occ_off.release(); occ_out.release(); occ_flag.release(); occ_cub.release();
         shard_off.release(); shard_pos.release(); shard_len.release(); shard_ref.release();
         for (Lane& L : lanes) {
             L.scratch.release();
@@ -891,6 +915,7 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
                 if (access((std::string(prefix) + exts[k]).c_str(), R_OK) == 0) { which = k; break; }
             read_thrbv_ms(std::string(prefix) + exts[which], bwt, which != 0);
             build_move_table(bwt, eo, img);
+            build_phi_tables(bwt, img);
         } catch (...) {
             slp_thread.join();
             throw;
@@ -913,6 +938,8 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             upload(R->slots, img.slots, st);
             upload(R->nodes, img.nodes, st);
             upload(R->pool, img.pool, st);
+            upload(R->phi, img.phi, st);
+            upload(R->phi_inv, img.phi_inv, st);
             R->sym.reserve(sizeof(SymbolTables));
             CK(cudaMemcpyAsync(R->sym.p, &img.sym, sizeof(SymbolTables), cudaMemcpyHostToDevice, st));
             R->counters.reserve(sizeof(Counters));
@@ -926,6 +953,8 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             v.nodes = R->nodes.as<SlpNode>();
             v.pool = R->pool.as<uint8_t>();
             v.sym = R->sym.as<SymbolTables>();
+            v.phi = R->phi.as<PhiEntry>();
+            v.phi_inv = R->phi_inv.as<PhiEntry>();
             v.hdr = img.hdr;
             idx->reps.push_back(std::move(R));
         }
@@ -1056,6 +1085,56 @@ int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offset
                    uint64_t* seed_offsets, uint64_t* seed_ref, uint32_t* seed_qpos, uint32_t* seed_len, uint64_t seed_capacity) {
     const uint32_t ml = min_len > 0x7FFFFFFFull ? 0x7FFFFFFFu : (uint32_t)min_len;     // reads are shorter than 2^31
     return mems_impl(idx, 2, seqs, offsets, n_reads, rec_out(seed_offsets, seed_qpos, 4, seed_len, 4, seed_ref, 8, seed_capacity, 12, ml));
+}
+
+int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
+                       uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity, int* truncated) {
+    if (!idx || !occ_offsets || (n_seeds && (!seed_ref || !seed_len)) || n_seeds >= 0x7FFFFFF0ull) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
+    if (truncated) *truncated = 0;
+    if (n_seeds == 0) { occ_offsets[0] = 0; return 0; }
+    if (!occs && occ_capacity) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    if (idx->hdr.phi_n == 0) { g_err = "this index has no Phi structures: load <prefix>.thrbv.full.ms (the `moni align` index)"; return MONI_GPU_EINVAL; }
+    if (!(idx->hdr.root_ref & kLeafBit)) { g_err = "occurrence enumeration needs the text in HBM (leaf_len = 0 / text_budget)"; return MONI_GPU_EINVAL; }
+    return guarded([&]() -> int {
+        Replica& R = *idx->reps[0];
+        std::lock_guard<std::mutex> lock(R.mu);
+        CK(cudaSetDevice(R.dev));
+        cudaStream_t st = R.stream();
+        R.occ_ref.reserve(n_seeds * 8);
+        R.occ_len.reserve(n_seeds * 4);
+        R.occ_off.reserve((n_seeds + 1) * 8);
+        R.occ_flag.reserve(16);
+        CK(cudaMemcpyAsync(R.occ_ref.p, seed_ref, n_seeds * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(R.occ_len.p, seed_len, n_seeds * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(R.occ_flag.p, 0, 4, st));
+        const unsigned blocks = (unsigned)((n_seeds + 1 + kBlock - 1) / kBlock);
+        k_occ_count<<<blocks, kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds, max_per_direction,
+                                               R.occ_off.as<uint64_t>(), R.occ_flag.as<uint32_t>());
+        g_launches++;
+        size_t tmp = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, R.occ_off.as<uint64_t>(), R.occ_off.as<uint64_t>(), (int)(n_seeds + 1), st));
+        R.occ_cub.reserve(tmp);
+        CK(cub::DeviceScan::ExclusiveSum(R.occ_cub.p, tmp, R.occ_off.as<uint64_t>(), R.occ_off.as<uint64_t>(), (int)(n_seeds + 1), st));
+        g_launches += 2;
+        uint32_t flag = 0;
+        CK(cudaMemcpyAsync(occ_offsets, R.occ_off.p, (n_seeds + 1) * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&flag, R.occ_flag.p, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (truncated) *truncated = flag ? 1 : 0;
+        const uint64_t total = occ_offsets[n_seeds];
+        if (total > occ_capacity) {
+            g_err = "occ_capacity too small: " + std::to_string(total) + " positions needed";
+            return MONI_GPU_ENOMEM;
+        }
+        R.occ_out.reserve(total * 8 + 16);
+        k_occ_fill<<<(unsigned)((n_seeds + kBlock - 1) / kBlock), kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds,
+                                                                               max_per_direction, R.occ_off.as<uint64_t>(), R.occ_out.as<uint64_t>());
+        g_launches++;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(occs, R.occ_out.p, total * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        return 0;
+    });
 }
 
 int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset) {

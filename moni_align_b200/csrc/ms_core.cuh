@@ -30,6 +30,8 @@ struct ImageView {
     const SlpNode* nodes = nullptr;
     const uint8_t* pool = nullptr;
     const SymbolTables* sym = nullptr;
+    const PhiEntry* phi = nullptr;       // `moni align` indexes only
+    const PhiEntry* phi_inv = nullptr;
     ImageHeader hdr;
 };
 
@@ -359,6 +361,66 @@ MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m
     while (st.i < (uint32_t)m)
         lengths_step<LenT, SEEDS>(v, seq, (uint32_t)m, ptr, ptr_stride, ptr_out, len, mem_out, st, cnt, ref_out, min_len, len_stride);
     return st.n_mems;
+}
+
+// ---- occurrence enumeration (`moni align`, include/aligner/seed_finder.hpp:169-251, 346-368) ---------------------
+// r_index::Phi (r_index.hpp:225-243) / ms_pointers::Phi_inv (moni.hpp:338-354) on a flattened table: jr = strict
+// predecessor of i among the keys, circular (sparse_sd_vector.hpp:168-172); delta = key < i ? i - key : i + 1;
+// result = (val + delta) % n.
+MONI_HD uint64_t phi_step(const PhiEntry* tab, uint64_t cnt, uint64_t n, uint64_t i) {
+    uint64_t lo = 0, hi = cnt;                       // # keys < i
+    while (lo < hi) {
+        const uint64_t mid = lo + (hi - lo) / 2;
+        if (ld(&tab[mid].key) < i) lo = mid + 1; else hi = mid;
+    }
+    const uint64_t jr = lo == 0 ? cnt - 1 : lo - 1;
+    const uint64_t j = ld(&tab[jr].key);
+    const uint64_t delta = j < i ? i - j : i + 1;
+    return (ld(&tab[jr].val) + delta) % n;
+}
+
+// Is the longest common extension of text positions a and b at least len?  What the caller of lceToRBounded
+// (thirdparty/ShapedSlp/Common.hpp:250-295) tests at seed_finder.hpp:178,208; requires the text in HBM (text mode) and
+// a + len <= N, b + len <= N.
+MONI_HD bool lce_at_least(const ImageView& v, uint64_t a, uint64_t b, uint64_t len) {
+    const uint8_t* t = v.pool + ((uint64_t)(v.hdr.root_ref & ~kLeafBit) << v.hdr.pool_shift);
+    uint64_t k = 0;
+    for (; k + 8 <= len; k += 8)
+        if (load8(t + a + k) != load8(t + b + k)) return false;
+    if (k < len) {
+        const uint64_t x = load8(t + a + k) ^ load8(t + b + k);
+        const uint64_t mask = (1ull << (8 * (len - k))) - 1ull;
+        if (x & mask) return false;
+    }
+    return true;
+}
+
+// seed_finder::find_MEM_occs without seed filtering (:239-251): the seed position, then find_MEM_above (:169-197: Phi steps
+// while the LCE with the previous suffix reaches len; get_prev_occ_with_lcp :359-370), then find_MEM_below (:201-229, Phi^-1,
+// get_next_occ_with_lcp :346-357).  Writes at most `cap` positions per direction to out (if not null; out[0] = pos) and
+// returns the number of positions (1 + above + below); *truncated is set when a direction stopped at the cap.
+MONI_HD uint64_t occ_walk(const ImageView& v, uint64_t pos, uint64_t len, uint64_t cap, uint64_t* out, bool* truncated) {
+    const uint64_t N = v.hdr.text_len, n = v.hdr.n;
+    uint64_t k = 0;
+    if (out) out[k] = pos;
+    ++k;
+    for (int dir = 0; dir < 2; ++dir) {
+        const PhiEntry* tab = dir == 0 ? v.phi : v.phi_inv;
+        const uint64_t stop_at = dir == 0 ? v.hdr.first_run_sample : v.hdr.init_sample;   // get_first / get_last_run_sample
+        uint64_t curr = pos, taken = 0;
+        for (;;) {
+            if (curr == stop_at) break;                                   // the reference returns lcp 0 here
+            const uint64_t next = phi_step(tab, v.hdr.phi_n, n, curr);
+            if (!((N - curr) >= len && (N - next) >= len)) break;         // lcp stays 0 (u64 arithmetic as in the reference)
+            if (!lce_at_least(v, curr, next, len)) break;
+            if (taken == cap) { if (truncated) *truncated = true; break; }
+            if (out) out[k] = next;
+            ++k;
+            ++taken;
+            curr = next;
+        }
+    }
+    return k;
 }
 
 }  // namespace moni

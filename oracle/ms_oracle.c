@@ -273,3 +273,79 @@ void oracle_seeds_batch(oracle_index* ix, const u8* seqs, const u64* offsets, u6
     seed_offsets[n_reads] = total;
     free(ptr); free(rec);
 }
+
+/* ---- occurrence enumeration of `moni align` (seed filtering off) -------------------------------------------------
+ * r_index::Phi (thirdparty/r-index/internal/r_index.hpp:225-243), ms_pointers::Phi_inv (include/ms/moni.hpp:338-354),
+ * sparse_sd_vector::predecessor_rank_circular (sparse_sd_vector.hpp:168-172), seed_finder::get_prev/next_occ_with_lcp
+ * (include/aligner/seed_finder.hpp:346-370), find_MEM_above / find_MEM_below / find_MEM_occs (:169-251).
+ * The bounded LCE (thirdparty/ShapedSlp/Common.hpp:250-295) is only ever tested for ">= len" by its callers, which is
+ * what lce_reaches answers character by character.  Pinned against oracle/_ref/bin/ref_seeds ... occs (tests/golden/*.occs12). */
+typedef struct {
+    u64 R;
+    const u64* pred; const u64* pred_to_run;               /* r_index::pred (positions of the set bits), pred_to_run */
+    const u64* pred_start; const u64* pred_start_to_run;   /* ms_pointers::pred_start, pred_start_to_run */
+} oracle_phi;
+
+static oracle_phi g_phi;   /* one index at a time is enough for the tests */
+
+void oracle_set_phi(u64 R, const u64* pred, const u64* pred_to_run, const u64* pred_start, const u64* pred_start_to_run) {
+    g_phi.R = R; g_phi.pred = pred; g_phi.pred_to_run = pred_to_run; g_phi.pred_start = pred_start; g_phi.pred_start_to_run = pred_start_to_run;
+}
+
+static u64 pred_rank_circular(const u64* ones, u64 m, u64 i) {          /* rank(i) == 0 ? number_of_1() - 1 : rank(i) - 1 */
+    const u64 rk = lower_bound(ones, m, i);
+    return rk == 0 ? m - 1 : rk - 1;
+}
+
+static u64 phi(const oracle_index* ix, u64 i) {
+    const u64 jr = pred_rank_circular(g_phi.pred, g_phi.R, i);
+    const u64 j = g_phi.pred[jr];
+    const u64 delta = j < i ? i - j : i + 1;
+    const u64 prev_sample = ix->samples_last[g_phi.pred_to_run[jr] - 1];
+    return (prev_sample + delta) % ix->n;
+}
+
+static u64 phi_inv(const oracle_index* ix, u64 i) {
+    const u64 jr = pred_rank_circular(g_phi.pred_start, g_phi.R, i);
+    const u64 j = g_phi.pred_start[jr];
+    const u64 delta = j < i ? i - j : i + 1;
+    const u64 prev_sample = ix->samples_start[g_phi.pred_start_to_run[jr] + 1];
+    return (prev_sample + delta) % ix->n;
+}
+
+static int lce_reaches(const oracle_index* ix, u64 a, u64 b, u64 len) {
+    for (u64 k = 0; k < len; ++k)
+        if (char_at(ix, a + k, NULL) != char_at(ix, b + k, NULL)) return 0;
+    return 1;
+}
+
+/* find_MEM_occs: occs = [pos] + above + below.  Returns the count; writes at most cap entries. */
+u64 oracle_find_mem_occs(oracle_index* ix, u64 pos, u64 len, u64* occs, u64 cap) {
+    const u64 n = ix->text_len;                                          /* seed_finder::n */
+    const u64 first_run_sample = (ix->samples_start[0] + 1) % ix->n;
+    const u64 last_run_sample = (ix->samples_last[ix->R - 1] + 1) % ix->n;
+    u64 k = 0;
+    if (k < cap) occs[k] = pos;
+    ++k;
+    for (u64 curr = pos;;) {                                             /* find_MEM_above */
+        if (curr == first_run_sample) break;
+        const u64 prev = phi(ix, curr);
+        u64 ok = 0;
+        if ((n - curr) >= len && (n - prev) >= len) ok = lce_reaches(ix, curr, prev, len);
+        if (!ok) break;
+        if (k < cap) occs[k] = prev;
+        ++k;
+        curr = prev;
+    }
+    for (u64 curr = pos;;) {                                             /* find_MEM_below */
+        if (curr == last_run_sample) break;
+        const u64 next = phi_inv(ix, curr);
+        u64 ok = 0;
+        if ((n - curr) >= len && (n - next) >= len) ok = lce_reaches(ix, curr, next, len);
+        if (!ok) break;
+        if (k < cap) occs[k] = next;
+        ++k;
+        curr = next;
+    }
+    return k;
+}

@@ -236,6 +236,9 @@ class OracleIndex:
         L.oracle_char_at.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
         L.oracle_char_at.restype = ctypes.c_uint8
         L.oracle_seeds_batch.argtypes = [ctypes.c_void_p, u8p, u64p, ctypes.c_uint64, ctypes.c_uint64, u64p, u64p, u64p, u64p]
+        L.oracle_set_phi.argtypes = [ctypes.c_uint64, u64p, u64p, u64p, u64p]
+        L.oracle_find_mem_occs.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, u64p, ctypes.c_uint64]
+        L.oracle_find_mem_occs.restype = ctypes.c_uint64
         import os as _os
         ext = next((e for e in (".thrbv.ms", ".thrbv.full.ms", ".thrbv.full.lcp.ms") if _os.path.exists(prefix + e)), ".thrbv.ms")
         self.bwt = read_thrbv_ms(prefix + ext, full=ext != ".thrbv.ms")
@@ -311,6 +314,26 @@ class OracleIndex:
         k = int(so[-1])
         return so, cols[0][:k], cols[1][:k], cols[2][:k]
 
+    def mem_occs(self, seed_ref, seed_len):
+        """(occ_offsets, occs): seed_finder::find_MEM_occs (unfiltered) for every seed; needs the `moni align` index."""
+        b = self.bwt
+        if "pred" not in b:
+            raise ValueError("the oracle index was not loaded from a .thrbv.full.ms file")
+        k = self._keep
+        for name in ("pred", "pred_to_run", "pred_start", "pred_start_to_run"):
+            k[name] = np.ascontiguousarray(b[name], dtype=np.uint64)
+        self.lib.oracle_set_phi(b["R"], *[_p(k[nm], ctypes.c_uint64) for nm in ("pred", "pred_to_run", "pred_start", "pred_start_to_run")])
+        off, out = [0], []
+        buf = np.zeros(1 << 16, dtype=np.uint64)
+        for p, l in zip(seed_ref, seed_len):
+            c = int(self.lib.oracle_find_mem_occs(self.h, int(p), int(l), _p(buf, ctypes.c_uint64), buf.shape[0]))
+            if c > buf.shape[0]:
+                buf = np.zeros(c, dtype=np.uint64)
+                c = int(self.lib.oracle_find_mem_occs(self.h, int(p), int(l), _p(buf, ctypes.c_uint64), buf.shape[0]))
+            out.append(buf[:c].copy())
+            off.append(off[-1] + c)
+        return np.array(off, dtype=np.uint64), (np.concatenate(out) if out else np.zeros(0, dtype=np.uint64))
+
     def counters(self, reset: bool = True) -> dict:
         out = np.zeros(5, dtype=np.uint64)
         self.lib.oracle_counters(self.h, _p(out, ctypes.c_uint64), 1 if reset else 0)
@@ -346,4 +369,17 @@ def format_seeds(names, seed_offsets, seed_ref, seed_len, seed_qpos) -> bytes:
     for r, nm in enumerate(names):
         a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
         out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d,%d) " % (int(seed_ref[t]), int(seed_len[t]), int(seed_qpos[t])) for t in range(a, b)) + b"\n")
+    return b"".join(out)
+
+
+def format_occs(names, seed_offsets, seed_ref, seed_len, seed_qpos, occ_offsets, occs) -> bytes:
+    """The text `ref_seeds ... occs` prints: '(' pos ',' len ',' idx ':' occ ',' occ ... ') ' tokens."""
+    out = []
+    for r, nm in enumerate(names):
+        a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
+        toks = []
+        for t in range(a, b):
+            oc = occs[int(occ_offsets[t]):int(occ_offsets[t + 1])]
+            toks.append(b"(%d,%d,%d:" % (int(seed_ref[t]), int(seed_len[t]), int(seed_qpos[t])) + b",".join(b"%d" % int(x) for x in oc) + b") ")
+        out.append(b">" + nm + b"\n" + b"".join(toks) + b"\n")
     return b"".join(out)

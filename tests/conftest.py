@@ -72,7 +72,12 @@ def run_host_sim(exe, prefix, flat, offs, tmpdir, extra=()):
     so = raw[at:at + nr + 1]
     ks = int(so[-1]) if nr >= 0 and so.shape[0] else 0
     at += nr + 1
-    return res + (so, raw[at:at + ks], raw[at + ks:at + 2 * ks], raw[at + 2 * ks:at + 3 * ks])
+    res = res + (so, raw[at:at + ks], raw[at + ks:at + 2 * ks], raw[at + 2 * ks:at + 3 * ks])
+    at += 3 * ks
+    if at < raw.shape[0]:              # occurrence lists (index with Phi structures, text mode)
+        oo = raw[at:at + ks + 1]
+        res = res + (oo, raw[at + ks + 1:at + ks + 1 + int(oo[-1])])
+    return res
 
 
 def full_only_prefix(case, tmpdir):

@@ -6,6 +6,7 @@
 //   batch.bin : u64 n_reads, u64 offsets[n_reads+1], u8 seqs[offsets[n_reads]]
 //   out.bin   : u64 ptr[total], u64 len[total], u64 mem_offsets[n_reads+1], u64 mem_pos[k], u64 mem_len[k], u64 counters[8]
 //               and, when seed_min_len is given: u64 seed_offsets[n_reads+1], u64 seed_ref[s], u64 seed_len[s], u64 seed_qpos[s]
+//               and, when the index has Phi structures: u64 occ_offsets[s+1], u64 occs[...]  (occ_walk per seed, cap 2^20)
 // If <prefix>.thrbv.ms does not exist, <prefix>.thrbv.full.ms (the `moni align` index) is read.
 #include <cstdio>
 #include <cstdlib>
@@ -42,9 +43,11 @@ int main(int argc, char** argv) {
         HostImage img;
         build_move_table(bwt, opt, img);
         build_grammar_table(slp, opt, img);
+        build_phi_tables(bwt, img);
         ImageView v;
         v.rows = img.rows.data(); v.row_pos = img.row_pos.data(); v.crun_row = img.crun_row.data();
         v.slots = img.slots.data(); v.nodes = img.nodes.data(); v.pool = img.pool.data(); v.sym = &img.sym; v.hdr = img.hdr;
+        v.phi = img.phi.data(); v.phi_inv = img.phi_inv.data();
 
         FILE* f = fopen(argv[2], "rb");
         if (!f) throw std::runtime_error("cannot open batch");
@@ -100,6 +103,17 @@ int main(int argc, char** argv) {
             fwrite(s_ref.data(), 8, s_ref.size(), f);
             fwrite(s_len.data(), 8, s_len.size(), f);
             fwrite(s_qpos.data(), 8, s_qpos.size(), f);
+            if (img.hdr.phi_n && (img.hdr.root_ref & kLeafBit)) {
+                std::vector<uint64_t> oo(1, 0), occs;
+                for (size_t t = 0; t < s_ref.size(); ++t) {
+                    const uint64_t c = occ_walk(v, s_ref[t], s_len[t], 1ull << 20, nullptr, nullptr);
+                    occs.resize(oo.back() + c);
+                    occ_walk(v, s_ref[t], s_len[t], 1ull << 20, occs.data() + oo.back(), nullptr);
+                    oo.push_back(oo.back() + c);
+                }
+                fwrite(oo.data(), 8, oo.size(), f);
+                fwrite(occs.data(), 8, occs.size(), f);
+            }
         }
         fclose(f);
         fprintf(stderr, "host_sim: bases %llu jumps %llu restarts %llu depth %llu chars %llu scan_rows %llu general %llu descents %llu; image %.1f MB\n",

@@ -368,3 +368,30 @@ def test_seeds_random_reads_chunked_and_sharded(m, oracle_mod):
             assert np.array_equal(got[2], want[2]) and np.array_equal(got[3], want[3])
     for ix in (one, small, three):
         ix.close()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_seed_occurrences_equal_reference_find_MEM_occs(case, m, indexes, oracle_mod, tmp_path):
+    """moni_gpu_seeds + moni_gpu_seed_occs on the `moni align` index == the reference's find_mems + find_MEM_occs
+    (tests/golden/<case>.occs12); per-direction cap and capacity errors behave as documented."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    ix = m.MoniIndex(full_only_prefix(case, tmp_path))
+    so, ref, qpos, ln = ix.find_mems(flat, offs, 12)
+    oo, occs, trunc = ix.find_MEM_occs(ref, ln)
+    assert not trunc
+    assert oracle_mod.format_occs(names, so, ref, ln, qpos, oo, occs) == open(pre + ".occs12", "rb").read()
+    # cap of one step per direction: a prefix-consistent subset, flagged
+    oo1, occs1, trunc1 = ix.find_MEM_occs(ref, ln, max_per_direction=1)
+    cnt, cnt1 = np.diff(oo.astype(np.int64)), np.diff(oo1.astype(np.int64))
+    assert (cnt1 <= 3).all() and (cnt1 <= cnt).all() and trunc1 == bool((cnt1 < cnt).any())
+    assert np.array_equal(occs1[oo1[:-1].astype(np.int64)], ref)
+    with pytest.raises(m.MoniGpuError) as e:
+        ix.find_MEM_occs(ref, ln, capacity=1)
+    assert e.value.code == -4
+    with pytest.raises(m.MoniGpuError) as e:          # an index without Phi structures refuses
+        indexes[case].find_MEM_occs(ref[:1], ln[:1])
+    assert e.value.code == -1
+    ix.close()

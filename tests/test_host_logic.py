@@ -143,3 +143,25 @@ def test_seed_core_on_N_rich_reads(host_sim, oracle_mod, tmp_path):
         res = run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path, (0, 8, min_len))
         so, ref, qpos, ln = ix.seeds(flat, offs, min_len)
         assert np.array_equal(res[6], so) and np.array_equal(res[7], ref) and np.array_equal(res[8], ln) and np.array_equal(res[9], qpos)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_occurrence_walk_matches_reference_find_MEM_occs(case, host_sim, oracle_mod, tmp_path):
+    """occ_walk (flattened Phi / Phi^-1 tables, word-wise bounded LCE on the text) on the image exported from the reference's
+    .thrbv.full.ms == the reference's find_MEM_occs lists (tests/golden/<case>.occs12)."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    res = run_host_sim(host_sim, full_only_prefix(case, tmp_path), flat, offs, tmp_path, (1 << 30, 8, 12))   # leaf_len >= text: text mode
+    assert len(res) == 12
+    so, ref, ln, qpos, oo, occs = res[6:12]
+    assert oracle_mod.format_occs(names, so, ref, ln, qpos, oo, occs) == open(pre + ".occs12", "rb").read()
+
+
+def test_occurrence_walk_needs_the_align_index(host_sim, tmp_path):
+    """From a plain .thrbv.ms there are no Phi structures: host_sim writes no occurrence section (the library returns EINVAL)."""
+    pre = os.path.join(GOLDEN, "pan4")
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs[:5])
+    assert len(run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path, (0, 8, 12))) == 10

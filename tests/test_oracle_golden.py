@@ -120,3 +120,18 @@ def test_seed_rule_drops_all_N_matches(oracle_mod):
     r = seqs.index(b"NNNNNNNNNNNNNNNNNNNN")
     assert int(mo[r + 1] - mo[r]) > 0 and int(ml[int(mo[r])]) > 0      # `mems` reports the N match ...
     assert int(so[r + 1] - so[r]) == 0                                  # ... the seed rule drops it
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_oracle_occurrences_equal_reference_find_MEM_occs(case, oracle_mod, tmp_path):
+    """oracle_find_mem_occs (Phi / Phi^-1 walks with the bounded LCE) == the reference's seed_finder::find_MEM_occs with seed
+    filtering off, on the reference's own .thrbv.full.ms (tests/golden/<case>.occs12, min_len 12)."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    ix = oracle_mod.OracleIndex(full_only_prefix(case, tmp_path))
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    so, ref, qpos, ln = ix.seeds(flat, offs, 12)
+    oo, occs = ix.mem_occs(ref, ln)
+    assert int(oo[-1]) > len(ref)            # some seeds do have further occurrences
+    assert oracle_mod.format_occs(names, so, ref, ln, qpos, oo, occs) == open(pre + ".occs12", "rb").read()
