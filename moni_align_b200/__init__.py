@@ -244,16 +244,21 @@ class MoniIndex:
         k = int(so[nr])
         return so, ref[:k], qp[:k], ln[:k]
 
-    def find_MEM_occs(self, seed_ref: np.ndarray, seed_len: np.ndarray, max_per_direction: int = 1 << 20, capacity: int | None = None):
+    def find_MEM_occs(self, seed_ref: np.ndarray, seed_len: np.ndarray, max_per_direction: int = 1 << 20, capacity: int | None = None,
+                      out=None):
         """(occ_offsets uint64[n+1], occs uint64[k], truncated) -- seed_finder::find_MEM_occs (unfiltered) for every seed:
         its own position, then the occurrences above and below it in suffix-array order."""
         seed_ref = np.ascontiguousarray(seed_ref, dtype=np.uint64)
         seed_len = np.ascontiguousarray(seed_len, dtype=np.uint32)
         n = seed_ref.shape[0]
-        off = np.empty(n + 1, dtype=np.uint64)
         tr = ctypes.c_int(0)
-        cap = max(4 * n, 1) if capacity is None else int(capacity)
-        occs = np.empty(max(cap, 1), dtype=np.uint64)
+        if out is not None:                      # caller's (pinned) arrays: offsets uint64[n+1], positions uint64[capacity]
+            off, occs = out
+            capacity = cap = occs.shape[0]
+        else:
+            off = np.empty(n + 1, dtype=np.uint64)
+            cap = max(4 * n, 1) if capacity is None else int(capacity)
+            occs = np.empty(max(cap, 1), dtype=np.uint64)
         rc = self._L.moni_gpu_seed_occs(self._h, _u64(seed_ref), _ptr(seed_len), n, int(max_per_direction), _u64(off), _u64(occs), cap,
                                         ctypes.byref(tr))
         if rc == -4 and capacity is None and n:      # capacity was a guess: the needed size is in off[n]

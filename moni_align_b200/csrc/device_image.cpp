@@ -242,6 +242,8 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
 void build_phi_tables(const FlatRlbwt& b, HostImage& img) {
     img.phi.clear();
     img.phi_inv.clear();
+    img.phi_dir.clear();
+    img.phi_inv_dir.clear();
     img.hdr.phi_n = 0;
     img.hdr.first_run_sample = b.R ? (b.samples_start[0] + 1) % b.n : 0;
     if (b.pred.empty() || b.pred_start.empty()) return;
@@ -261,6 +263,23 @@ void build_phi_tables(const FlatRlbwt& b, HostImage& img) {
         img.phi_inv[j].val = run_s + 1 < R ? b.samples_start[run_s + 1] : kPhiNone;
     }
     img.hdr.phi_n = R;
+    // bucket directories: about four keys per bucket, so a predecessor search is one directory word pair plus one or two
+    // lines of entries instead of log2(R) dependent probes
+    uint32_t shift = 0;
+    while (shift < 40 && ((b.n >> shift) > R / 4 + 1)) ++shift;
+    img.hdr.phi_shift = shift;
+    const uint64_t nb = (b.n >> shift) + 2;
+    auto fill = [&](const std::vector<PhiEntry>& tab, std::vector<uint32_t>& dir) {
+        dir.assign(nb, 0);
+        uint64_t j = 0;
+        for (uint64_t bk = 0; bk < nb; ++bk) {
+            const uint64_t lim = bk << shift;                 // first key of bucket bk
+            while (j < R && tab[j].key < lim) ++j;
+            dir[bk] = (uint32_t)j;
+        }
+    };
+    fill(img.phi, img.phi_dir);
+    fill(img.phi_inv, img.phi_inv_dir);
 }
 
 void build_grammar_table(const FlatSlp& g, const ExportOptions& opt, HostImage& img) {

@@ -101,6 +101,7 @@ struct ImageHeader {
     uint32_t slp_depth_max = 0;
     uint32_t init_row = 0, init_off = 0;         // pos = n - 1 as (row, offset)
     uint64_t phi_n = 0;                          // entries of each Phi table (R), 0 without the `moni align` index
+    uint32_t phi_shift = 0;                      // bucket b of a Phi directory covers keys in [b << phi_shift, (b + 1) << phi_shift)
     uint64_t first_run_sample = 0;               // (samples_start[0] + 1) % n   (include/ms/moni.hpp:330-332)
 };
 
@@ -115,10 +116,11 @@ struct HostImage {
     std::vector<SlpNode> nodes;
     std::vector<uint8_t> pool;
     std::vector<PhiEntry> phi, phi_inv; // R each, keys increasing (empty without the `moni align` index)
+    std::vector<uint32_t> phi_dir, phi_inv_dir;   // (n >> phi_shift) + 2 each: dir[b] = # keys < (b << phi_shift)
     uint64_t bytes() const {
         return rows.size() * sizeof(MoveRow) + row_pos.size() * 8 + crun_row.size() * 4 +
                slots.size() * sizeof(GapSlot) + nodes.size() * sizeof(SlpNode) + pool.size() +
-               (phi.size() + phi_inv.size()) * sizeof(PhiEntry);
+               (phi.size() + phi_inv.size()) * sizeof(PhiEntry) + (phi_dir.size() + phi_inv_dir.size()) * 4;
     }
 };
 

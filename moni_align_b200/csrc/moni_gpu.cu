@@ -404,7 +404,7 @@ struct Replica {
     int dev = 0;
     std::vector<Lane> lanes;
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
-    DevBuf phi, phi_inv;                                  // `moni align` indexes only
+    DevBuf phi, phi_inv, phi_dir, phi_inv_dir;            // `moni align` indexes only
     DevBuf occ_ref, occ_len, occ_off, occ_out, occ_flag, occ_cub;   // moni_gpu_seed_occs scratch
     DevBuf shard_off, shard_pos, shard_len, shard_ref;   // multi-GPU mems: a shard's records wait here for their global offset
     ImageView view;
@@ -415,7 +415,7 @@ struct Replica {
         cudaSetDevice(dev);
         rows.release(); row_pos.release(); crun_row.release(); slots.release(); nodes.release(); pool.release();
         sym.release(); counters.release();
-        phi.release(); phi_inv.release();
+        phi.release(); phi_inv.release(); phi_dir.release(); phi_inv_dir.release();
         occ_ref.release(); occ_len.release(); occ_off.release(); occ_out.release(); occ_flag.release(); occ_cub.release();
         shard_off.release(); shard_pos.release(); shard_len.release(); shard_ref.release();
         for (Lane& L : lanes) {
@@ -940,6 +940,8 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             upload(R->pool, img.pool, st);
             upload(R->phi, img.phi, st);
             upload(R->phi_inv, img.phi_inv, st);
+            upload(R->phi_dir, img.phi_dir, st);
+            upload(R->phi_inv_dir, img.phi_inv_dir, st);
             R->sym.reserve(sizeof(SymbolTables));
             CK(cudaMemcpyAsync(R->sym.p, &img.sym, sizeof(SymbolTables), cudaMemcpyHostToDevice, st));
             R->counters.reserve(sizeof(Counters));
@@ -955,6 +957,8 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             v.sym = R->sym.as<SymbolTables>();
             v.phi = R->phi.as<PhiEntry>();
             v.phi_inv = R->phi_inv.as<PhiEntry>();
+            v.phi_dir = R->phi_dir.as<uint32_t>();
+            v.phi_inv_dir = R->phi_inv_dir.as<uint32_t>();
             v.hdr = img.hdr;
             idx->reps.push_back(std::move(R));
         }
@@ -1100,6 +1104,11 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
         std::lock_guard<std::mutex> lock(R.mu);
         CK(cudaSetDevice(R.dev));
         cudaStream_t st = R.stream();
+        Lane& L0 = R.lanes[0];
+        L0.used = 0;
+        L0.take();
+        cudaEvent_t* e = L0.events.data();      // 0 start, 1 seeds on the device, 2 counted + scanned, 3 filled, 4 home
+        CK(cudaEventRecord(e[0], st));
         R.occ_ref.reserve(n_seeds * 8);
         R.occ_len.reserve(n_seeds * 4);
         R.occ_off.reserve((n_seeds + 1) * 8);
@@ -1107,6 +1116,7 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
         CK(cudaMemcpyAsync(R.occ_ref.p, seed_ref, n_seeds * 8, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(R.occ_len.p, seed_len, n_seeds * 4, cudaMemcpyHostToDevice, st));
         CK(cudaMemsetAsync(R.occ_flag.p, 0, 4, st));
+        CK(cudaEventRecord(e[1], st));
         const unsigned blocks = (unsigned)((n_seeds + 1 + kBlock - 1) / kBlock);
         k_occ_count<<<blocks, kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds, max_per_direction,
                                                R.occ_off.as<uint64_t>(), R.occ_flag.as<uint32_t>());
@@ -1116,6 +1126,7 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
         R.occ_cub.reserve(tmp);
         CK(cub::DeviceScan::ExclusiveSum(R.occ_cub.p, tmp, R.occ_off.as<uint64_t>(), R.occ_off.as<uint64_t>(), (int)(n_seeds + 1), st));
         g_launches += 2;
+        CK(cudaEventRecord(e[2], st));
         uint32_t flag = 0;
         CK(cudaMemcpyAsync(occ_offsets, R.occ_off.p, (n_seeds + 1) * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&flag, R.occ_flag.p, 4, cudaMemcpyDeviceToHost, st));
@@ -1131,8 +1142,14 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
                                                                                max_per_direction, R.occ_off.as<uint64_t>(), R.occ_out.as<uint64_t>());
         g_launches++;
         CK(cudaGetLastError());
+        CK(cudaEventRecord(e[3], st));
         CK(cudaMemcpyAsync(occs, R.occ_out.p, total * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(e[4], st));
         CK(cudaStreamSynchronize(st));
+        // moni_gpu_timing: t[0] seeds in, t[1] count walk + scan, t[2] fill walk (after the offsets went home), t[4] positions out
+        R.t[0] = ev_ms(e[0], e[1]); R.t[1] = ev_ms(e[1], e[2]); R.t[2] = ev_ms(e[2], e[3]); R.t[3] = 0; R.t[4] = ev_ms(e[3], e[4]);
+        R.t[5] = ev_ms(e[0], e[4]);
+        for (int k = 0; k < 6; ++k) idx->t[k] = R.t[k];
         return 0;
     });
 }

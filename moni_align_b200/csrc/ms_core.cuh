@@ -32,6 +32,8 @@ struct ImageView {
     const SymbolTables* sym = nullptr;
     const PhiEntry* phi = nullptr;       // `moni align` indexes only
     const PhiEntry* phi_inv = nullptr;
+    const uint32_t* phi_dir = nullptr;
+    const uint32_t* phi_inv_dir = nullptr;
     ImageHeader hdr;
 };
 
@@ -367,8 +369,10 @@ MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m
 // r_index::Phi (r_index.hpp:225-243) / ms_pointers::Phi_inv (moni.hpp:338-354) on a flattened table: jr = strict
 // predecessor of i among the keys, circular (sparse_sd_vector.hpp:168-172); delta = key < i ? i - key : i + 1;
 // result = (val + delta) % n.
-MONI_HD uint64_t phi_step(const PhiEntry* tab, uint64_t cnt, uint64_t n, uint64_t i) {
-    uint64_t lo = 0, hi = cnt;                       // # keys < i
+// The directory narrows the search to the bucket of i (keys in [b << shift, (b + 1) << shift), about four of them).
+MONI_HD uint64_t phi_step(const PhiEntry* tab, const uint32_t* dir, uint32_t shift, uint64_t cnt, uint64_t n, uint64_t i) {
+    const uint64_t bk = i >> shift;                  // i < n, the directory has (n >> shift) + 2 words
+    uint64_t lo = ld(dir + bk), hi = ld(dir + bk + 1);   // # keys < i lies in [lo, hi]
     while (lo < hi) {
         const uint64_t mid = lo + (hi - lo) / 2;
         if (ld(&tab[mid].key) < i) lo = mid + 1; else hi = mid;
@@ -404,13 +408,15 @@ MONI_HD uint64_t occ_walk(const ImageView& v, uint64_t pos, uint64_t len, uint64
     uint64_t k = 0;
     if (out) out[k] = pos;
     ++k;
+    if (pos >= n) return k;          // not a text position (a wrapped pointer): the reference's Phi is undefined there
     for (int dir = 0; dir < 2; ++dir) {
         const PhiEntry* tab = dir == 0 ? v.phi : v.phi_inv;
+        const uint32_t* bdir = dir == 0 ? v.phi_dir : v.phi_inv_dir;
         const uint64_t stop_at = dir == 0 ? v.hdr.first_run_sample : v.hdr.init_sample;   // get_first / get_last_run_sample
         uint64_t curr = pos, taken = 0;
         for (;;) {
             if (curr == stop_at) break;                                   // the reference returns lcp 0 here
-            const uint64_t next = phi_step(tab, v.hdr.phi_n, n, curr);
+            const uint64_t next = phi_step(tab, bdir, v.hdr.phi_shift, v.hdr.phi_n, n, curr);
             if (!((N - curr) >= len && (N - next) >= len)) break;         // lcp stays 0 (u64 arithmetic as in the reference)
             if (!lce_at_least(v, curr, next, len)) break;
             if (taken == cap) { if (truncated) *truncated = true; break; }

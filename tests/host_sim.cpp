@@ -47,7 +47,7 @@ int main(int argc, char** argv) {
         ImageView v;
         v.rows = img.rows.data(); v.row_pos = img.row_pos.data(); v.crun_row = img.crun_row.data();
         v.slots = img.slots.data(); v.nodes = img.nodes.data(); v.pool = img.pool.data(); v.sym = &img.sym; v.hdr = img.hdr;
-        v.phi = img.phi.data(); v.phi_inv = img.phi_inv.data();
+        v.phi = img.phi.data(); v.phi_inv = img.phi_inv.data(); v.phi_dir = img.phi_dir.data(); v.phi_inv_dir = img.phi_inv_dir.data();
 
         FILE* f = fopen(argv[2], "rb");
         if (!f) throw std::runtime_error("cannot open batch");
