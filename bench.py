@@ -151,6 +151,29 @@ def reference_arm(args) -> None:
     emit(line)
 
 
+_ORIG_AFFINITY: list = []
+
+
+def bind_near_gpu(local: int) -> str:
+    """Pins this rank's host threads to the CPUs NVML reports as local to its GPU, before any pinned buffer is allocated, so
+    that the page-locked batch buffers (first touched here) and the PCIe copies stay on the GPU's NUMA node.  Returns a note."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64 + 16)
+        near = {64 * w + b for w, x in enumerate(words) for b in range(64) if (x >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        _ORIG_AFFINITY.append(allowed)
+        use = near & allowed
+        if not use or use == allowed:
+            return f"no change ({len(near)} local CPUs, {len(allowed)} allowed)"
+        os.sched_setaffinity(0, use)
+        return f"bound to {len(use)} of {len(allowed)} allowed CPUs"
+    except Exception as e:  # best effort: never fail the bench over placement
+        return f"skipped: {type(e).__name__}: {e}"
+
+
 # ------------------------------------------------------------------------------------------ our arm
 def ours_arm(args) -> None:
     import torch
@@ -166,6 +189,8 @@ def ours_arm(args) -> None:
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_note = "off" if args.no_numa_bind else bind_near_gpu(local)
+    log(f"rank {rank}: CPU placement: {numa_note}")
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     w = workloads.WORKLOADS[args.workload]
@@ -294,6 +319,8 @@ def ours_arm(args) -> None:
     cpu = None
     if not args.no_cpu_baseline and world == 1 and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "mems")):
         try:
+            if _ORIG_AFFINITY:      # the reference gets every host core the process was given, not only the GPU's neighbours
+                os.sched_setaffinity(0, _ORIG_AFFINITY[0])
             pairs = max(1000, args.ref_reads // 2)
             sample = workloads.reads_of(args.workload, pairs=pairs)
             cores = os.cpu_count() or 1
@@ -331,7 +358,7 @@ def ours_arm(args) -> None:
                     "d2h_bytes_per_step": int(8 * (n_reads + 1) + 16 * n_mems), "ms_per_step_wall": e2e64_wall_ms / args.steps,
                     "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage64 / args.steps).tolist()))},
         "mem_records_per_step": n_mems,
-        "gpu_launches": int(launches), "options": args.opt, "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
+        "gpu_launches": int(launches), "options": args.opt, "cpu_placement": numa_note, "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
     }
     emit(line)
     if world > 1:
@@ -348,6 +375,7 @@ def main():
     ap.add_argument("--pairs", type=int, default=0, help="read pairs per GPU per step (default: the workload's)")
     ap.add_argument("--ref-reads", type=int, default=100_000, help="reads in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true", help="do not pin each rank to the CPUs local to its GPU")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (moni_gpu_set_option), repeatable")
     args = ap.parse_args()

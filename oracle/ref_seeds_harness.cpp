@@ -26,7 +26,11 @@ int main(int argc, char** argv) {
     if (argc != 5 && argc != 6) { fprintf(stderr, "usage: ref_seeds prefix reads.fq min_len out [occs]\n"); return 2; }
     const bool with_occs = argc == 6;
     const size_t min_len = (size_t)atoll(argv[3]);
+#ifdef REF_SEEDS_LCP   // the sampled-LCP index: <prefix>.thrbv.full.lcp.ms, occurrences through moni_lcp::Phi_lcp / Phi_inv_lcp
+    seed_finder<plain_slp_t, moni_lcp<>> sf(argv[1], min_len, false, 5000);
+#else
     seed_finder<plain_slp_t, ms_pointers<>> sf(argv[1], min_len, false, 5000);
+#endif
     gzFile fp = gzopen(argv[2], "r");
     if (!fp) { fprintf(stderr, "cannot open %s\n", argv[2]); return 1; }
     FILE* out = fopen(argv[4], "w");

@@ -80,11 +80,13 @@ def run_host_sim(exe, prefix, flat, offs, tmpdir, extra=()):
     return res
 
 
-def full_only_prefix(case, tmpdir):
-    """A prefix under tmpdir that holds ONLY the `moni align` index of a golden case (+ the grammar)."""
+def full_only_prefix(case, tmpdir, lcp=False):
+    """A prefix under tmpdir that holds ONLY a `moni align` index of a golden case (+ the grammar): .thrbv.full.ms, or the
+    sampled-LCP variant .thrbv.full.lcp.ms."""
     import shutil
-    pre = os.path.join(str(tmpdir), case + "_full.fa")
-    shutil.copy(os.path.join(GOLDEN, case + ".fa.thrbv.full.ms"), pre + ".thrbv.full.ms")
+    ext = ".thrbv.full.lcp.ms" if lcp else ".thrbv.full.ms"
+    pre = os.path.join(str(tmpdir), case + ("_lcp.fa" if lcp else "_full.fa"))
+    shutil.copy(os.path.join(GOLDEN, case + ".fa" + ext), pre + ext)
     shutil.copy(os.path.join(GOLDEN, case + ".fa.plain.slp"), pre + ".plain.slp")
     return pre
 

@@ -60,10 +60,11 @@ def make_case(name: str, records, seed: int, n_reads: int, trivial_grammar: bool
             os.remove(os.path.join(HERE, f))
 
 
-def main():
+def cases():
+    """(name, records, make_case keyword arguments) of the three fixtures, in generation order (the rng is shared)."""
     rng = np.random.default_rng(7)
     # 1: small pangenome, ACGT only
-    make_case("pan4", synth.pangenome(6000, 4, 11, 1e-2, 2e-3), seed=12, n_reads=60)
+    yield "pan4", synth.pangenome(6000, 4, 11, 1e-2, 2e-3), dict(seed=12, n_reads=60)
     # 2: text with N stretches and a fifth frequent symbol -> exercises the general path
     recs = synth.pangenome(5000, 3, 21, 2e-2, 2e-3)
     for r in recs:
@@ -71,10 +72,15 @@ def main():
             p = int(rng.integers(0, r.shape[0] - 40))
             r[p:p + int(rng.integers(1, 30))] = ord("N")
         r[rng.integers(0, r.shape[0], size=60)] = ord("R")
-    make_case("withN", recs, seed=22, n_reads=40)
+    yield "withN", recs, dict(seed=22, n_reads=40)
     # 3: two-letter text (fewer than four table symbols), trivial grammar, long runs
     ab = np.frombuffer(b"AC", dtype=np.uint8)[(rng.random(3000) < 0.2).astype(np.int64)]
-    make_case("twoletter", [np.concatenate([ab, ab[:2000], ab[500:2500]])], seed=32, n_reads=30, trivial_grammar=True, length=80)
+    yield "twoletter", [np.concatenate([ab, ab[:2000], ab[500:2500]])], dict(seed=32, n_reads=30, trivial_grammar=True, length=80)
+
+
+def main():
+    for name, records, kw in cases():
+        make_case(name, records, **kw)
 
 
 if __name__ == "__main__":

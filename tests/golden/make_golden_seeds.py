@@ -20,7 +20,38 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 BIN = os.path.join(ROOT, "oracle", "_ref", "bin")
 
 
+def lcp_variant():
+    """<case>.fa.thrbv.full.lcp.ms: the sampled-LCP align index (reference rlebwt_ms_full_build without -n).  It needs the
+    builder's .slcp, which is not kept under tests/golden/, so the text is regenerated from its seed (make_golden.cases), the
+    builder is re-run, and its run files are checked against the committed ones.  The reference's LCP-based enumeration
+    (seed_finder<plain_slp_t, moni_lcp<>>, ref_seeds_lcp) must print exactly the committed .seeds25 / .occs12."""
+    import filecmp
+    import sys
+    sys.path.insert(0, HERE)
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import make_golden
+    import synth
+    for case, records, kw in make_golden.cases():
+        with tempfile.TemporaryDirectory() as td:
+            fa = os.path.join(td, case + ".fa")
+            synth.write_fasta(fa, records)
+            for cmd in ([os.path.join(BIN, "newscanNT.x"), fa, "-w", "10", "-p", "100", "-f"], [os.path.join(BIN, "pfp_thresholds"), fa, "-w", "10", "-r"]):
+                subprocess.run(cmd, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            for ext in (".bwt.heads", ".bwt.len", ".ssa", ".esa", ".thr_pos"):
+                assert filecmp.cmp(fa + ext, os.path.join(HERE, case + ".fa" + ext), shallow=False), (case, ext)
+            subprocess.run([os.path.join(BIN, "rlebwt_ms_full_build"), fa], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            shutil.copy(os.path.join(HERE, case + ".fa.plain.slp"), td)
+            open(fa + ".ldx", "wb").close()
+            fq = os.path.join(HERE, case + ".fq")
+            subprocess.run([os.path.join(BIN, "ref_seeds_lcp"), fa, fq, "25", os.path.join(td, "s25")], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            subprocess.run([os.path.join(BIN, "ref_seeds_lcp"), fa, fq, "12", os.path.join(td, "o12"), "occs"], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            assert filecmp.cmp(os.path.join(td, "s25"), os.path.join(HERE, case + ".seeds25"), shallow=False), case
+            assert filecmp.cmp(os.path.join(td, "o12"), os.path.join(HERE, case + ".occs12"), shallow=False), case
+            shutil.copy(fa + ".thrbv.full.lcp.ms", HERE)
+
+
 def main():
+    lcp_variant()
     for case in ("pan4", "withN", "twoletter"):
         with tempfile.TemporaryDirectory() as td:
             for f in os.listdir(HERE):

@@ -7,7 +7,7 @@
 //   out.bin   : u64 ptr[total], u64 len[total], u64 mem_offsets[n_reads+1], u64 mem_pos[k], u64 mem_len[k], u64 counters[8]
 //               and, when seed_min_len is given: u64 seed_offsets[n_reads+1], u64 seed_ref[s], u64 seed_len[s], u64 seed_qpos[s]
 //               and, when the index has Phi structures: u64 occ_offsets[s+1], u64 occs[...]  (occ_walk per seed, cap 2^20)
-// If <prefix>.thrbv.ms does not exist, <prefix>.thrbv.full.ms (the `moni align` index) is read.
+// If <prefix>.thrbv.ms does not exist, <prefix>.thrbv.full.ms or .thrbv.full.lcp.ms (the `moni align` indexes) is read.
 #include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
@@ -23,14 +23,14 @@ int main(int argc, char** argv) {
     try {
         FlatRlbwt bwt;
         FlatSlp slp;
-        {
-            const std::string plain = std::string(argv[1]) + ".thrbv.ms", full = std::string(argv[1]) + ".thrbv.full.ms";
-            FILE* probe = fopen(plain.c_str(), "rb");
-            FILE* probe2 = probe ? nullptr : fopen(full.c_str(), "rb");
-            if (probe) fclose(probe);
-            if (probe2) fclose(probe2);
-            if (!probe && probe2) read_thrbv_ms(full, bwt, true);
-            else read_thrbv_ms(plain, bwt);
+        {   // same choice as moni_gpu_index_load: the ms/mems index, else one of the two `moni align` indexes
+            const char* exts[3] = {".thrbv.ms", ".thrbv.full.ms", ".thrbv.full.lcp.ms"};
+            int which = 0;
+            for (int k = 0; k < 3; ++k) {
+                FILE* probe = fopen((std::string(argv[1]) + exts[k]).c_str(), "rb");
+                if (probe) { fclose(probe); which = k; break; }
+            }
+            read_thrbv_ms(std::string(argv[1]) + exts[which], bwt, which != 0);
         }
         read_plain_slp(std::string(argv[1]) + ".plain.slp", slp);
         ExportOptions opt;

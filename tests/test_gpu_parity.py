@@ -371,6 +371,24 @@ def test_seeds_random_reads_chunked_and_sharded(m, oracle_mod):
 
 
 @pytest.mark.parametrize("case", CASES)
+def test_lcp_align_index_on_the_gpu(case, m, oracle_mod, tmp_path):
+    """The default `moni align` index (.thrbv.full.lcp.ms): same seeds, same occurrence lists as the reference's
+    LCP-based enumeration (identical to .seeds25 / .occs12, see make_golden_seeds.py::lcp_variant)."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    ix = m.MoniIndex(full_only_prefix(case, tmp_path, lcp=True))
+    so, ref, qpos, ln = ix.find_mems(flat, offs, 25)
+    assert m.format_seeds(names, so, ref, ln, qpos) == open(pre + ".seeds25", "rb").read()
+    so, ref, qpos, ln = ix.find_mems(flat, offs, 12)
+    oo, occs, trunc = ix.find_MEM_occs(ref, ln)
+    assert not trunc
+    assert oracle_mod.format_occs(names, so, ref, ln, qpos, oo, occs) == open(pre + ".occs12", "rb").read()
+    ix.close()
+
+
+@pytest.mark.parametrize("case", CASES)
 def test_seed_occurrences_equal_reference_find_MEM_occs(case, m, indexes, oracle_mod, tmp_path):
     """moni_gpu_seeds + moni_gpu_seed_occs on the `moni align` index == the reference's find_mems + find_MEM_occs
     (tests/golden/<case>.occs12); per-direction cap and capacity errors behave as documented."""

@@ -165,3 +165,19 @@ def test_occurrence_walk_needs_the_align_index(host_sim, tmp_path):
     names, seqs = read_fastq(pre + ".fq")
     flat, offs = pack(seqs[:5])
     assert len(run_host_sim(host_sim, pre + ".fa", flat, offs, tmp_path, (0, 8, 12))) == 10
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_lcp_align_index_gives_the_same_seeds_and_occurrences(case, host_sim, oracle_mod, tmp_path):
+    """.thrbv.full.lcp.ms (the default `moni align` index: one more trailing vector, the sampled LCPs) loads, and seeds and
+    occurrence lists are the ones the reference's LCP-based enumeration prints (verified identical to .seeds25 / .occs12 when
+    the fixture was generated, tests/golden/make_golden_seeds.py::lcp_variant)."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    res = run_host_sim(host_sim, full_only_prefix(case, tmp_path, lcp=True), flat, offs, tmp_path, (1 << 30, 8, 12))
+    so, ref, ln, qpos, oo, occs = res[6:12]
+    assert oracle_mod.format_occs(names, so, ref, ln, qpos, oo, occs) == open(pre + ".occs12", "rb").read()
+    d = oracle_mod.read_thrbv_ms(os.path.join(GOLDEN, case + ".fa.thrbv.full.lcp.ms"), full=True)
+    assert d["slcp"].shape[0] == d["R"]
