@@ -25,7 +25,7 @@ from typing import Iterable, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmoni_gpu.so")
+LIB_PATH = os.environ.get("MONI_GPU_LIB") or os.path.join(_HERE, "libmoni_gpu.so")   # the override is for A/B builds of the same library
 
 _u64p = ctypes.POINTER(ctypes.c_uint64)
 _lib = None

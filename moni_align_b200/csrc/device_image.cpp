@@ -299,17 +299,32 @@ void build_grammar_table(const FlatSlp& g, const ExportOptions& opt, HostImage& 
     std::vector<uint8_t>& pool = img.pool;
     pool.clear();
     std::vector<uint32_t> stack;
+    constexpr uint64_t kCopyMin = 24;                   // shorter expansions are cheaper to walk than to look up
+    std::vector<uint64_t> first_at(NR, ~0ULL);          // pool offset of the first complete expansion of a rule
     auto leaf_ref = [&](uint32_t v) -> uint32_t {
         if (ref[v] != 0xFFFFFFFFu) return ref[v];
         while (pool.size() % align) pool.push_back(0);
         const uint64_t off = pool.size() >> img.hdr.pool_shift;
         if (off >= kLeafBit) throw std::runtime_error("exporter: literal pool exceeds the addressable range; lower leaf_len");
+        // depth-first expansion; a variable met again is copied from where its expansion was first written (the grammar of
+        // a pangenome reuses long variables: this turns ~|T| stack operations into block copies)
         stack.clear();
         stack.push_back(v);
         while (!stack.empty()) {
             const uint32_t x = stack.back();
             stack.pop_back();
             if (x < A) { pool.push_back(g.alph[x]); continue; }
+            const uint64_t len = g.explen[x - A];
+            if (len >= kCopyMin) {
+                uint64_t& fp = first_at[x - A];
+                if (fp != ~0ULL) {
+                    const size_t old = pool.size();
+                    pool.resize(old + len);
+                    memcpy(pool.data() + old, pool.data() + fp, len);     // [fp, fp + len) was complete before `old`
+                    continue;
+                }
+                fp = pool.size();
+            }
             stack.push_back(g.right[x - A]);
             stack.push_back(g.left[x - A]);
         }

@@ -37,6 +37,9 @@ using namespace moni;
 // ================================================================================ kernels
 namespace {
 
+#ifndef MONI_P1_MINBLOCKS
+#define MONI_P1_MINBLOCKS 1          // resident CTAs per SM the pass-1 kernel is compiled for (register cap = 65536 / (128 * this))
+#endif
 constexpr int kBlock = 128;          // 4 warps; warps never synchronise with each other after the prologue
 constexpr int kTile = 32;            // steps staged per refill
 constexpr int kTileStride = 36;      // bytes per read in the tile: 9 words, odd -> conflict-free column reads
@@ -100,7 +103,7 @@ __global__ void k_warp_extent(const uint64_t* __restrict__ offs, const uint32_t*
 
 // ---- pass 1: MS pointers -------------------------------------------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock) k_ms_pointers(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
+__global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
                                                         uint64_t* __restrict__ ptr_t, Counters* g) {
     __shared__ uint8_t tcode[256];
     __shared__ __align__(16) uint8_t tiles[kBlock / 32][32 * kTileStride];
