@@ -413,3 +413,34 @@ def test_seed_occurrences_equal_reference_find_MEM_occs(case, m, indexes, oracle
         indexes[case].find_MEM_occs(ref[:1], ln[:1])
     assert e.value.code == -1
     ix.close()
+
+
+def test_concurrent_callers_on_one_index(m, indexes, oracle_mod):
+    """The library is thread-safe per index (one mutex per GPU replica): four host threads calling ms, mems,
+    packed mems and seeds on the same index at once each get the bits of a lone call."""
+    import threading
+    import synth
+    pre = os.path.join(GOLDEN, "pan4.fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = list(synth.short_reads(text, 4000, 110, 51, err=0.02)) + synth.long_reads(text, 20, 52, mean=800, sd=300, lo=60, hi=2000)
+    flat, offs = m.pack_reads(reads)
+    ix = indexes["pan4"]
+    want = {"ms": ix.matching_statistics(flat, offs), "mems": ix.maxrimal_exact_matches(flat, offs),
+            "packed": ix.maxrimal_exact_matches_packed(flat, offs), "seeds": ix.find_mems(flat, offs, 15)}
+    calls = {"ms": lambda: ix.matching_statistics(flat, offs), "mems": lambda: ix.maxrimal_exact_matches(flat, offs),
+             "packed": lambda: ix.maxrimal_exact_matches_packed(flat, offs), "seeds": lambda: ix.find_mems(flat, offs, 15)}
+    bad = []
+
+    def worker(name):
+        for _ in range(5):
+            got = calls[name]()
+            if not all(np.array_equal(a, b) for a, b in zip(got, want[name])):
+                bad.append(name)
+
+    th = [threading.Thread(target=worker, args=(k,)) for k in calls]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not bad, bad
