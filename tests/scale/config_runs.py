@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Parity + throughput of the BASELINE.json configurations that are not the bench line (run on the GPU box):
 
-    python tools/config_runs.py [--workload cfg2s] [--out gpurun_out/config_runs.json]
+    python tests/scale/config_runs.py [--workload cfg2s] [--out gpurun_out/config_runs.json]
 
   cfg1-like  `ms`   on 100k x 150 bp reads (1 % substitutions, half reverse-complemented)
   cfg5-like  `ms` + `mems` on ragged ONT-like reads (mean 10 kbp, 15 % errors): warp divergence, long scans, the
@@ -9,7 +9,7 @@
 Each case: results through the C ABI with pinned host buffers, wall-clock throughput, and a differential check of a
 read sample against the UNMODIFIED reference binaries (oracle/_ref/bin/ms, mems) on the same index files -- the
 files the reference writes are compared byte for byte with the ones formatted from the GPU results.
-Input preparation and checking only; nothing here is on the product path.
+Checking at scale (test infrastructure: it runs the reference binaries and the CPU oracle as the checker); nothing here is on the product path.
 """
 from __future__ import annotations
 
@@ -22,7 +22,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 import build_index  # noqa: E402

@@ -1,14 +1,14 @@
 #!/usr/bin/env python
 """The `moni align` seed stage at scale on the GPU box:
 
-    python tools/occ_run.py [--prefix data/cfg4s_full/ref.fa] [--workload cfg4s] [--pairs 1000000]
+    python tests/scale/occ_run.py [--prefix data/cfg4s_full/ref.fa] [--workload cfg4s] [--pairs 1000000]
 
   seeds        moni_gpu_seeds (seed_finder::find_mems, min_len 25) over the read batch, pinned host buffers
   occurrences  moni_gpu_seed_occs (seed_finder::find_MEM_occs, unfiltered) for every seed: Phi / Phi^-1 walks + bounded LCE
   checks       a sample of seeds against the CPU oracle's restatement; for ALL occurrences T[occ : occ+len] == T[pos : pos+len]
                at three probe offsets, the seed's own position first, no position twice within a seed
 The index prefix holds the reference builder's `.thrbv.full.ms` (rlebwt_ms_full_build -n) and `.plain.slp`.
-Input preparation and checking only; nothing here is on the product path.
+Checking at scale (test infrastructure: it runs the reference binaries and the CPU oracle as the checker); nothing here is on the product path.
 """
 from __future__ import annotations
 
@@ -20,7 +20,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 import workloads  # noqa: E402

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """BASELINE.json configs[2] (and a configs[4]-like ragged case on the same index) on the GPU box:
 
-    python tools/scale_run.py [--workload cfg3] [--out gpurun_out/scale_run.json]
+    python tests/scale/scale_run.py [--workload cfg3] [--out gpurun_out/scale_run.json]
 
 The cfg3 index (40 Mbp x 32 haplotypes, n = 1.28 G) is too large to build inside a gpurun call with the reference's
 pfp_thresholds (~10 min) AND to ship complete (the snapshot is limited to 512 MiB): `<prefix>.thrbv.ms` (the reference
@@ -18,7 +18,7 @@ Stages (each records its outcome in the JSON as soon as it is known):
               through the drop-in moni_align_b200/bin/{ms,mems}: the output files must be byte-identical
   seeds       moni_gpu_seeds on a sample against the CPU oracle's restatement of seed_finder::find_mems
   long        ragged ONT-like reads (mean 10 kbp, 15 % errors): e2e rates and file parity against the reference
-Input preparation and checking only; nothing here is on the product path.
+Checking at scale (test infrastructure: it runs the reference binaries and the CPU oracle as the checker); nothing here is on the product path.
 """
 from __future__ import annotations
 
@@ -32,7 +32,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 import build_index  # noqa: E402

@@ -31,7 +31,7 @@ WORKLOADS = {
                   pairs=1_000_000, insert=(400, 50), err=0.01,
                   desc="cfg2 stand-in scaled to the snapshot limit: 28 Mbp x 7 haplotypes, mems on 1M x 2 x 150 bp paired-end reads"),
     # BASELINE.json configs[2]: "synthetic 32-haplotype chr21-scale pangenome, MS+MEMs on 10M 150 bp reads, 1 B200".  The index
-    # (~1.28 Gbp) is too large for the gpurun snapshot, so it is built on the GPU box by tools/scale_run.py.
+    # (~1.28 Gbp) is too large for the gpurun snapshot, so it is built on the GPU box by tests/scale/scale_run.py.
     "cfg3": dict(base_len=40_000_000, haplotypes=32, seed=301, snp=1e-3, indel=1e-4, read_seed=302, read_len=150,
                  pairs=5_000_000, insert=(400, 50), err=0.01,
                  desc="cfg3: 40 Mbp x 32 haplotypes (SNP 1e-3, indel 1e-4), 10M x 150 bp reads, 1% substitutions"),
