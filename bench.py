@@ -216,13 +216,13 @@ def ours_arm(args) -> None:
     n_reads, read_len = reads.shape
     total = n_reads * read_len
     # pinned host buffers for the end-to-end leg
-    h_seqs = m.pinned_empty(total, np.uint8)
+    h_seqs = m.pinned_empty(total, np.uint8, gpu=local)
     h_seqs[:] = reads.reshape(-1)
-    h_offs = m.pinned_empty(n_reads + 1, np.uint64)
+    h_offs = m.pinned_empty(n_reads + 1, np.uint64, gpu=local)
     h_offs[:] = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(read_len)
-    h_mo = m.pinned_empty(n_reads + 1, np.uint64)
-    h_mp = m.pinned_empty(total, np.uint64)
-    h_ml = m.pinned_empty(total, np.uint64)
+    h_mo = m.pinned_empty(n_reads + 1, np.uint64, gpu=local)
+    h_mp = m.pinned_empty(total, np.uint64, gpu=local)
+    h_ml = m.pinned_empty(total, np.uint64, gpu=local)
     del reads
 
     def barrier():
@@ -259,8 +259,8 @@ def ours_arm(args) -> None:
 
     # ---- end-to-end leg through the C ABI with host buffers: moni_gpu_mems32 (32-bit record fields) is the headline,
     # moni_gpu_mems (64-bit fields, twice the device->host bytes) is reported beside it
-    h_mp32 = m.pinned_empty(total, np.uint32)
-    h_ml32 = m.pinned_empty(total, np.uint32)
+    h_mp32 = m.pinned_empty(total, np.uint32, gpu=local)
+    h_ml32 = m.pinned_empty(total, np.uint32, gpu=local)
 
     def e2e_leg(out):
         call = ix.maxrimal_exact_matches if len(out) == 3 else ix.maxrimal_exact_matches_packed
@@ -358,7 +358,7 @@ def ours_arm(args) -> None:
                     "d2h_bytes_per_step": int(8 * (n_reads + 1) + 16 * n_mems), "ms_per_step_wall": e2e64_wall_ms / args.steps,
                     "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage64 / args.steps).tolist()))},
         "mem_records_per_step": n_mems,
-        "gpu_launches": int(launches), "options": args.opt, "cpu_placement": numa_note, "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
+        "gpu_launches": int(launches), "options": args.opt, "cpu_placement": numa_note, "host_buffers": f"pinned, NUMA node of the GPU ({m.load_library().moni_gpu_numa_node(local)})", "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
     }
     emit(line)
     if world > 1:

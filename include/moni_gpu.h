@@ -96,6 +96,13 @@ int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offset
 int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
                        uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity, int* truncated);
 
+/* moni_gpu_ms with 7 bytes of results per base instead of 16 (the call is bound by the device->host copy): the pointer's low
+ * 40 bits as ptr_lo (u32) + ptr_hi (u8), the length as u16.  pointer = lo | hi << 32, and if that is >= 2^40 - 2^31 subtract
+ * 2^40 in 64-bit arithmetic: such a value is one of the reference's wrapped pointers 2^64 - k (its `sample--` after an absent
+ * symbol set sample to 0, ms_pointers.hpp:470-481).  Needs reads shorter than 65536 bases and n <= 2^40 - 2^31 (else EINVAL). */
+int moni_gpu_ms_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
+                       uint32_t* ptr_lo, uint8_t* ptr_hi, uint16_t* lengths);
+
 /* Event counters accumulated over all calls since the last reset, when counting is enabled
  * (moni_gpu_set_option("count", "1"); off by default, it costs a few percent):
  * c[0]=bases, c[1]=threshold jumps (ms_pointers.hpp:482-505 taken), c[2]=LCE restarts,
@@ -118,6 +125,11 @@ int moni_gpu_set_option(const char* key, const char* value);
 /* Pinned host memory for batch buffers (cudaHostAlloc / cudaFreeHost). */
 void* moni_gpu_host_alloc(uint64_t bytes);
 void moni_gpu_host_free(void* p);
+/* Same, placed on the NUMA node of CUDA device `gpu` (sysfs numa_node of its PCI function; plain moni_gpu_host_alloc when the
+ * node is unknown or the policy call is refused), so copies to and from that GPU stay off the socket interconnect: what a
+ * caller feeding several GPUs of a two-socket host wants for its batch buffers.  moni_gpu_numa_node returns that node or -1. */
+void* moni_gpu_host_alloc_near(int gpu, uint64_t bytes);
+int moni_gpu_numa_node(int gpu);
 
 /* ---- resident batches: inputs stay in HBM across runs (pipelines, kernel-only measurement) ----
  * gpu_slot indexes the `gpus` list given to moni_gpu_index_load. */

@@ -39,7 +39,7 @@ class MoniGpuError(RuntimeError):
 
 EXPORTS = [
     "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems", "moni_gpu_mems32",
-    "moni_gpu_mems_packed", "moni_gpu_seeds", "moni_gpu_seed_occs",
+    "moni_gpu_mems_packed", "moni_gpu_seeds", "moni_gpu_seed_occs", "moni_gpu_ms_packed", "moni_gpu_host_alloc_near", "moni_gpu_numa_node",
     "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
@@ -72,6 +72,10 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_set_option.argtypes = [cc, cc]
     L.moni_gpu_host_alloc.argtypes = [ctypes.c_uint64]
     L.moni_gpu_host_alloc.restype = vp
+    L.moni_gpu_host_alloc_near.argtypes = [ci, ctypes.c_uint64]
+    L.moni_gpu_host_alloc_near.restype = vp
+    L.moni_gpu_numa_node.argtypes = [ci]
+    L.moni_gpu_ms_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, vp, vp, vp]
     L.moni_gpu_host_free.argtypes = [vp]
     L.moni_gpu_host_free.restype = None
     L.moni_gpu_batch_create.argtypes = [vp, ci, vp, _u64p, ctypes.c_uint64, ctypes.POINTER(vp)]
@@ -100,12 +104,13 @@ def launch_count() -> int:
     return int(load_library().moni_gpu_launch_count())
 
 
-def pinned_empty(n: int, dtype) -> np.ndarray:
-    """numpy array over cudaHostAlloc memory.  The allocation lives until release_pinned() or exit."""
+def pinned_empty(n: int, dtype, gpu: int | None = None) -> np.ndarray:
+    """numpy array over cudaHostAlloc memory (on the NUMA node of CUDA device `gpu` when given).  The allocation lives until
+    release_pinned() or exit."""
     L = load_library()
     dt = np.dtype(dtype)
     nbytes = max(int(n) * dt.itemsize, 1)
-    p = L.moni_gpu_host_alloc(nbytes)
+    p = L.moni_gpu_host_alloc(nbytes) if gpu is None else L.moni_gpu_host_alloc_near(int(gpu), nbytes)
     if not p:
         raise MoniGpuError(-4, "pinned allocation failed")
     buf = (ctypes.c_uint8 * nbytes).from_address(p)
@@ -188,6 +193,19 @@ class MoniIndex:
             ptr, ln = out
         _check(self._L.moni_gpu_ms(self._h, _ptr(seqs), _u64(offsets), nr, _u64(ptr), _u64(ln)))
         return ptr[:total], ln[:total]
+
+    def matching_statistics_packed(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
+        """(ptr_lo uint32, ptr_hi uint8, lengths uint16) -- moni_gpu_ms_packed; unpack_pointers() gives the u64 pointers."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        nr = offsets.shape[0] - 1
+        if out is None:
+            lo, hi, ln = np.empty(max(total, 1), np.uint32), np.empty(max(total, 1), np.uint8), np.empty(max(total, 1), np.uint16)
+        else:
+            lo, hi, ln = out
+        _check(self._L.moni_gpu_ms_packed(self._h, _ptr(seqs), _u64(offsets), nr, _ptr(lo), _ptr(hi), _ptr(ln)))
+        return lo[:total], hi[:total], ln[:total]
 
     def maxrimal_exact_matches(self, seqs: np.ndarray, offsets: np.ndarray, out=None, dtype=np.uint64):
         """(mem_offsets uint64[n+1], mem_pos, mem_len) -- mems_c::maxrimal_exact_matches for every read;
@@ -355,3 +373,12 @@ def format_seeds(names: Iterable[bytes], seed_offsets, seed_ref, seed_len, seed_
         a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
         out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d,%d) " % (int(seed_ref[t]), int(seed_len[t]), int(seed_qpos[t])) for t in range(a, b)) + b"\n")
     return b"".join(out)
+
+
+def unpack_pointers(ptr_lo: np.ndarray, ptr_hi: np.ndarray) -> np.ndarray:
+    """u64 pointers from the two halves moni_gpu_ms_packed returns (values >= 2^40 - 2^31 are the reference's wrapped 2^64 - k)."""
+    v = ptr_lo.astype(np.uint64) | (ptr_hi.astype(np.uint64) << np.uint64(32))
+    wrapped = v >= np.uint64((1 << 40) - (1 << 31))
+    with np.errstate(over="ignore"):
+        v[wrapped] = v[wrapped] - np.uint64(1 << 40)
+    return v

@@ -9,6 +9,7 @@
 // contiguous 256-byte line.  The per-read arithmetic lives in ms_core.cuh.
 // No tensor cores, no CPU fallback: without a device every entry point fails.
 #include <cuda_runtime.h>
+#include <sys/syscall.h>
 #include <unistd.h>
 
 #include <algorithm>
@@ -16,6 +17,7 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
+#include <cctype>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -176,9 +178,14 @@ __global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_
 // ms: warp-transposed (pointer, length) -> the caller's layout (u64 each, laid out like seqs).  One warp per 32 reads,
 // 32 steps at a time through shared memory: 256-byte loads along the lanes, 256-byte stores along each read.
 constexpr int kUtBlock = 64;
+// PACKED: 7 bytes per base instead of 16 -- the low 40 bits of the pointer as u32 + u8 (a pointer is a text position < n,
+// or 2^64 - k with k < 2^31 after the reference's `sample--` wrapped: both survive `& (2^40 - 1)` when n <= 2^40 - 2^31)
+// and the length as u16 (reads shorter than 65536 bases).
+template <bool PACKED>
 __global__ void __launch_bounds__(kUtBlock) k_ms_untranspose(ChunkMap cm, const uint64_t* __restrict__ ptr_t,
                                                              const uint32_t* __restrict__ len_t, uint64_t* __restrict__ ptr_out,
-                                                             uint64_t* __restrict__ len_out) {
+                                                             uint64_t* __restrict__ len_out, uint32_t* __restrict__ lo_out,
+                                                             uint8_t* __restrict__ hi_out, uint16_t* __restrict__ len16_out) {
     __shared__ uint64_t tp[kUtBlock / 32][32 * 33];
     __shared__ uint32_t tl[kUtBlock / 32][32 * 33];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
@@ -210,8 +217,15 @@ __global__ void __launch_bounds__(kUtBlock) k_ms_untranspose(ChunkMap cm, const 
             const uint32_t step = t0 + lane;
             if (step < m_r) {
                 const uint64_t at = o_r + (m_r - 1 - step);
-                ptr_out[at] = P[lane * 33 + rr];
-                len_out[at] = Q[lane * 33 + rr];
+                const uint64_t pv = P[lane * 33 + rr];
+                if (PACKED) {
+                    lo_out[at] = (uint32_t)pv;
+                    hi_out[at] = (uint8_t)(pv >> 32);
+                    len16_out[at] = (uint16_t)Q[lane * 33 + rr];
+                } else {
+                    ptr_out[at] = pv;
+                    len_out[at] = Q[lane * 33 + rr];
+                }
             }
         }
         __syncwarp();
@@ -358,9 +372,10 @@ struct Scratch {   // device buffers of one chunk
     DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, wbase, ptr_t, out_ptr, out_len, rec, counts, moff, mem_pos, mem_len, cub;
     DevBuf rec_ref, mem_ref;     // seeds only
     DevBuf len_t;                // ms only: lengths, warp-transposed like ptr_t
+    DevBuf out_hi;               // ms, packed outputs: bits 32..39 of the pointers (out_ptr then holds the u32 halves, out_len u16 lengths)
     void release() {
         for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &wbase, &ptr_t, &out_ptr, &out_len, &rec, &counts, &moff,
-                          &mem_pos, &mem_len, &cub, &rec_ref, &mem_ref, &len_t})
+                          &mem_pos, &mem_len, &cub, &rec_ref, &mem_ref, &len_t, &out_hi})
             b->release();
     }
     void reserve(const ChunkPlan& p, bool ms, bool mems, bool seeds = false) {
@@ -372,7 +387,7 @@ struct Scratch {   // device buffers of one chunk
             keys_in.reserve(p.n * 4); keys_out.reserve(p.n * 4); vals_in.reserve(p.n * 4); perm.reserve(p.n * 4);
             wbase.reserve((p.n_warps() + 1) * 8);
         }
-        if (ms) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); len_t.reserve(p.ptr_entries() * 4); }
+        if (ms) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); len_t.reserve(p.ptr_entries() * 4); out_hi.reserve(p.bases + 16); }
         if (mems) {
             rec.reserve(p.bases * 8 + 16);
             counts.reserve((p.n + 1) * 4);
@@ -530,11 +545,15 @@ void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, int mode, cudaStre
 }
 
 // ms: pointers and lengths from the warp-transposed buffers to the caller's layout
-void launch_untranspose(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
+void launch_untranspose(Scratch& S, const ChunkPlan& p, cudaStream_t st, bool packed = false) {
     if (!p.n) return;
     const dim3 grid((unsigned)((p.n_warps() * 32 + kUtBlock - 1) / kUtBlock));
-    k_ms_untranspose<<<grid, kUtBlock, 0, st>>>(chunk_map(S, p), S.ptr_t.as<uint64_t>(), S.len_t.as<uint32_t>(), S.out_ptr.as<uint64_t>(),
-                                                S.out_len.as<uint64_t>());
+    if (packed)
+        k_ms_untranspose<true><<<grid, kUtBlock, 0, st>>>(chunk_map(S, p), S.ptr_t.as<uint64_t>(), S.len_t.as<uint32_t>(), nullptr, nullptr,
+                                                          S.out_ptr.as<uint32_t>(), S.out_hi.as<uint8_t>(), S.out_len.as<uint16_t>());
+    else
+        k_ms_untranspose<false><<<grid, kUtBlock, 0, st>>>(chunk_map(S, p), S.ptr_t.as<uint64_t>(), S.len_t.as<uint32_t>(), S.out_ptr.as<uint64_t>(),
+                                                           S.out_len.as<uint64_t>(), nullptr, nullptr, nullptr);
     g_launches++;
     CK(cudaGetLastError());
 }
@@ -701,9 +720,15 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
             launch_compact(S, p, out.fmt, L.stream);
             CK(cudaEventRecord(e[4], L.stream));
         } else {
-            launch_untranspose(S, p, L.stream);
+            const bool packed = out.fmt == 7;      // moni_gpu_ms_packed: col[] = u32 pointer halves, u8 pointer bits 32..39, u16 lengths
+            if (packed && p.max_len > 0xFFFFull) throw BadBatch("packed matching statistics need reads shorter than 65536 bases");
+            launch_untranspose(S, p, L.stream, packed);
             CK(cudaEventRecord(e[4], L.stream));
-            if (p.bases) {
+            if (p.bases && packed) {
+                DevBuf* const src[3] = {&S.out_ptr, &S.out_hi, &S.out_len};
+                for (int q = 0; q < 3; ++q)
+                    CK(cudaMemcpyAsync((char*)out.col[q] + p.base * out.width[q], src[q]->p, p.bases * out.width[q], cudaMemcpyDeviceToHost, L.stream));
+            } else if (p.bases) {
                 CK(cudaMemcpyAsync(pointers + p.base, S.out_ptr.p, p.bases * 8, cudaMemcpyDeviceToHost, L.stream));
                 CK(cudaMemcpyAsync(lengths + p.base, S.out_len.p, p.bases * 8, cudaMemcpyDeviceToHost, L.stream));
             }
@@ -870,6 +895,37 @@ void* moni_gpu_host_alloc(uint64_t bytes) {
     }
     return p;
 }
+// NUMA node of a CUDA device from sysfs (-1 if unknown): /sys/bus/pci/devices/<domain:bus:dev.fn>/numa_node
+static int gpu_numa_node(int dev) {
+    char bdf[32] = {0};
+    if (cudaDeviceGetPCIBusId(bdf, sizeof(bdf), dev) != cudaSuccess) return -1;
+    for (char* c = bdf; *c; ++c) *c = (char)tolower(*c);
+    const std::string path = std::string("/sys/bus/pci/devices/") + bdf + "/numa_node";
+    FILE* f = fopen(path.c_str(), "r");
+    if (!f) return -1;
+    int node = -1;
+    if (fscanf(f, "%d", &node) != 1) node = -1;
+    fclose(f);
+    return node;
+}
+
+void* moni_gpu_host_alloc_near(int gpu, uint64_t bytes) {
+    // Page-locked memory is faulted in by cudaHostAlloc itself, so a "preferred node" memory policy held across the call
+    // places the buffer on the GPU's NUMA node: the PCIe copies then do not cross the socket interconnect.
+    const int node = gpu_numa_node(gpu);
+    bool policy_set = false;
+    if (node >= 0 && node < 1024) {
+        unsigned long mask[16] = {0};
+        mask[node / (8 * sizeof(unsigned long))] = 1ul << (node % (8 * sizeof(unsigned long)));
+        policy_set = syscall(SYS_set_mempolicy, 1 /* MPOL_PREFERRED */, mask, (unsigned long)(sizeof(mask) * 8)) == 0;
+    }
+    void* p = moni_gpu_host_alloc(bytes);
+    if (policy_set) syscall(SYS_set_mempolicy, 0 /* MPOL_DEFAULT */, nullptr, 0ul);
+    return p;
+}
+
+int moni_gpu_numa_node(int gpu) { return gpu_numa_node(gpu); }
+
 void moni_gpu_host_free(void* p) {
     if (p) cudaFreeHost(p);
 }
@@ -981,10 +1037,12 @@ int moni_gpu_index_info(const moni_gpu_index* idx, uint64_t* n, uint64_t* r, uin
     return 0;
 }
 
-int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* pointers, uint64_t* lengths) {
+static int ms_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* pointers, uint64_t* lengths,
+                   const RecOut& out) {
     if (!idx || !offsets || (!seqs && n_reads && offsets[n_reads] != offsets[0])) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
     if (n_reads == 0) return 0;
-    if (!pointers || !lengths) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    if (out.fmt == 7 ? (!out.col[0] || !out.col[1] || !out.col[2]) : (!pointers || !lengths)) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    if (out.fmt == 7 && idx->hdr.n > (1ull << 40) - (1ull << 31)) { g_err = "packed pointers need n <= 2^40 - 2^31"; return MONI_GPU_EINVAL; }
     return guarded([&]() -> int {
         const int G = (int)idx->reps.size();
         std::vector<uint64_t> cut;
@@ -993,7 +1051,7 @@ int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, 
         std::vector<int> rc(G, 0);
         auto work = [&](int g) {
             rc[g] = guarded([&]() -> int {
-                run_shard(idx, *idx->reps[g], 0, seqs, offsets, cut[g], cut[g + 1], pointers, lengths, RecOut(), nullptr);
+                run_shard(idx, *idx->reps[g], 0, seqs, offsets, cut[g], cut[g + 1], pointers, lengths, out, nullptr);
                 return 0;
             });
             if (rc[g]) errs[g] = g_err;
@@ -1008,6 +1066,21 @@ int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, 
         for (int g = 0; g < G; ++g) if (rc[g]) { g_err = errs[g]; return rc[g]; }
         return 0;
     });
+}
+
+int moni_gpu_ms(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* pointers, uint64_t* lengths) {
+    return ms_impl(idx, seqs, offsets, n_reads, pointers, lengths, RecOut());
+}
+
+int moni_gpu_ms_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint32_t* ptr_lo, uint8_t* ptr_hi,
+                       uint16_t* lengths) {
+    RecOut o;
+    o.col[0] = ptr_lo; o.width[0] = 4;
+    o.col[1] = ptr_hi; o.width[1] = 1;
+    o.col[2] = lengths; o.width[2] = 2;
+    o.ncol = 3;
+    o.fmt = 7;
+    return ms_impl(idx, seqs, offsets, n_reads, nullptr, nullptr, o);
 }
 
 static int mems_impl(moni_gpu_index* idx, int mode, const char* seqs, const uint64_t* offsets, uint64_t n_reads, RecOut out) {

@@ -241,6 +241,17 @@ def main():
         dt = time.perf_counter() - t
         out["ms"] = {"reads": int(k_ms), "wall_ms": dt * 1e3, "reads_per_s": k_ms / dt, "bases_per_s": t_ms / dt, "d2h_bytes": 16 * t_ms,
                      "timing": ix.timing(), "hash": hash64(p_, l_)}
+        lo, hi, l16 = m.pinned_empty(t_ms, np.uint32), m.pinned_empty(t_ms, np.uint8), m.pinned_empty(t_ms, np.uint16)
+        ix.matching_statistics_packed(h_seqs[:t_ms], h_offs[:k_ms + 1], out=(lo, hi, l16))
+        t = time.perf_counter()
+        ix.matching_statistics_packed(h_seqs[:t_ms], h_offs[:k_ms + 1], out=(lo, hi, l16))
+        dt = time.perf_counter() - t
+        same = True
+        for s0 in range(0, t_ms, 1 << 26):
+            sl_ = slice(s0, s0 + (1 << 26))
+            same = same and bool(np.array_equal(m.unpack_pointers(lo[sl_], hi[sl_]), p_[sl_]) and np.array_equal(l16[sl_], l_[sl_]))
+        out["ms_packed"] = {"reads": int(k_ms), "wall_ms": dt * 1e3, "reads_per_s": k_ms / dt, "bases_per_s": t_ms / dt, "d2h_bytes": 7 * t_ms,
+                            "timing": ix.timing(), "same_as_ms": same}
         # properties of the complete result: lengths are matching statistics of the pointers
         Lm = l_.reshape(-1, L)
         ok1 = ok2 = True

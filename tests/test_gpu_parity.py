@@ -444,3 +444,32 @@ def test_concurrent_callers_on_one_index(m, indexes, oracle_mod):
     for t in th:
         t.join()
     assert not bad, bad
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_ms_packed_equals_ms(case, m, indexes):
+    """moni_gpu_ms_packed (u32 + u8 pointer halves, u16 lengths) decodes to exactly the u64 results of moni_gpu_ms,
+    including the reference's wrapped pointers (withN has reads with symbols absent from the text)."""
+    names, seqs = read_fastq(os.path.join(GOLDEN, case + ".fq"))
+    flat, offs = pack(seqs)
+    ptr, ln = indexes[case].matching_statistics(flat, offs)
+    lo, hi, l16 = indexes[case].matching_statistics_packed(flat, offs)
+    assert lo.dtype == np.uint32 and hi.dtype == np.uint8 and l16.dtype == np.uint16
+    assert np.array_equal(m.unpack_pointers(lo, hi), ptr) and np.array_equal(l16, ln)
+    if case == "withN":
+        assert (ptr >= np.uint64(1 << 63)).any()          # wrapped pointers are present in this fixture
+    three = m.MoniIndex(os.path.join(GOLDEN, case + ".fa"), gpus=[0, 0, 0])
+    lo3, hi3, l3 = three.matching_statistics_packed(flat, offs)
+    assert np.array_equal(lo3, lo) and np.array_equal(hi3, hi) and np.array_equal(l3, l16)
+    three.close()
+    with pytest.raises(m.MoniGpuError) as e:
+        indexes[case].matching_statistics_packed(*pack([b"AC" * 40000]))
+    assert e.value.code == -1
+
+
+def test_numa_near_pinned_buffers(m, indexes):
+    """moni_gpu_host_alloc_near gives usable page-locked memory whatever the host topology."""
+    a = m.pinned_empty(1000, np.uint64, gpu=0)
+    a[:] = 7
+    assert int(a.sum()) == 7000
+    assert m.load_library().moni_gpu_numa_node(0) >= -1
