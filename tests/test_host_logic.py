@@ -181,3 +181,13 @@ def test_lcp_align_index_gives_the_same_seeds_and_occurrences(case, host_sim, or
     assert oracle_mod.format_occs(names, so, ref, ln, qpos, oo, occs) == open(pre + ".occs12", "rb").read()
     d = oracle_mod.read_thrbv_ms(os.path.join(GOLDEN, case + ".fa.thrbv.full.lcp.ms"), full=True)
     assert d["slcp"].shape[0] == d["R"]
+
+
+def test_row_layout_phi_step_and_packed_pointers_at_40_bits(tmp_path):
+    """tests/unit_rows.cpp: RowRegs decodes every MoveRow field at its extremes (40-bit samples, u32 rows), phi_step is right
+    near 2^40 including the circular predecessor, packed pointers round-trip wrapped values."""
+    import subprocess
+    exe = str(tmp_path / "unit_rows")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", os.path.join(ROOT, "tests", "unit_rows.cpp"), "-o", exe])
+    r = subprocess.run([exe], capture_output=True)
+    assert r.returncode == 0, r.stderr
