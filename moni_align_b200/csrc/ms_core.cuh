@@ -388,6 +388,25 @@ MONI_HD uint64_t phi_step(const PhiEntry* tab, const uint32_t* dir, uint32_t shi
 // a + len <= N, b + len <= N.
 MONI_HD bool lce_at_least(const ImageView& v, uint64_t a, uint64_t b, uint64_t len) {
     const uint8_t* t = v.pool + ((uint64_t)(v.hdr.root_ref & ~kLeafBit) << v.hdr.pool_shift);
+#if defined(__CUDA_ARCH__)
+    // both sides as streams of aligned 8-byte words: one new load per side and step (load8 would issue two)
+    const unsigned long long pa = (unsigned long long)(t + a), pb = (unsigned long long)(t + b);
+    const uint32_t sa = (uint32_t)(pa & 7ull) * 8u, sb = (uint32_t)(pb & 7ull) * 8u;
+    const uint64_t* qa = reinterpret_cast<const uint64_t*>(pa & ~7ull);
+    const uint64_t* qb = reinterpret_cast<const uint64_t*>(pb & ~7ull);
+    uint64_t wa = __ldg(qa), wb = __ldg(qb);
+    for (uint64_t k = 0; k < len; k += 8) {
+        const uint64_t na = __ldg(++qa), nb = __ldg(++qb);
+        const uint64_t xa = sa ? (wa >> sa) | (na << (64u - sa)) : wa;
+        const uint64_t xb = sb ? (wb >> sb) | (nb << (64u - sb)) : wb;
+        uint64_t x = xa ^ xb;
+        if (len - k < 8) x &= (1ull << (8 * (len - k))) - 1ull;
+        if (x) return false;
+        wa = na;
+        wb = nb;
+    }
+    return true;
+#else
     uint64_t k = 0;
     for (; k + 8 <= len; k += 8)
         if (load8(t + a + k) != load8(t + b + k)) return false;
@@ -397,6 +416,7 @@ MONI_HD bool lce_at_least(const ImageView& v, uint64_t a, uint64_t b, uint64_t l
         if (x & mask) return false;
     }
     return true;
+#endif
 }
 
 // seed_finder::find_MEM_occs without seed filtering (:239-251): the seed position, then find_MEM_above (:169-197: Phi steps
