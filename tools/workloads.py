@@ -22,6 +22,11 @@ import build_index  # noqa: E402
 import synth  # noqa: E402
 
 WORKLOADS = {
+    # BASELINE.json configs[0]: "data/yeast.fasta index, `moni ms` on 100k synthetic 150 bp reads (1% errors)".  data/yeast.fasta is
+    # not in the reference checkout (.MISSING_LARGE_BLOBS): yeast-scale stand-in of SURVEY.md 8(d), 12.16 Mbp of uniform ACGT.
+    "cfg1": dict(base_len=12_160_000, haplotypes=1, seed=101, snp=0.0, indel=0.0, read_seed=102, read_len=150,
+                 pairs=50_000, insert=(400, 50), err=0.01,
+                 desc="cfg1 stand-in: 12.16 Mbp single genome, ms on 100k x 150 bp reads, 1% substitutions, half reverse-complemented"),
     "cfg2": dict(base_len=61_400_000, haplotypes=7, seed=201, snp=5e-3, indel=5e-4, read_seed=203, read_len=150,
                  pairs=1_000_000, insert=(400, 50), err=0.01,
                  desc="cfg2 stand-in: 61.4 Mbp x 7 haplotypes, mems on 1M x 2 x 150 bp paired-end reads"),
