@@ -42,7 +42,9 @@ typedef struct moni_gpu_batch moni_gpu_batch; /* opaque: a read batch resident i
  * and uploads one replica to every listed CUDA device.  gpus == NULL: devices 0..n_gpus-1.
  * If `<prefix>.thrbv.ms` does not exist, the `moni align` index `<prefix>.thrbv.full.ms` (ms_pointers<>::load,
  * include/ms/moni.hpp:392-409) or `<prefix>.thrbv.full.lcp.ms` (moni_lcp<>::load, include/aligner/moni_lcp.hpp:208-225) is
- * read instead: same query structures, the Phi / LCP members are skipped. */
+ * read instead: same query structures, the Phi / LCP members are skipped.  The grammar is `<prefix>.plain.slp`; when only
+ * `<prefix>.slp` exists, or after moni_gpu_set_option("grammar", "shaped"), the shaped grammar is read instead
+ * (SelfShapedSlp::load, thirdparty/ShapedSlp/SelfShapedSlp.hpp:378-397; ms_c<shaped_slp_t>, src/matching_statistics.cpp:624-627). */
 int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gpu_index** out);
 void moni_gpu_index_free(moni_gpu_index* idx);
 
@@ -118,6 +120,8 @@ int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset);
 int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
 
 /* Options ("leaf_len", "max_scan", "chunk_bases" apply to indexes loaded afterwards; "count" and "verbose" apply at once): "leaf_len" (grammar literal block length; default 0 = auto: the whole text as one literal block if it fits "text_budget" bytes, default 64 GiB, else 128),
+ * "grammar" ("plain" = <prefix>.plain.slp, falling back to <prefix>.slp when only that exists; "shaped" = <prefix>.slp, the file `-q` names,
+ * SelfShapedSlp::load, thirdparty/ShapedSlp/SelfShapedSlp.hpp:378-397; default "plain"),
  * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
  * "chunk_bases" (bases per device chunk, default 2^24) and "chunk_min_reads" (a chunk is not closed before it holds this many reads, default 98304; hard cap 2^29 bases), "lanes" (chunks in flight per GPU, default 4), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
 int moni_gpu_set_option(const char* key, const char* value);

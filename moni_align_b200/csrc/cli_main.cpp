@@ -5,8 +5,10 @@
 //   mems infile [-p patterns] [-o output] [-t threads] [-l len]     src/mems.cpp:432-484
 // default output prefix = patterns + "_" + basename(infile) (:503-506); outputs <out>.pointers and
 // <out>.lengths (ms, text format :569-598) or <out>.mems (mems, src/mems.cpp:585-587), records in input
-// order.  `-l` is parsed and ignored exactly like the reference; `-q` is rejected like the reference
-// (its getopt string has no 'q').  `-t` is the number of host threads that format text; the GPUs do the
+// order.  `-l` is parsed and ignored exactly like the reference.  `-q` selects the shaped grammar `<infile>.slp`: the reference
+// advertises and implements it (:438-440, :178-182, :626) but leaves 'q' out of its getopt string (:447), so there the flag
+// is rejected; here it works, with identical results (they do not depend on the grammar encoding).
+// `-t` is the number of host threads that format text; the GPUs do the
 // computation (extra flag `-g 0,1,..` selects devices; default: device 0, or $MONI_GPUS).
 // Reads: FASTA or FASTQ, plain or gzip (zlib), names cut at the first whitespace, sequence bytes used
 // verbatim -- the behaviour of kseq.h in the reference (thirdparty/klib/kseq.h).
@@ -187,16 +189,17 @@ int main(int argc, char** argv) {
     std::string patterns, output, gpus_arg;
     size_t threads = 1;
     const std::string usage = "usage: " + std::string(argv[0]) +
-                              " infile [-p patterns] [-o output] [-t threads] [-l len] [-g gpus]\n\nComputes the " + what +
+                              " infile [-p patterns] [-o output] [-t threads] [-l len] [-q shaped_slp] [-g gpus]\n\nComputes the " + what +
                               " of the reads in the pattern against the reference index in infile (B200 implementation).\n";
     int c;
-    while ((c = getopt(argc, argv, "l:hp:o:t:g:")) != -1) {
+    while ((c = getopt(argc, argv, "l:hp:o:t:g:q")) != -1) {
         switch (c) {
             case 'p': patterns = optarg; break;
             case 'o': output = optarg; break;
             case 'l': (void)atoi(optarg); break;          // parsed and unused, like the reference
             case 't': threads = (size_t)std::max(1, atoi(optarg)); break;
             case 'g': gpus_arg = optarg; break;
+            case 'q': moni_gpu_set_option("grammar", "shaped"); break;
             case 'h': die(usage);
             default: die("Unknown option.\n" + usage);
         }

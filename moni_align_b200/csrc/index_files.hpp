@@ -42,5 +42,9 @@ struct FlatSlp {
 // Both throw std::runtime_error with a message naming the file and the failing field.
 void read_thrbv_ms(const std::string& path, FlatRlbwt& out, bool full = false);
 void read_plain_slp(const std::string& path, FlatSlp& out);
+// <prefix>.slp = SelfShapedSlp<u32,DagcSd,DagcSd,SelSd>::serialize (reference thirdparty/ShapedSlp/SelfShapedSlp.hpp:399-418),
+// the grammar `ms -q` / `mems -q` name (src/matching_statistics.cpp:164-168,178-182): decoded into the same flat rule
+// table (children by variable id, the root sequence folded into a balanced tree of extra rules).
+void read_shaped_slp(const std::string& path, FlatSlp& out);
 
 }  // namespace moni

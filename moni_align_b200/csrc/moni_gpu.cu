@@ -312,6 +312,7 @@ std::atomic<uint64_t> g_launches{0};
 std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
+    int grammar = 0;                          // 0 = <prefix>.plain.slp, else <prefix>.slp if that is the only one; 1 = <prefix>.slp (`-q`)
     uint64_t leaf_len = 0;                    // 0 = auto: the whole text as one literal block when it fits text_budget, else 128
     uint64_t text_budget = 64ull << 30;       // bytes of HBM the plain text may take per GPU
     uint32_t max_scan = 8;
@@ -878,6 +879,7 @@ int moni_gpu_set_option(const char* key, const char* value) {
     else if (k == "text_budget" && v >= 0) g_opt.text_budget = (uint64_t)v;
     else if (k == "max_scan" && v >= 2 && v <= 4096) g_opt.max_scan = (uint32_t)v;
     else if (k == "verbose") g_opt.verbose = v != 0;
+    else if (k == "grammar" && (std::string(value) == "plain" || std::string(value) == "shaped")) g_opt.grammar = value[0] == 's';
     else if (k == "count") { g_opt.count = v != 0; g_count.store(v != 0); }
     else if (k == "chunk_bases" && v >= 1 && v <= (1ll << 31)) g_opt.chunk_bases = (uint64_t)v;
     else if (k == "chunk_min_reads" && v >= 0) g_opt.chunk_min_reads = (uint64_t)v;
@@ -952,7 +954,12 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
                 ExportOptions eo;
                 eo.verbose = idx->opt.verbose;
                 FlatSlp slp;
-                read_plain_slp(std::string(prefix) + ".plain.slp", slp);
+                // the grammar `ms` / `mems` load by default is the plain one; `-q` names the shaped one
+                // (src/matching_statistics.cpp:178-188).  Both decode to the same rule table; results do not depend on which.
+                const std::string plain = std::string(prefix) + ".plain.slp", shaped = std::string(prefix) + ".slp";
+                const bool use_shaped = idx->opt.grammar == 1 || (access(plain.c_str(), R_OK) != 0 && access(shaped.c_str(), R_OK) == 0);
+                if (use_shaped) read_shaped_slp(shaped, slp);
+                else read_plain_slp(plain, slp);
                 // B200 has the HBM to keep the text itself next to the move table (6 GB for a 6 Gbp pangenome): then an LCE
                 // restart is one random line instead of a root-to-leaf walk.  Larger texts keep the grammar with 128-byte leaves.
                 eo.leaf_len = idx->opt.leaf_len ? idx->opt.leaf_len : (slp.text_len <= idx->opt.text_budget ? std::max<uint64_t>(slp.text_len, 1) : 128);

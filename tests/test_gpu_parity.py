@@ -262,11 +262,50 @@ def test_drop_in_cli_writes_identical_files(case, threads, tmp_path):
         assert open(out + ext, "rb").read() == open(pre + ext, "rb").read(), ext
 
 
-def test_cli_rejects_q_like_the_reference(tmp_path):
+@pytest.mark.parametrize("case", CASES)
+def test_cli_q_reads_the_shaped_grammar(case, tmp_path):
+    """`-q` = the shaped grammar <infile>.slp (the reference implements it but its getopt string lacks 'q',
+    src/matching_statistics.cpp:447,466,624-627): same output bytes as the plain grammar."""
     import subprocess
-    pre = os.path.join(GOLDEN, "pan4")
-    r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", "ms"), pre + ".fa", "-p", pre + ".fq", "-q"], capture_output=True)
-    assert r.returncode == 1 and b"[ERROR]" in r.stderr
+    pre = os.path.join(GOLDEN, case)
+    out = str(tmp_path / "o")
+    for exe in ("ms", "mems"):
+        r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", exe), pre + ".fa", "-p", pre + ".fq", "-o", out, "-q"],
+                           capture_output=True)
+        assert r.returncode == 0, r.stderr
+    for ext in (".pointers", ".lengths", ".mems"):
+        assert open(out + ext, "rb").read() == open(pre + ext, "rb").read(), ext
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("leaf_len", [0, 64])
+def test_shaped_grammar_index_gives_identical_results(case, leaf_len, m, tmp_path):
+    """An index directory that holds only <prefix>.slp is loaded through read_shaped_slp (text mode, and grammar mode
+    with 64-byte literal blocks so the kernels walk the node table built from it); option grammar=shaped does the same when
+    both grammars are present.  ms and mems bytes equal the reference's files."""
+    import shutil
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    only = str(tmp_path / (case + ".fa"))
+    shutil.copy(pre + ".fa.thrbv.ms", only + ".thrbv.ms")
+    shutil.copy(pre + ".fa.slp", only + ".slp")
+    m.set_option("leaf_len", leaf_len)
+    try:
+        for prefix, opt in ((only, "plain"), (pre + ".fa", "shaped")):
+            m.set_option("grammar", opt)
+            ix = m.MoniIndex(prefix)
+            ptr, ln = ix.matching_statistics(flat, offs)
+            assert m.format_ms(names, offs, ptr) == open(pre + ".pointers", "rb").read()
+            assert m.format_ms(names, offs, ln) == open(pre + ".lengths", "rb").read()
+            mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+            assert m.format_mems(names, mo, mp, ml) == open(pre + ".mems", "rb").read()
+            ix.close()
+    finally:
+        m.set_option("leaf_len", 0)
+        m.set_option("grammar", "plain")
+    with pytest.raises(m.MoniGpuError):
+        m.set_option("grammar", "folded")
 
 
 def test_cli_reads_gzip_and_fasta(tmp_path):

@@ -191,3 +191,54 @@ def test_row_layout_phi_step_and_packed_pointers_at_40_bits(tmp_path):
     subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", os.path.join(ROOT, "tests", "unit_rows.cpp"), "-o", exe])
     r = subprocess.run([exe], capture_output=True)
     assert r.returncode == 0, r.stderr
+
+
+@pytest.fixture(scope="module")
+def slp_text_exe(tmp_path_factory):
+    """tests/slp_text.cpp: the product's grammar readers + exporter, text written to stdout."""
+    import subprocess
+    exe = str(tmp_path_factory.mktemp("slp") / "slp_text")
+    src = [os.path.join(ROOT, "tests", "slp_text.cpp"), os.path.join(ROOT, "moni_align_b200", "csrc", "index_files.cpp"),
+           os.path.join(ROOT, "moni_align_b200", "csrc", "device_image.cpp")]
+    subprocess.check_call(["g++", "-O2", "-std=c++17", *src, "-o", exe, "-lpthread"])
+    return exe
+
+
+@pytest.mark.parametrize("case", ["pan4", "withN", "twoletter"])
+def test_shaped_grammar_decodes_to_the_reference_text(case, slp_text_exe):
+    """<case>.fa.slp (SelfShapedSlp, written by the reference encoder) read by read_shaped_slp -- RecSplit length hash,
+    gamma arrays, group tables -- expands to the text the reference's own SelfShapedSlp decoder produced
+    (tests/golden/<case>.text.sha256, from oracle/ref_slp_text.cpp), in text mode and through the node table with
+    64- and 16-byte literal blocks; the plain grammar of the same case expands to the same bytes."""
+    import hashlib
+    import subprocess
+    want, n = open(os.path.join(GOLDEN, case + ".text.sha256")).read().split()
+    shaped, plain = os.path.join(GOLDEN, case + ".fa.slp"), os.path.join(GOLDEN, case + ".fa.plain.slp")
+    for leaf in ([], ["64"], ["16"]):
+        out = subprocess.check_output([slp_text_exe, shaped, "shaped", *leaf], stderr=subprocess.DEVNULL)
+        assert len(out) == int(n) and hashlib.sha256(out).hexdigest() == want
+    out = subprocess.check_output([slp_text_exe, plain, "plain"], stderr=subprocess.DEVNULL)
+    assert hashlib.sha256(out).hexdigest() == want
+
+
+def test_shaped_grammar_reader_rejects_damaged_files(slp_text_exe, tmp_path):
+    """Truncations and a flipped byte in each section end in an error exit (never a crash or a silent wrong text)."""
+    import hashlib
+    import subprocess
+    src = open(os.path.join(GOLDEN, "pan4.fa.slp"), "rb").read()
+    want = open(os.path.join(GOLDEN, "pan4.text.sha256")).read().split()[0]
+    p = str(tmp_path / "bad.slp")
+    for cut in (0, 7, 40, len(src) // 3, len(src) - 1):
+        open(p, "wb").write(src[:cut])
+        r = subprocess.run([slp_text_exe, p, "shaped"], capture_output=True)
+        assert r.returncode == 1 and b"slp_text:" in r.stderr, cut
+    rng = np.random.default_rng(5)
+    for at in rng.integers(0, len(src), size=40):
+        b = bytearray(src)
+        b[at] ^= 0x5A
+        open(p, "wb").write(bytes(b))
+        r = subprocess.run([slp_text_exe, p, "shaped"], capture_output=True, timeout=60)
+        assert r.returncode in (0, 1), (at, r.returncode)          # no signal
+        if r.returncode == 0 and hashlib.sha256(r.stdout).hexdigest() != want:
+            # damage the format cannot detect (a child offset, an alphabet byte): still a text of the stated length
+            assert len(r.stdout) == 23992
