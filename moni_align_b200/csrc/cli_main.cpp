@@ -12,14 +12,21 @@
 // computation (extra flag `-g 0,1,..` selects devices; default: device 0, or $MONI_GPUS).
 // Reads: FASTA or FASTQ, plain or gzip (zlib), names cut at the first whitespace, sequence bytes used
 // verbatim -- the behaviour of kseq.h in the reference (thirdparty/klib/kseq.h).
+#include <fcntl.h>
 #include <getopt.h>
 #include <libgen.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <zlib.h>
 
+#include <algorithm>
+#include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -50,6 +57,7 @@ struct SeqReader {
     std::vector<unsigned char> buf;
     size_t pos = 0, len = 0;
     int last = 0;   // the record marker already consumed ('>' or '@'), 0 = none yet
+    std::string header, qual;
     bool eof = false;
     explicit SeqReader(const std::string& path) : buf(1 << 20) {
         f = gzopen(path.c_str(), "r");
@@ -57,22 +65,33 @@ struct SeqReader {
         gzbuffer(f, 1 << 20);
     }
     ~SeqReader() { if (f) gzclose(f); }
+    bool fill() {
+        if (eof) return false;
+        const int k = gzread(f, buf.data(), (unsigned)buf.size());
+        if (k <= 0) { eof = true; return false; }
+        len = (size_t)k;
+        pos = 0;
+        return true;
+    }
     int getc() {
-        if (pos >= len) {
-            if (eof) return -1;
-            const int k = gzread(f, buf.data(), (unsigned)buf.size());
-            if (k <= 0) { eof = true; return -1; }
-            len = (size_t)k;
-            pos = 0;
-        }
+        if (pos >= len && !fill()) return -1;
         return buf[pos++];
     }
-    // appends the rest of the current line (without the newline) to out; returns the delimiter (-1 at EOF)
+    // appends the rest of the current line (without the newline, carriage returns dropped) to out; returns the
+    // delimiter (-1 at EOF).  Whole buffer spans at a time: the parser runs at memchr speed, not a call per byte.
     int line(std::string* out) {
         for (;;) {
-            const int c = getc();
-            if (c < 0 || c == '\n') return c;
-            if (out && c != '\r') out->push_back((char)c);
+            if (pos >= len && !fill()) return -1;
+            const unsigned char* s = buf.data() + pos;
+            const size_t avail = len - pos;
+            const unsigned char* nl = (const unsigned char*)memchr(s, '\n', avail);
+            const size_t k = nl ? (size_t)(nl - s) : avail;
+            if (out && k) {
+                if (!memchr(s, '\r', k)) out->append((const char*)s, k);
+                else for (size_t i = 0; i < k; ++i) if (s[i] != '\r') out->push_back((char)s[i]);
+            }
+            pos += k + (nl ? 1 : 0);
+            if (nl) return '\n';
         }
     }
     // Reads one record; name cut at first whitespace.  Returns false at end of file.
@@ -85,10 +104,10 @@ struct SeqReader {
         }
         name.clear();
         seq.clear();
-        std::string header;
+        header.clear();
         line(&header);
         const size_t sp = header.find_first_of(" \t");
-        name = header.substr(0, sp);
+        name.assign(header, 0, sp);
         // sequence lines until the next marker
         while ((c = getc()) >= 0 && c != '>' && c != '+' && c != '@') {
             if (c == '\n') continue;
@@ -99,7 +118,6 @@ struct SeqReader {
         if (c != '+') { if (c < 0) last = 0, eof = true; return true; }
         line(nullptr);                                   // rest of the '+' line
         size_t q = 0;
-        std::string qual;
         while (q < seq.size()) {                          // quality: as many characters as bases
             qual.clear();
             const int d = line(&qual);
@@ -111,73 +129,209 @@ struct SeqReader {
     }
 };
 
+// integer -> decimal ASCII, two digits per division
 inline char* put_u64(char* p, uint64_t v) {
+    static const char kPairs[201] =
+        "00010203040506070809101112131415161718192021222324252627282930313233343536373839"
+        "40414243444546474849505152535455565758596061626364656667686970717273747576777879"
+        "8081828384858687888990919293949596979899";
     char tmp[24];
-    int k = 0;
-    do { tmp[k++] = (char)('0' + v % 10); v /= 10; } while (v);
-    while (k) *p++ = tmp[--k];
-    return p;
+    int k = 24;
+    while (v >= 100) {
+        const uint64_t q = v / 100;
+        const unsigned r = (unsigned)(v - q * 100);
+        v = q;
+        tmp[--k] = kPairs[2 * r + 1];
+        tmp[--k] = kPairs[2 * r];
+    }
+    if (v >= 10) { tmp[--k] = kPairs[2 * v + 1]; tmp[--k] = kPairs[2 * v]; }
+    else tmp[--k] = (char)('0' + v);
+    memcpy(p, tmp + k, 24 - k);
+    return p + (24 - k);
 }
 
-struct Batch {
-    std::vector<std::string> names;
-    std::string seqs;
-    std::vector<uint64_t> offsets{0};
-    void clear() { names.clear(); seqs.clear(); offsets.assign(1, 0); }
+// A batch travelling through the three stages (parse -> GPU call -> format + write).  Sequence and result buffers are
+// pinned so the library's copies run at PCIe speed; results come back in the packed layouts (7 bytes per base for ms,
+// 4 bytes per MEM) unless a read of 65536 bases or more forces the wide calls.
+struct Slot {
+    std::string names;                       // name bytes back to back
+    std::vector<uint32_t> name_end{0};       // n_reads + 1
+    std::vector<uint64_t> offsets{0};        // n_reads + 1
+    char* seqs = nullptr;                    // pinned
+    uint64_t cap = 0;                        // bases the pinned buffers hold
+    uint32_t* lo = nullptr;                  // ms: pointer low words; mems: packed records        (pinned, cap)
+    uint8_t* hi = nullptr;                   // ms: pointer bits 32..39                             (pinned, cap)
+    uint16_t* len16 = nullptr;               // ms: lengths                                         (pinned, cap)
+    std::vector<uint64_t> moff;              // mems: n_reads + 1
+    std::vector<uint64_t> w1, w2;            // wide fallback (reads of >= 65536 bases)
+    uint64_t max_len = 0;
+    bool wide = false, last = false;
+    size_t n_reads() const { return offsets.size() - 1; }
+    uint64_t total() const { return offsets.back(); }
+    void clear() { names.clear(); name_end.assign(1, 0); offsets.assign(1, 0); max_len = 0; wide = false; last = false; }
+    void release() {
+        moni_gpu_host_free(seqs); moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(len16);
+        seqs = nullptr; lo = nullptr; hi = nullptr; len16 = nullptr; cap = 0;
+    }
+    // grows the pinned buffers to hold `bases` (keeps the sequence bytes already there)
+    void ensure(uint64_t bases, bool mems) {
+        if (bases <= cap) return;
+        // doubling up to one full batch (+ room for the read that crosses the limit); beyond that only a single huge read grows it
+        const uint64_t soft = (64u << 20) + (1u << 20);
+        const uint64_t ncap = bases <= soft ? std::min<uint64_t>(std::max<uint64_t>(cap * 2, bases), soft) : std::max<uint64_t>(bases, cap * 2);
+        char* ns = (char*)moni_gpu_host_alloc(ncap + 16);
+        if (!ns) die("cannot allocate pinned host memory for the read batch");
+        if (seqs) memcpy(ns, seqs, total());
+        moni_gpu_host_free(seqs); moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(len16);
+        seqs = ns;
+        lo = (uint32_t*)moni_gpu_host_alloc((ncap + 4) * 4);
+        hi = mems ? nullptr : (uint8_t*)moni_gpu_host_alloc(ncap + 16);
+        len16 = mems ? nullptr : (uint16_t*)moni_gpu_host_alloc((ncap + 8) * 2);
+        if (!lo || (!mems && (!hi || !len16))) die("cannot allocate pinned host memory for the results");
+        cap = ncap;
+    }
+    void add(const std::string& name, const std::string& seq, bool mems) {
+        ensure(total() + seq.size(), mems);
+        memcpy(seqs + total(), seq.data(), seq.size());
+        names += name;
+        name_end.push_back((uint32_t)names.size());
+        offsets.push_back(total() + seq.size());
+        max_len = std::max<uint64_t>(max_len, seq.size());
+    }
 };
 
-// formats reads [a, b) of one batch into `out`
-void format_values(const Batch& B, const uint64_t* vals, size_t a, size_t b, std::string& out) {
+inline uint64_t unpack_pointer(uint32_t lo, uint8_t hi) {        // include/moni_gpu.h, moni_gpu_ms_packed
+    uint64_t v = (uint64_t)lo | (uint64_t)hi << 32;
+    if (v >= (1ULL << 40) - (1ULL << 31)) v -= 1ULL << 40;       // the reference's wrapped pointers 2^64 - k
+    return v;
+}
+
+inline void put_header(const Slot& B, size_t r, std::string& out) {
+    out.push_back('>');
+    out.append(B.names, B.name_end[r], B.name_end[r + 1] - B.name_end[r]);
+    out.push_back('\n');
+}
+
+// ms text of reads [a, b): ">name\n" + "v v v \n" per read (src/matching_statistics.cpp:588-598); which = 0 pointers, 1 lengths
+void format_ms(const Slot& B, int which, size_t a, size_t b, std::string& out) {
     out.clear();
     std::vector<char> tmp;
     for (size_t r = a; r < b; ++r) {
         const uint64_t o = B.offsets[r], m = B.offsets[r + 1] - o;
         tmp.resize(m * 21 + 8);
         char* p = tmp.data();
-        for (uint64_t i = 0; i < m; ++i) { p = put_u64(p, vals[o + i]); *p++ = ' '; }
-        out.push_back('>');
-        out += B.names[r];
-        out.push_back('\n');
+        if (B.wide) {
+            const uint64_t* v = (which ? B.w2.data() : B.w1.data()) + o;
+            for (uint64_t i = 0; i < m; ++i) { p = put_u64(p, v[i]); *p++ = ' '; }
+        } else if (which) {
+            for (uint64_t i = 0; i < m; ++i) { p = put_u64(p, B.len16[o + i]); *p++ = ' '; }
+        } else {
+            for (uint64_t i = 0; i < m; ++i) { p = put_u64(p, unpack_pointer(B.lo[o + i], B.hi[o + i])); *p++ = ' '; }
+        }
+        put_header(B, r, out);
         out.append(tmp.data(), p - tmp.data());
         out.push_back('\n');
     }
 }
 
-void format_mems(const Batch& B, const uint64_t* moff, const uint64_t* mpos, const uint64_t* mlen, size_t a, size_t b, std::string& out) {
+// mems text: ">name\n" + "(pos,len) " per record + "\n" (src/mems.cpp:585-587)
+void format_mems(const Slot& B, size_t a, size_t b, std::string& out) {
     out.clear();
     std::vector<char> tmp;
     for (size_t r = a; r < b; ++r) {
-        const uint64_t s = moff[r], e = moff[r + 1];
+        const uint64_t s = B.moff[r], e = B.moff[r + 1];
         tmp.resize((e - s) * 46 + 8);
         char* p = tmp.data();
         for (uint64_t k = s; k < e; ++k) {
+            const uint64_t pos = B.wide ? B.w1[k] : B.lo[k] >> 16, len = B.wide ? B.w2[k] : B.lo[k] & 0xFFFF;
             *p++ = '(';
-            p = put_u64(p, mpos[k]);
+            p = put_u64(p, pos);
             *p++ = ',';
-            p = put_u64(p, mlen[k]);
+            p = put_u64(p, len);
             *p++ = ')';
             *p++ = ' ';
         }
-        out.push_back('>');
-        out += B.names[r];
-        out.push_back('\n');
+        put_header(B, r, out);
         out.append(tmp.data(), p - tmp.data());
         out.push_back('\n');
     }
 }
 
-template <typename F>
-void parallel_format(size_t n_reads, size_t threads, std::vector<std::string>& parts, F&& fn) {
-    threads = std::max<size_t>(1, std::min(threads, n_reads ? n_reads : 1));
-    parts.resize(threads);
-    std::vector<std::thread> th;
-    for (size_t t = 0; t < threads; ++t)
-        th.emplace_back([&, t]() { fn(n_reads * t / threads, n_reads * (t + 1) / threads, parts[t]); });
-    for (auto& x : th) x.join();
-}
+// formats a batch with `threads` workers, then every worker writes its own part at its final file offset
+struct Writer {
+    int fd = -1;
+    uint64_t at = 0;
+    std::vector<std::string> parts;
+    void open_file(const std::string& path) {
+        fd = ::open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
+        if (fd < 0) die("open() file " + path + " failed");
+    }
+    void close_file() { if (fd >= 0) ::close(fd); fd = -1; }
+    template <typename F>
+    void run(const Slot& B, size_t threads, F&& fn) {
+        const size_t nr = B.n_reads();
+        // split by bases so that workers get equal amounts of text
+        threads = std::max<size_t>(1, std::min(threads, nr ? nr : 1));
+        parts.resize(threads);
+        std::vector<size_t> cut(threads + 1, nr);
+        cut[0] = 0;
+        for (size_t t = 1; t < threads; ++t) {
+            const uint64_t want = B.total() * t / threads;
+            cut[t] = (size_t)(std::lower_bound(B.offsets.begin(), B.offsets.end(), want) - B.offsets.begin());
+            cut[t] = std::min(std::max(cut[t], cut[t - 1]), nr);
+        }
+        std::vector<std::thread> th;
+        for (size_t t = 0; t < threads; ++t) th.emplace_back([&, t]() { fn(cut[t], cut[t + 1], parts[t]); });
+        for (auto& x : th) x.join();
+        th.clear();
+        std::vector<uint64_t> where(threads);
+        for (size_t t = 0; t < threads; ++t) { where[t] = at; at += parts[t].size(); }
+        std::atomic<bool> failed{false};
+        for (size_t t = 0; t < threads; ++t)
+            th.emplace_back([&, t]() {
+                const char* p = parts[t].data();
+                uint64_t left = parts[t].size(), off = where[t];
+                while (left) {
+                    const ssize_t k = pwrite(fd, p, left, (off_t)off);
+                    if (k <= 0) { failed = true; return; }
+                    p += k; left -= (uint64_t)k; off += (uint64_t)k;
+                }
+            });
+        for (auto& x : th) x.join();
+        if (failed) die("write failed");
+    }
+};
 
 }  // namespace
 
+#if defined(MONI_CLI_SELFTEST)
+// Host-only check of the reader and the number formatter (tests/test_host_logic.py):
+//   parse FILE  -> one line "name<TAB>sequence" per record;   u64 -> every whitespace-separated number of stdin through put_u64
+int main(int argc, char** argv) {
+    if (argc >= 3 && !strcmp(argv[1], "parse")) {
+        SeqReader rd(argv[2]);
+        std::string name, seq;
+        while (rd.next(name, seq)) {
+            fwrite(name.data(), 1, name.size(), stdout);
+            fputc('\t', stdout);
+            fwrite(seq.data(), 1, seq.size(), stdout);
+            fputc('\n', stdout);
+        }
+        return 0;
+    }
+    if (argc >= 2 && !strcmp(argv[1], "u64")) {
+        unsigned long long v;
+        char buf[32];
+        while (scanf("%llu", &v) == 1) {
+            char* e = put_u64(buf, v);
+            *e++ = '\n';
+            fwrite(buf, 1, e - buf, stdout);
+        }
+        return 0;
+    }
+    return 2;
+}
+#else
 int main(int argc, char** argv) {
 #if defined(MONI_CLI_MEMS)
     const bool mems = true;
@@ -227,65 +381,128 @@ int main(int argc, char** argv) {
     std::string out_prefix = patterns + "_" + basename(ibuf.data());
     if (!output.empty()) out_prefix = output;
 
-    FILE* f1 = nullptr;
-    FILE* f2 = nullptr;
+    Writer out1, out2;
     if (mems) {
-        f1 = fopen((out_prefix + ".mems").c_str(), "wb");
-        if (!f1) die("open() file " + out_prefix + ".mems failed");
+        out1.open_file(out_prefix + ".mems");
     } else {
-        f1 = fopen((out_prefix + ".pointers").c_str(), "wb");
-        if (!f1) die("open() file " + out_prefix + ".pointers failed");
-        f2 = fopen((out_prefix + ".lengths").c_str(), "wb");
-        if (!f2) die("open() file " + out_prefix + ".lengths failed");
+        out1.open_file(out_prefix + ".pointers");
+        out2.open_file(out_prefix + ".lengths");
     }
 
     info("Processing patterns");
     t0 = now_s();
-    SeqReader rd(patterns);
-    Batch B;
-    std::string name, seq;
-    std::vector<uint64_t> v1, v2, moff;
-    std::vector<std::string> parts1, parts2;
+    // Three stages on three threads, batches of ~64 M bases in a ring of slots: while the GPUs work on one batch the next
+    // is being parsed and the previous one formatted and written (the reference splits the file and runs a worker per
+    // part instead, src/matching_statistics.cpp:311-426; records come out in input order either way).
+    constexpr int kSlots = 3;
+    const uint64_t kBatchBases = 64u << 20, kBatchReads = 2u << 20;
+    Slot slots[kSlots];
+    int state[kSlots] = {0, 0, 0};            // 0 = free, 1 = parsed, 2 = results ready
+    std::mutex mu;
+    std::condition_variable cv;
+    auto wait_for = [&](int slot, int want) {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&]() { return state[slot] == want; });
+    };
+    auto set_state = [&](int slot, int v) {
+        { std::lock_guard<std::mutex> lk(mu); state[slot] = v; }
+        cv.notify_all();
+    };
     uint64_t n_reads = 0, n_bases = 0;
-    double t_gpu = 0;
-    const size_t kBatchBases = 256u << 20, kBatchReads = 4u << 20;
-    bool more = true;
-    while (more) {
-        B.clear();
-        while (B.seqs.size() < kBatchBases && B.names.size() < kBatchReads) {
-            if (!rd.next(name, seq)) { more = false; break; }
-            B.names.push_back(name);
-            B.seqs += seq;
-            B.offsets.push_back(B.seqs.size());
-        }
-        const size_t nr = B.names.size();
-        if (!nr) break;
-        n_reads += nr;
-        n_bases += B.seqs.size();
-        const size_t total = B.seqs.size();
-        v1.resize(total + 1);
-        v2.resize(total + 1);
-        const double tg = now_s();
-        if (mems) {
-            moff.resize(nr + 1);
-            if (moni_gpu_mems(idx, B.seqs.data(), B.offsets.data(), nr, moff.data(), v1.data(), v2.data(), total) != 0)
-                die(moni_gpu_last_error());
-            t_gpu += now_s() - tg;
-            parallel_format(nr, threads, parts1, [&](size_t a, size_t b, std::string& o) { format_mems(B, moff.data(), v1.data(), v2.data(), a, b, o); });
-            for (auto& p : parts1) fwrite(p.data(), 1, p.size(), f1);
-        } else {
-            if (moni_gpu_ms(idx, B.seqs.data(), B.offsets.data(), nr, v1.data(), v2.data()) != 0) die(moni_gpu_last_error());
-            t_gpu += now_s() - tg;
-            parallel_format(nr, threads, parts1, [&](size_t a, size_t b, std::string& o) { format_values(B, v1.data(), a, b, o); });
-            parallel_format(nr, threads, parts2, [&](size_t a, size_t b, std::string& o) { format_values(B, v2.data(), a, b, o); });
-            for (auto& p : parts1) fwrite(p.data(), 1, p.size(), f1);
-            for (auto& p : parts2) fwrite(p.data(), 1, p.size(), f2);
+    double t_parse = 0, t_gpu = 0, t_out = 0;
+
+    // pinned buffers are sized once from the file size (a FASTQ holds about one base per two bytes, a gzip four times that):
+    // page-locking is slow enough that growing by doubling would show in the parse stage
+    uint64_t first_cap = 1u << 20;
+    {
+        struct stat st;
+        if (stat(patterns.c_str(), &st) == 0) {
+            const bool gz = patterns.size() > 3 && patterns.compare(patterns.size() - 3, 3, ".gz") == 0;
+            first_cap = std::min<uint64_t>(kBatchBases + (1u << 20), std::max<uint64_t>(first_cap, (uint64_t)st.st_size * (gz ? 4 : 1)));
         }
     }
-    fclose(f1);
-    if (f2) fclose(f2);
+    std::thread parser([&]() {
+        SeqReader rd(patterns);
+        std::string name, seq;
+        bool more = true;
+        for (int k = 0; more; k = (k + 1) % kSlots) {
+            wait_for(k, 0);
+            const double ts = now_s();
+            Slot& B = slots[k];
+            B.clear();
+            B.ensure(first_cap, mems);
+            while (B.total() < kBatchBases && B.n_reads() < kBatchReads) {
+                if (!rd.next(name, seq)) { more = false; break; }
+                B.add(name, seq, mems);
+            }
+            B.last = !more;
+            t_parse += now_s() - ts;
+            set_state(k, 1);
+        }
+    });
+    std::thread caller([&]() {
+        for (int k = 0;; k = (k + 1) % kSlots) {
+            wait_for(k, 1);
+            Slot& B = slots[k];
+            const size_t nr = B.n_reads();
+            const uint64_t total = B.total();
+            const double ts = now_s();
+            if (nr) {
+                B.wide = B.max_len >= 65536;
+                int rc = 0;
+                if (mems) {
+                    B.moff.resize(nr + 1);
+                    if (!B.wide) rc = moni_gpu_mems_packed(idx, B.seqs, B.offsets.data(), nr, B.moff.data(), B.lo, total);
+                    else {
+                        B.w1.resize(total + 1); B.w2.resize(total + 1);
+                        rc = moni_gpu_mems(idx, B.seqs, B.offsets.data(), nr, B.moff.data(), B.w1.data(), B.w2.data(), total);
+                    }
+                } else {
+                    if (!B.wide) {
+                        rc = moni_gpu_ms_packed(idx, B.seqs, B.offsets.data(), nr, B.lo, B.hi, B.len16);
+                        if (rc == MONI_GPU_EINVAL) B.wide = true;          // text too long for 40-bit packed pointers
+                    }
+                    if (B.wide) {
+                        B.w1.resize(total + 1); B.w2.resize(total + 1);
+                        rc = moni_gpu_ms(idx, B.seqs, B.offsets.data(), nr, B.w1.data(), B.w2.data());
+                    }
+                }
+                if (rc != 0) die(moni_gpu_last_error());
+            }
+            t_gpu += now_s() - ts;
+            const bool last = B.last;
+            set_state(k, 2);
+            if (last) break;
+        }
+    });
+    for (int k = 0;; k = (k + 1) % kSlots) {
+        wait_for(k, 2);
+        Slot& B = slots[k];
+        const double ts = now_s();
+        if (B.n_reads()) {
+            n_reads += B.n_reads();
+            n_bases += B.total();
+            if (mems) {
+                out1.run(B, threads, [&](size_t a, size_t b, std::string& o) { format_mems(B, a, b, o); });
+            } else {
+                out1.run(B, threads, [&](size_t a, size_t b, std::string& o) { format_ms(B, 0, a, b, o); });
+                out2.run(B, threads, [&](size_t a, size_t b, std::string& o) { format_ms(B, 1, a, b, o); });
+            }
+        }
+        t_out += now_s() - ts;
+        const bool last = B.last;
+        set_state(k, 0);
+        if (last) break;
+    }
+    parser.join();
+    caller.join();
+    out1.close_file();
+    out2.close_file();
+    for (auto& sl : slots) sl.release();
     printf("[INFO] Elapsed time (s): %g\n", now_s() - t0);
-    printf("[INFO] reads %llu bases %llu gpu-call time (s) %g gpus %zu\n", (unsigned long long)n_reads, (unsigned long long)n_bases, t_gpu, gpus.size());
+    printf("[INFO] reads %llu bases %llu gpu-call time (s) %g parse (s) %g format+write (s) %g gpus %zu\n", (unsigned long long)n_reads,
+           (unsigned long long)n_bases, t_gpu, t_parse, t_out, gpus.size());
     moni_gpu_index_free(idx);
     return 0;
 }
+#endif

@@ -242,3 +242,68 @@ def test_shaped_grammar_reader_rejects_damaged_files(slp_text_exe, tmp_path):
         if r.returncode == 0 and hashlib.sha256(r.stdout).hexdigest() != want:
             # damage the format cannot detect (a child offset, an alphabet byte): still a text of the stated length
             assert len(r.stdout) == 23992
+
+
+@pytest.fixture(scope="module")
+def cli_selftest(tmp_path_factory):
+    """csrc/cli_main.cpp compiled with -DMONI_CLI_SELFTEST: its reader and number formatter without any GPU call."""
+    import subprocess
+    exe = str(tmp_path_factory.mktemp("cli") / "cli_selftest")
+    pkg = os.path.join(ROOT, "moni_align_b200")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-DMONI_CLI_SELFTEST", os.path.join(pkg, "csrc", "cli_main.cpp"), "-o", exe,
+                           "-L" + pkg, "-lmoni_gpu", "-lz", "-lpthread", "-Wl,-rpath," + pkg], stderr=subprocess.DEVNULL)
+    return exe
+
+
+def _parsed(exe, path):
+    import subprocess
+    out = subprocess.check_output([exe, "parse", str(path)])
+    recs = [l.split(b"\t", 1) for l in out.split(b"\n")[:-1]]
+    return [r[0] for r in recs], [r[1] for r in recs]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_cli_reader_parses_the_golden_fastq(case, cli_selftest):
+    names, seqs = read_fastq(os.path.join(GOLDEN, case + ".fq"))
+    got_names, got_seqs = _parsed(cli_selftest, os.path.join(GOLDEN, case + ".fq"))
+    assert got_names == [n if isinstance(n, bytes) else n.encode() for n in names]
+    assert got_seqs == [bytes(s) for s in seqs]
+
+
+def test_cli_reader_kseq_corner_cases(cli_selftest, tmp_path):
+    """Spans across the 1 MiB read buffer, CRLF, multi-line FASTA, a quality line that starts with '@', blank lines, a file
+    without a final newline, gzip: the record boundaries of kseq.h (thirdparty/klib/kseq.h) that the reference reads with."""
+    import gzip
+    rng = np.random.default_rng(3)
+    big = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=3_300_000))
+    cases = {
+        "crlf.fq": (b"@a x\r\nACGT\r\n+\r\nIIII\r\n@b\r\nGG\r\n+\r\nII\r\n", [(b"a", b"ACGT"), (b"b", b"GG")]),
+        "multi.fa": (b">s1 desc\tmore\nACG\nTTA\n\n>s2\nGG\n", [(b"s1", b"ACGTTA"), (b"s2", b"GG")]),
+        "atqual.fq": (b"@q\nACGT\n+\n@III\n@r\nAC\n+q again\nII\n", [(b"q", b"ACGT"), (b"r", b"AC")]),
+        "nonl.fq": (b"@x\nACGTN\n+\nIIIII", [(b"x", b"ACGTN")]),
+        "nonl.fa": (b">x\nACGT\n>y\nTT", [(b"x", b"ACGT"), (b"y", b"TT")]),
+        "big.fq": (b"@big\n" + big + b"\n+\n" + b"I" * len(big) + b"\n@after\nAC\n+\nII\n", [(b"big", big), (b"after", b"AC")]),
+        "biglines.fa": (b">w\n" + b"\n".join(big[i:i + 70_001] for i in range(0, len(big), 70_001)) + b"\n>z\nA\n", [(b"w", big), (b"z", b"A")]),
+        "empty.fq": (b"", []),
+        "emptyseq.fa": (b">e\n>f\nAC\n", [(b"e", b""), (b"f", b"AC")]),
+    }
+    for name, (data, want) in cases.items():
+        p = tmp_path / name
+        p.write_bytes(data)
+        names, seqs = _parsed(cli_selftest, p)
+        assert list(zip(names, seqs)) == want, name
+        gz = tmp_path / (name + ".gz")
+        with gzip.open(gz, "wb") as f:
+            f.write(data)
+        names, seqs = _parsed(cli_selftest, gz)
+        assert list(zip(names, seqs)) == want, name + ".gz"
+
+
+def test_cli_number_formatter(cli_selftest):
+    import subprocess
+    rng = np.random.default_rng(11)
+    vals = [0, 1, 9, 10, 11, 99, 100, 101, 999, 1000, 65535, 65536, 2**32 - 1, 2**32, 2**40 - 1, 2**40, 2**63, 2**64 - 1, 2**64 - 2]
+    vals += [10**k for k in range(20)] + [10**k - 1 for k in range(1, 20)]
+    vals += [int(x) for x in rng.integers(0, 2**63, size=2000)] + [int(x) >> int(s) for x, s in zip(rng.integers(0, 2**63, size=2000), rng.integers(0, 63, size=2000))]
+    out = subprocess.run([cli_selftest, "u64"], input=" ".join(map(str, vals)).encode(), capture_output=True, check=True).stdout
+    assert out.decode().split() == [str(v) for v in vals]
