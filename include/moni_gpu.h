@@ -125,6 +125,8 @@ int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
  * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
  * "chunk_bases" (bases per device chunk, default 2^24) and "chunk_min_reads" (a chunk is not closed before it holds this many reads, default 98304; hard cap 2^29 bases), "lanes" (chunks in flight per GPU, default 4), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
 int moni_gpu_set_option(const char* key, const char* value);
+/* Environment: MONI_GPU_VERBOSE=1 prints the exporter's and the index load's phase times on stderr (as option "verbose");
+ * MONI_GPU_TRACE=1 prints a per-chunk timeline of every call. */
 
 /* Pinned host memory for batch buffers (cudaHostAlloc / cudaFreeHost). */
 void* moni_gpu_host_alloc(uint64_t bytes);

@@ -7,6 +7,9 @@
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
+#include <thread>
+
+#include <sys/mman.h>
 
 #include "index_files.hpp"
 
@@ -20,6 +23,53 @@ inline void put40(uint8_t* d, uint64_t v) {
 double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
+
+// fn(t) for t in [0, T) on T threads (the caller's thread takes t = 0); the first exception is rethrown
+template <typename F>
+void run_parts(unsigned T, F&& fn) {
+    std::vector<std::thread> th;
+    std::vector<std::exception_ptr> err(T);
+    auto guarded = [&](unsigned t) {
+        try { fn(t); } catch (...) { err[t] = std::current_exception(); }
+    };
+    for (unsigned t = 1; t < T; ++t) th.emplace_back(guarded, t);
+    guarded(0);
+    for (auto& x : th) x.join();
+    for (auto& e : err) if (e) std::rethrow_exception(e);
+}
+
+// v.assign(n, val) for the image's large tables: the cost of a fresh multi-GB vector is its page faults, so the pages are
+// touched from P threads first (and offered to the kernel as huge pages); the assign then runs at memory speed.
+template <typename T>
+void assign_large(std::vector<T>& v, size_t n, const T& val, unsigned P) {
+    v.clear();
+    v.reserve(n);
+    const size_t bytes = n * sizeof(T);
+    char* base = reinterpret_cast<char*>(v.data());
+    if (P > 1 && bytes >= (32u << 20) && base) {
+        const uintptr_t lo = ((uintptr_t)base + (2u << 20) - 1) & ~(uintptr_t)((2u << 20) - 1), hi = ((uintptr_t)base + bytes) & ~(uintptr_t)((2u << 20) - 1);
+        if (hi > lo) madvise((void*)lo, hi - lo, MADV_HUGEPAGE);           // best effort
+        run_parts(P, [&](unsigned t) {
+            for (size_t o = bytes / P * t, e = t + 1 == P ? bytes : bytes / P * (t + 1); o < e; o += 4096) base[o] = 0;
+        });
+    }
+    v.assign(n, val);
+}
+
+// The row passes below are scans with a carried state (characters of each table symbol seen so far, runs of each symbol
+// closed so far, ...).  Every such state is a sum or a last-index over the rows before: the rows are cut into T contiguous
+// parts, one cheap pass gives each part's contribution, an exclusive scan over the parts gives each part's initial state, and
+// the parts then run the same loop side by side.  The LF cursor (first row that starts after an image start) is monotone and
+// is found by one binary search per part and symbol.
+struct PartSums {
+    uint64_t len[4] = {0, 0, 0, 0};              // characters of table symbol tc in rows of the part
+    uint64_t first_piece[4];                     // first row of the part that starts a run of tc   (~0 = none)
+    uint64_t last_piece[4];                      // last row of the part that ends a run of tc      (~0 = none)
+    std::vector<uint64_t> runs, chars;           // per byte value: runs closed / characters in closed runs
+    PartSums() : runs(256, 0), chars(256, 0) {
+        for (int c = 0; c < 4; ++c) first_piece[c] = last_piece[c] = ~0ULL;
+    }
+};
 
 }  // namespace
 
@@ -68,8 +118,9 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
             S.crun_base[c] = cb;
             if (b.count[c]) { sb += b.nruns[c] + 1; cb += b.nruns[c]; }
         }
-        img.slots.assign(sb, GapSlot{0, 0, 0, 0});
-        img.crun_row.assign(cb, 0);
+        const unsigned Pz = opt.threads ? opt.threads : std::min(32u, std::max(1u, std::thread::hardware_concurrency()));
+        assign_large(img.slots, sb, GapSlot{0, 0, 0, 0}, Pz);
+        assign_large(img.crun_row, cb, (uint32_t)0, Pz);
     }
     const uint8_t* tcode = S.tcode;
 
@@ -81,30 +132,59 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
     for (uint64_t k = 0; k < R; ++k)
         for (uint64_t s = b.starts[k]; s < b.starts[k + 1]; s += kMaxPiece) { pos.push_back(s); run.push_back((uint32_t)k); }
 
+    unsigned T = opt.threads ? opt.threads : std::min(32u, std::max(1u, std::thread::hardware_concurrency()));
+    auto parts_for = [&](uint64_t rows) -> unsigned {      // explicit thread counts are honoured down to one row per part (tests)
+        if (opt.threads) return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(opt.threads, rows));
+        return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(T, rows / 65536));
+    };
+
     std::vector<uint64_t> cuts;     // absolute positions of new row starts found in one round
     uint32_t worst = 0;
     for (uint32_t round = 0;; ++round) {
         const uint64_t nr = pos.size();
+        const unsigned P = parts_for(nr);
+        std::vector<PartSums> part(P);
+        std::vector<std::vector<uint64_t>> part_cuts(P);
+        std::vector<uint32_t> part_worst(P, 0);
+        auto row_len = [&](uint64_t i) { return (i + 1 < nr ? pos[i + 1] : n) - pos[i]; };
+        run_parts(P, [&](unsigned t) {
+            for (uint64_t i = nr * t / P, e = nr * (t + 1) / P; i < e; ++i) {
+                const uint8_t tc = tcode[b.heads[run[i]]];
+                if (tc != 0xFF) part[t].len[tc] += row_len(i);
+            }
+        });
+        run_parts(P, [&](unsigned t) {
+            uint64_t seen[4] = {0, 0, 0, 0};   // # of the table symbol before the current row
+            for (unsigned u = 0; u < t; ++u)
+                for (int c = 0; c < 4; ++c) seen[c] += part[u].len[c];
+            uint64_t q[4] = {~0ULL, ~0ULL, ~0ULL, ~0ULL};      // first row whose start is > the image start of the current row
+            std::vector<uint64_t>& my_cuts = part_cuts[t];
+            uint32_t my_worst = 0;
+            for (uint64_t i = nr * t / P, e = nr * (t + 1) / P; i < e; ++i) {
+                const uint8_t tc = tcode[b.heads[run[i]]];
+                if (tc == 0xFF) continue;
+                const uint64_t len = row_len(i);
+                const uint64_t pi = S.F[b.heads[run[i]]] + seen[tc];
+                seen[tc] += len;
+                uint64_t tt = q[tc];
+                if (tt == ~0ULL) tt = (uint64_t)(std::upper_bound(pos.begin(), pos.end(), pi) - pos.begin());
+                while (tt < nr && pos[tt] <= pi) ++tt;
+                uint32_t inside = 0;
+                while (tt < nr && pos[tt] < pi + len) {
+                    ++inside;
+                    if (inside % opt.max_scan == 0 && round < opt.max_rounds) my_cuts.push_back(pos[i] + (pos[tt] - pi));
+                    ++tt;
+                }
+                my_worst = std::max(my_worst, inside);
+                q[tc] = tt;
+            }
+            part_worst[t] = my_worst;
+        });
         cuts.clear();
         worst = 0;
-        uint64_t seen[4] = {0, 0, 0, 0};   // # of the table symbol before the current row
-        uint64_t q[4] = {0, 0, 0, 0};      // first row whose start is > the image start of the current row
-        for (uint64_t i = 0; i < nr; ++i) {
-            const uint8_t tc = tcode[b.heads[run[i]]];
-            if (tc == 0xFF) continue;
-            const uint64_t len = (i + 1 < nr ? pos[i + 1] : n) - pos[i];
-            const uint64_t pi = S.F[b.heads[run[i]]] + seen[tc];
-            seen[tc] += len;
-            uint64_t t = q[tc];
-            while (t < nr && pos[t] <= pi) ++t;
-            uint32_t inside = 0;
-            while (t < nr && pos[t] < pi + len) {
-                ++inside;
-                if (inside % opt.max_scan == 0 && round < opt.max_rounds) cuts.push_back(pos[i] + (pos[t] - pi));
-                ++t;
-            }
-            worst = std::max(worst, inside);
-            q[tc] = t;
+        for (unsigned t = 0; t < P; ++t) {
+            cuts.insert(cuts.end(), part_cuts[t].begin(), part_cuts[t].end());
+            worst = std::max(worst, part_worst[t]);
         }
         if (opt.verbose)
             fprintf(stderr, "[moni-gpu] balance round %u: rows %llu, new cuts %llu, widest image %u rows\n", round,
@@ -139,16 +219,37 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
     img.hdr.init_off = (uint32_t)(n - 1 - pos[nr - 1]);
 
     // ---- fill rows -----------------------------------------------------------------------------
-    img.rows.assign(nr + 1, MoveRow{});
-    img.row_pos.resize(nr + 1);
-    for (uint64_t i = 0; i < nr; ++i) img.row_pos[i] = pos[i];
-    img.row_pos[nr] = n;
+    assign_large(img.rows, nr + 1, MoveRow{}, T);
+    img.row_pos.assign(pos.begin(), pos.end());
+    img.row_pos.push_back(n);
     const int nts = (int)img.hdr.n_table_syms;
-    {
+    const unsigned P = parts_for(nr);
+    auto part_lo = [&](unsigned t) { return nr * t / P; };
+    std::vector<PartSums> part(P);
+    run_parts(P, [&](unsigned t) {                 // each part's contribution to the carried states
+        PartSums& ps = part[t];
+        for (uint64_t i = part_lo(t), e = part_lo(t + 1); i < e; ++i) {
+            const uint32_t k = run[i];
+            const uint8_t h = b.heads[k];
+            const uint8_t th = tcode[h];
+            if (th != 0xFF) {
+                ps.len[th] += img.row_pos[i + 1] - pos[i];
+                if ((i == 0 || run[i - 1] != k) && ps.first_piece[th] == ~0ULL) ps.first_piece[th] = i;
+            }
+            if (i + 1 == nr || run[i + 1] != k) {
+                ps.runs[h] += 1;
+                ps.chars[h] += b.starts[k + 1] - b.starts[k];
+                if (th != 0xFF) ps.last_piece[th] = i;
+            }
+        }
+    });
+    run_parts(P, [&](unsigned t) {
         // backward pass: row of the first piece of the next c-run after row i (for dist_dn)
         uint64_t nxt[4] = {~0ULL, ~0ULL, ~0ULL, ~0ULL};
+        for (int c = 0; c < 4; ++c)
+            for (unsigned u = t + 1; u < P && nxt[c] == ~0ULL; ++u) nxt[c] = part[u].first_piece[c];
         // store the clipped distance directly into the row while walking backwards
-        for (uint64_t ii = nr; ii-- > 0;) {
+        for (uint64_t ii = part_lo(t + 1), lo = part_lo(t); ii-- > lo;) {
             MoveRow& r = img.rows[ii];
             const uint8_t h = b.heads[run[ii]];
             const uint8_t th = tcode[h];
@@ -162,16 +263,26 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
                 if (first_piece) nxt[th] = ii;
             }
         }
-    }
-    {
+    });
+    std::vector<uint64_t> total_runs(256, 0), total_chars(256, 0);
+    for (unsigned u = 0; u < P; ++u)
+        for (int c = 0; c < 256; ++c) { total_runs[c] += part[u].runs[c]; total_chars[c] += part[u].chars[c]; }
+    run_parts(P, [&](unsigned t) {
         uint64_t seen[4] = {0, 0, 0, 0};
-        uint64_t q[4] = {0, 0, 0, 0};
+        uint64_t q[4] = {~0ULL, ~0ULL, ~0ULL, ~0ULL};
         uint64_t jc[256];                 // # c-runs that ended before the current run
         uint64_t cum[256];                // # c before the current run
         uint64_t last_piece[4] = {~0ULL, ~0ULL, ~0ULL, ~0ULL};
         memset(jc, 0, sizeof(jc));
         memset(cum, 0, sizeof(cum));
-        for (uint64_t i = 0; i < nr; ++i) {
+        for (unsigned u = 0; u < t; ++u) {
+            for (int c = 0; c < 4; ++c) {
+                seen[c] += part[u].len[c];
+                if (part[u].last_piece[c] != ~0ULL) last_piece[c] = part[u].last_piece[c];
+            }
+            for (int c = 0; c < 256; ++c) { jc[c] += part[u].runs[c]; cum[c] += part[u].chars[c]; }
+        }
+        for (uint64_t i = part_lo(t), e = part_lo(t + 1); i < e; ++i) {
             MoveRow& r = img.rows[i];
             const uint32_t k = run[i];
             const uint8_t h = b.heads[k];
@@ -198,11 +309,12 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
             if (th != 0xFF) {
                 const uint64_t pi = S.F[h] + seen[th];
                 seen[th] += len;
-                uint64_t t = q[th];
-                while (t < nr && pos[t] <= pi) ++t;
-                q[th] = t;                    // images of later h-rows start further right
-                r.dest_row = (uint32_t)(t - 1);
-                r.dest_off = (uint16_t)(pi - pos[t - 1]);
+                uint64_t tt = q[th];
+                if (tt == ~0ULL) tt = (uint64_t)(std::upper_bound(pos.begin(), pos.end(), pi) - pos.begin());
+                while (tt < nr && pos[tt] <= pi) ++tt;
+                q[th] = tt;                   // images of later h-rows start further right
+                r.dest_row = (uint32_t)(tt - 1);
+                r.dest_off = (uint16_t)(pi - pos[tt - 1]);
                 for (int c = 0, s = 0; c < nts; ++c) {
                     if (c == th) continue;
                     const uint8_t sym = img.hdr.table_syms[c];
@@ -221,13 +333,13 @@ void build_move_table(const FlatRlbwt& b, const ExportOptions& opt, HostImage& i
                 if (th != 0xFF) last_piece[th] = i;
             }
         }
-        for (int c = 0; c < 256; ++c) {
-            if (!b.count[c]) continue;
-            if (jc[c] != b.nruns[c] || cum[c] != b.count[c]) throw std::runtime_error("exporter: per-symbol totals mismatch");
-            GapSlot& g = img.slots[S.slot_base[c] + b.nruns[c]];
-            g.thr = kThrInf;              // after the last c-run the reference can only jump up
-            g.cum = b.count[c];
-        }
+    });
+    for (int c = 0; c < 256; ++c) {
+        if (!b.count[c]) continue;
+        if (total_runs[c] != b.nruns[c] || total_chars[c] != b.count[c]) throw std::runtime_error("exporter: per-symbol totals mismatch");
+        GapSlot& g = img.slots[S.slot_base[c] + b.nruns[c]];
+        g.thr = kThrInf;              // after the last c-run the reference can only jump up
+        g.cum = b.count[c];
     }
     // sentinel row = "pos == n": never scanned past (len 1), always general path
     MoveRow& z = img.rows[nr];

@@ -132,6 +132,7 @@ struct ExportOptions {
     uint32_t max_scan = 8;       // balancing target: rows covered by one row's LF image
     uint32_t max_rounds = 24;
     bool verbose = false;
+    uint32_t threads = 0;        // host threads of the exporter's row passes; 0 = one per core, at most 32 (same image for any value)
 };
 
 // Throws std::runtime_error on anything the image cannot represent.

@@ -18,6 +18,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cctype>
+#include <chrono>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -323,6 +324,7 @@ struct Options {
     uint32_t lanes = 4;
 };
 Options g_opt;
+inline double wall_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 std::mutex g_opt_mu;
 
 struct CudaError : std::runtime_error {
@@ -936,9 +938,11 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
     if (!prefix || !out || n_gpus < 1) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
     *out = nullptr;
     return guarded([&]() -> int {
+        const double t_init0 = wall_s();
         int ndev = 0;
         CK(cudaGetDeviceCount(&ndev));
         if (ndev < 1) throw CudaError("no CUDA device: libmoni_gpu has no CPU path");
+        const double t_init = wall_s() - t_init0;
         std::vector<int> devs(n_gpus);
         for (int g = 0; g < n_gpus; ++g) {
             devs[g] = gpus ? gpus[g] : g;
@@ -946,6 +950,13 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
         }
         std::unique_ptr<moni_gpu_index> idx(new moni_gpu_index);
         { std::lock_guard<std::mutex> lock(g_opt_mu); idx->opt = g_opt; }
+        if (getenv("MONI_GPU_VERBOSE")) idx->opt.verbose = true;
+        const double t_load0 = wall_s();
+        // the CUDA contexts come up (hundreds of ms each) while the files are decoded
+        std::thread ctx_thread([&]() {
+            for (int d : devs) { if (cudaSetDevice(d) == cudaSuccess) cudaFree(nullptr); }
+        });
+        struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } ctx_join{ctx_thread};
         HostImage img;
         // the two files are decoded and exported side by side (they fill disjoint members of the image)
         std::exception_ptr slp_err;
@@ -990,6 +1001,8 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
         if (slp_err) std::rethrow_exception(slp_err);
         idx->hdr = img.hdr;
         idx->device_bytes = img.bytes() + sizeof(SymbolTables);
+        ctx_thread.join();
+        const double t_load1 = wall_s();
         for (int g = 0; g < n_gpus; ++g) {
             std::unique_ptr<Replica> R(new Replica);
             R->dev = devs[g];
@@ -1028,6 +1041,9 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             v.hdr = img.hdr;
             idx->reps.push_back(std::move(R));
         }
+        if (idx->opt.verbose)
+            fprintf(stderr, "[moni-gpu] index load: driver init %.2f s, decode + export %.2f s, upload of %.2f GB to %d GPU(s) %.2f s\n", t_init,
+                    t_load1 - t_load0, (double)idx->device_bytes / 1e9, n_gpus, wall_s() - t_load1);
         *out = idx.release();
         return 0;
     });

@@ -47,7 +47,7 @@ def host_sim():
     deps = srcs + [os.path.join(ROOT, "moni_align_b200", "csrc", f) for f in ("ms_core.cuh", "device_image.hpp", "index_files.hpp")]
     if not os.path.exists(out) or os.path.getmtime(out) < max(os.path.getmtime(d) for d in deps):
         os.makedirs(os.path.dirname(out), exist_ok=True)
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", *srcs, "-o", out])
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-pthread", "-x", "c++", *srcs, "-o", out])
     return out
 
 

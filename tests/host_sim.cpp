@@ -40,8 +40,23 @@ int main(int argc, char** argv) {
         const bool want_seeds = argc > 6;
         const uint32_t seed_min_len = want_seeds ? (uint32_t)atoll(argv[6]) : 0;
         std::vector<uint64_t> so, s_ref, s_len, s_qpos;
+        if (getenv("HOST_SIM_THREADS")) opt.threads = (uint32_t)atoi(getenv("HOST_SIM_THREADS"));
         HostImage img;
         build_move_table(bwt, opt, img);
+        {   // hash of the move-table image (rows, row starts, gap slots, run rows): the same for any exporter thread count
+            auto fnv = [](uint64_t h, const void* p, size_t k) {
+                const uint8_t* b = (const uint8_t*)p;
+                for (size_t i = 0; i < k; ++i) { h ^= b[i]; h *= 0x100000001b3ULL; }
+                return h;
+            };
+            uint64_t h = 0xcbf29ce484222325ULL;
+            h = fnv(h, img.rows.data(), img.rows.size() * sizeof(MoveRow));
+            h = fnv(h, img.row_pos.data(), img.row_pos.size() * sizeof(img.row_pos[0]));
+            h = fnv(h, img.slots.data(), img.slots.size() * sizeof(GapSlot));
+            h = fnv(h, img.crun_row.data(), img.crun_row.size() * sizeof(img.crun_row[0]));
+            fprintf(stderr, "host_sim: move table hash %016llx rows %llu max_scan %u\n", (unsigned long long)h,
+                    (unsigned long long)img.hdr.n_rows, img.hdr.max_scan);
+        }
         build_grammar_table(slp, opt, img);
         build_phi_tables(bwt, img);
         ImageView v;

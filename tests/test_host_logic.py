@@ -307,3 +307,20 @@ def test_cli_number_formatter(cli_selftest):
     vals += [int(x) for x in rng.integers(0, 2**63, size=2000)] + [int(x) >> int(s) for x, s in zip(rng.integers(0, 2**63, size=2000), rng.integers(0, 63, size=2000))]
     out = subprocess.run([cli_selftest, "u64"], input=" ".join(map(str, vals)).encode(), capture_output=True, check=True).stdout
     assert out.decode().split() == [str(v) for v in vals]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_exporter_image_does_not_depend_on_its_thread_count(case, host_sim, tmp_path):
+    """build_move_table cuts its row passes into parts with prefix-computed initial states: the move table (rows, row starts,
+    gap slots, run rows) must be the same bytes for 1, 2, 5 and one-row-per-part threads, with and without balancing cuts."""
+    import subprocess
+    b = tmp_path / "b.bin"
+    b.write_bytes(np.uint64(1).tobytes() + np.array([0, 4], dtype=np.uint64).tobytes() + b"ACGT")
+    for max_scan in (8, 2):
+        seen = set()
+        for th in (1, 2, 5, 100000):
+            r = subprocess.run([host_sim, os.path.join(GOLDEN, case + ".fa"), str(b), str(tmp_path / "o.bin"), "64", str(max_scan)],
+                               env=dict(os.environ, HOST_SIM_THREADS=str(th)), capture_output=True)
+            assert r.returncode == 0, r.stderr
+            seen.add(re.search(rb"move table hash ([0-9a-f]+) rows (\d+)", r.stderr).groups())
+        assert len(seen) == 1, (max_scan, seen)
