@@ -15,9 +15,12 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
+#include <functional>
 #include <stdexcept>
+#include <thread>
 
 namespace moni {
 namespace {
@@ -96,8 +99,30 @@ void skip_select_support(Cursor& c, const char* what) {
     for (uint64_t i = 0; i < sb; ++i) read_int_vector(c, 0, what);  // one long- or mini-block each
 }
 
-// Elias-Fano sd_vector -> positions of its 1 bits.  Returns the universe size.
-uint64_t read_sd_vector(Cursor& c, std::vector<uint64_t>& ones, const char* what) {
+// Decoding work found while walking a file: the walk itself only reads sizes, the decodes run afterwards on all cores.
+struct Tasks {
+    std::vector<std::function<void()>> list;
+    void add(std::function<void()> fn) { list.push_back(std::move(fn)); }
+    void run() {
+        const unsigned T = (unsigned)std::max<size_t>(1, std::min<size_t>({list.size(), (size_t)32, (size_t)std::max(1u, std::thread::hardware_concurrency())}));
+        std::atomic<size_t> next{0};
+        std::vector<std::exception_ptr> err(T);
+        auto work = [&](unsigned t) {
+            try {
+                for (size_t i; (i = next.fetch_add(1)) < list.size();) list[i]();
+            } catch (...) { err[t] = std::current_exception(); }
+        };
+        std::vector<std::thread> th;
+        for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
+        work(0);
+        for (auto& x : th) x.join();
+        list.clear();
+        for (auto& e : err) if (e) std::rethrow_exception(e);
+    }
+};
+
+// Elias-Fano sd_vector -> positions of its 1 bits.  Returns the universe size; `ones` is filled by a task.
+uint64_t read_sd_vector(Cursor& c, std::vector<uint64_t>& ones, const char* what, Tasks* tasks = nullptr) {
     const uint64_t size = c.u64(what);
     const uint8_t wl = c.u8(what);
     PackedView low = read_int_vector(c, 0, what);
@@ -106,29 +131,34 @@ uint64_t read_sd_vector(Cursor& c, std::vector<uint64_t>& ones, const char* what
     skip_select_support(c, what);
     const uint64_t m = low.size();
     ones.clear();
-    ones.reserve(m);
     if (wl != low.width && m) throw std::runtime_error(c.name + ": sd_vector wl/low width mismatch in " + what);
-    uint64_t i = 0;
-    const uint64_t nwords = (high.bits + 63) >> 6;
-    for (uint64_t w = 0; w < nwords && i < m; ++w) {
-        uint64_t x = high.word(w);
-        while (x && i < m) {
-            const uint64_t p = (w << 6) + (uint64_t)__builtin_ctzll(x);
-            x &= x - 1;
-            ones.push_back(((p - i) << wl) | (wl ? low.get(i) : 0));
-            ++i;
+    const std::string name = c.name;
+    auto decode = [&ones, low, high, wl, m, name, what]() {
+        ones.reserve(m);
+        uint64_t i = 0;
+        const uint64_t nwords = (high.bits + 63) >> 6;
+        for (uint64_t w = 0; w < nwords && i < m; ++w) {
+            uint64_t x = high.word(w);
+            while (x && i < m) {
+                const uint64_t p = (w << 6) + (uint64_t)__builtin_ctzll(x);
+                x &= x - 1;
+                ones.push_back(((p - i) << wl) | (wl ? low.get(i) : 0));
+                ++i;
+            }
         }
-    }
-    if (i != m) throw std::runtime_error(c.name + ": sd_vector high has fewer 1s than low entries in " + what);
+        if (i != m) throw std::runtime_error(name + ": sd_vector high has fewer 1s than low entries in " + what);
+    };
+    if (tasks) tasks->add(decode);
+    else decode();
     return size;
 }
 
 // ri::sparse_sd_vector: u64 u, then (if u != 0) the sd_vector.
-uint64_t read_sparse_sd(Cursor& c, std::vector<uint64_t>& ones, const char* what) {
+uint64_t read_sparse_sd(Cursor& c, std::vector<uint64_t>& ones, const char* what, Tasks* tasks = nullptr) {
     ones.clear();
     const uint64_t u = c.u64(what);
     if (u == 0) return 0;
-    read_sd_vector(c, ones, what);
+    read_sd_vector(c, ones, what, tasks);
     return u;
 }
 
@@ -140,7 +170,7 @@ void unpack(const PackedView& v, std::vector<uint64_t>& out) {
 
 // wt_huff<> -> the symbol sequence.  No rank structure is needed for a bulk decode: one cursor
 // per inner node, consumed in sequence order.
-void read_wt_huff(Cursor& c, std::vector<uint8_t>& seq) {
+void read_wt_huff(Cursor& c, std::vector<uint8_t>& seq, Tasks& tasks) {
     const uint64_t size = c.u64("wt.size");
     const uint64_t sigma = c.u64("wt.sigma");
     (void)sigma;
@@ -168,23 +198,25 @@ void read_wt_huff(Cursor& c, std::vector<uint8_t>& seq) {
             if (c_to_leaf[s] >= n_nodes) throw std::runtime_error(c.name + ": wt leaf id out of range");
             leaf_sym[c_to_leaf[s]] = s;
         }
-    seq.resize(size);
-    if (size == 0) return;
-    if (n_nodes == 0) throw std::runtime_error(c.name + ": empty wavelet tree for a non-empty sequence");
-    std::vector<uint64_t> cur(n_nodes);
-    for (uint64_t i = 0; i < n_nodes; ++i) cur[i] = nodes[i].bv_pos;
-    for (uint64_t i = 0; i < size; ++i) {
-        uint32_t v = 0;
-        while (nodes[v].child[0] != 0xFFFF) {
-            const uint64_t b = cur[v]++;
-            if (b >= bv.bits) throw std::runtime_error(c.name + ": wavelet tree bit cursor out of range");
-            const uint64_t bit = (bv.word(b >> 6) >> (b & 63)) & 1;
-            v = nodes[v].child[bit];
-            if (v >= n_nodes) throw std::runtime_error(c.name + ": wavelet tree child out of range");
+    if (size && n_nodes == 0) throw std::runtime_error(c.name + ": empty wavelet tree for a non-empty sequence");
+    const std::string name = c.name;
+    tasks.add([&seq, size, n_nodes, nodes, leaf_sym, bv, name]() {
+        seq.resize(size);
+        std::vector<uint64_t> cur(n_nodes);
+        for (uint64_t i = 0; i < n_nodes; ++i) cur[i] = nodes[i].bv_pos;
+        for (uint64_t i = 0; i < size; ++i) {
+            uint32_t v = 0;
+            while (nodes[v].child[0] != 0xFFFF) {
+                const uint64_t b = cur[v]++;
+                if (b >= bv.bits) throw std::runtime_error(name + ": wavelet tree bit cursor out of range");
+                const uint64_t bit = (bv.word(b >> 6) >> (b & 63)) & 1;
+                v = nodes[v].child[bit];
+                if (v >= n_nodes) throw std::runtime_error(name + ": wavelet tree child out of range");
+            }
+            if (leaf_sym[v] < 0) throw std::runtime_error(name + ": wavelet tree leaf without a symbol");
+            seq[i] = (uint8_t)leaf_sym[v];
         }
-        if (leaf_sym[v] < 0) throw std::runtime_error(c.name + ": wavelet tree leaf without a symbol");
-        seq[i] = (uint8_t)leaf_sym[v];
-    }
+    });
 }
 
 }  // namespace
@@ -208,14 +240,31 @@ void read_thrbv_ms(const std::string& path, FlatRlbwt& o, bool full) {
     if (o.n == 0 || o.R == 0 || o.R > o.n || B == 0) throw std::runtime_error(path + ": implausible n/R/B header");
     if (o.n >= (1ULL << 40)) throw std::runtime_error(path + ": BWT length >= 2^40 is not supported");
     if (o.R >= 0xFFFFFFF0ULL) throw std::runtime_error(path + ": run count >= 2^32 is not supported");
+    // the walk below only reads sizes and records where every member lies; the decodes run on all cores afterwards
+    Tasks tasks;
+    auto unpack_later = [&tasks](PackedView v, std::vector<uint64_t>& out) { tasks.add([v, &out]() { unpack(v, out); }); };
     std::vector<uint64_t> run_marks;
-    read_sparse_sd(c, run_marks, "bwt.runs");
+    read_sparse_sd(c, run_marks, "bwt.runs", &tasks);
     std::vector<std::vector<uint64_t>> per_letter(256);
-    for (int s = 0; s < 256; ++s) {
-        o.count[s] = read_sparse_sd(c, per_letter[s], "bwt.runs_per_letter");
-        o.nruns[s] = per_letter[s].size();
+    for (int s = 0; s < 256; ++s) o.count[s] = read_sparse_sd(c, per_letter[s], "bwt.runs_per_letter", &tasks);
+    read_wt_huff(c, o.heads, tasks);
+    if (full) {
+        read_sparse_sd(c, o.pred, "pred", &tasks);
+        unpack_later(read_int_vector(c, 0, "pred_to_run"), o.pred_to_run);
     }
-    read_wt_huff(c, o.heads);
+    unpack_later(read_int_vector(c, 0, "samples_last"), o.samples_last);
+    for (int s = 0; s < 256; ++s) read_sparse_sd(c, o.thr[s], "thresholds_per_letter", &tasks);
+    if (full) {
+        read_sparse_sd(c, o.pred_start, "pred_start", &tasks);
+        unpack_later(read_int_vector(c, 0, "pred_start_to_run"), o.pred_start_to_run);
+    }
+    unpack_later(read_int_vector(c, 0, "samples_start"), o.samples_start);
+    if (full && c.off != c.size) {                    // .thrbv.full.lcp.ms: sampled LCP values, one per run
+        if (read_int_vector(c, 0, "slcp").size() != o.R) throw std::runtime_error(path + ": slcp does not have R entries");
+    }
+    if (c.off != c.size) throw std::runtime_error(path + ": " + std::to_string(c.size - c.off) + " trailing bytes");
+    tasks.run();
+    for (int s = 0; s < 256; ++s) o.nruns[s] = per_letter[s].size();
     if (o.heads.size() != o.R) throw std::runtime_error(path + ": run_heads length != R");
     // run lengths = gaps of runs_per_letter[head] (ms_rle_string.hpp:284-285, sparse_sd_vector.hpp:179-187)
     o.starts.resize(o.R + 1);
@@ -244,31 +293,15 @@ void read_thrbv_ms(const std::string& path, FlatRlbwt& o, bool full) {
     }
     per_letter.clear();
     per_letter.shrink_to_fit();
-    if (full) {
-        read_sparse_sd(c, o.pred, "pred");
-        unpack(read_int_vector(c, 0, "pred_to_run"), o.pred_to_run);
-        if (o.pred_to_run.size() != o.R || o.pred.size() != o.R)
-            throw std::runtime_error(path + ": Phi structures (pred) do not have R entries");
-    }
-    unpack(read_int_vector(c, 0, "samples_last"), o.samples_last);
-    for (int s = 0; s < 256; ++s) {
-        read_sparse_sd(c, o.thr[s], "thresholds_per_letter");
+    if (full && (o.pred_to_run.size() != o.R || o.pred.size() != o.R))
+        throw std::runtime_error(path + ": Phi structures (pred) do not have R entries");
+    for (int s = 0; s < 256; ++s)
         for (size_t i = 1; i < o.thr[s].size(); ++i)
             if (o.thr[s][i] <= o.thr[s][i - 1]) throw std::runtime_error(path + ": thresholds not increasing");
-    }
-    if (full) {
-        read_sparse_sd(c, o.pred_start, "pred_start");
-        unpack(read_int_vector(c, 0, "pred_start_to_run"), o.pred_start_to_run);
-        if (o.pred_start_to_run.size() != o.R || o.pred_start.size() != o.R)
-            throw std::runtime_error(path + ": Phi structures (pred_start) do not have R entries");
-    }
-    unpack(read_int_vector(c, 0, "samples_start"), o.samples_start);
-    if (full && c.off != c.size) {                    // .thrbv.full.lcp.ms: sampled LCP values, one per run
-        if (read_int_vector(c, 0, "slcp").size() != o.R) throw std::runtime_error(path + ": slcp does not have R entries");
-    }
+    if (full && (o.pred_start_to_run.size() != o.R || o.pred_start.size() != o.R))
+        throw std::runtime_error(path + ": Phi structures (pred_start) do not have R entries");
     if (o.samples_last.size() != o.R || o.samples_start.size() != o.R)
         throw std::runtime_error(path + ": sample arrays do not have R entries");
-    if (c.off != c.size) throw std::runtime_error(path + ": " + std::to_string(c.size - c.off) + " trailing bytes");
 }
 
 void read_plain_slp(const std::string& path, FlatSlp& o) {

@@ -447,10 +447,15 @@ struct Replica {
     }
 };
 
+// One table of the image into a replica: from the host for the first replica, from the first replica's HBM for the others
+// (device to device over NVLink / NVSwitch where the GPUs are peers; cudaMemcpyPeerAsync stages through the host otherwise),
+// so the host link carries the image once however many GPUs hold it.
 template <typename T>
-void upload(DevBuf& b, const std::vector<T>& v, cudaStream_t s) {
+void upload(DevBuf& b, const std::vector<T>& v, cudaStream_t s, const DevBuf* from = nullptr, int from_dev = 0, int to_dev = 0) {
     b.reserve(std::max<size_t>(v.size() * sizeof(T), 16));
-    if (!v.empty()) CK(cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
+    if (v.empty()) return;
+    if (from) CK(cudaMemcpyPeerAsync(b.p, to_dev, from->p, from_dev, v.size() * sizeof(T), s));
+    else CK(cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
 }
 
 }  // namespace
@@ -938,25 +943,35 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
     if (!prefix || !out || n_gpus < 1) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
     *out = nullptr;
     return guarded([&]() -> int {
-        const double t_init0 = wall_s();
-        int ndev = 0;
-        CK(cudaGetDeviceCount(&ndev));
-        if (ndev < 1) throw CudaError("no CUDA device: libmoni_gpu has no CPU path");
-        const double t_init = wall_s() - t_init0;
         std::vector<int> devs(n_gpus);
         for (int g = 0; g < n_gpus; ++g) {
             devs[g] = gpus ? gpus[g] : g;
-            if (devs[g] < 0 || devs[g] >= ndev) { g_err = "GPU ordinal out of range"; return MONI_GPU_EINVAL; }
+            if (devs[g] < 0) { g_err = "GPU ordinal out of range"; return MONI_GPU_EINVAL; }
         }
         std::unique_ptr<moni_gpu_index> idx(new moni_gpu_index);
         { std::lock_guard<std::mutex> lock(g_opt_mu); idx->opt = g_opt; }
         if (getenv("MONI_GPU_VERBOSE")) idx->opt.verbose = true;
         const double t_load0 = wall_s();
-        // the CUDA contexts come up (hundreds of ms each) while the files are decoded
+        // the driver (seconds in a fresh process, more with many GPUs visible) and the CUDA contexts come up while the files
+        // are decoded; without a usable device the call still fails with MONI_GPU_ECUDA, whatever else went wrong
+        int ndev = 0;
+        cudaError_t init_err = cudaSuccess;
+        double t_init = 0;
         std::thread ctx_thread([&]() {
-            for (int d : devs) { if (cudaSetDevice(d) == cudaSuccess) cudaFree(nullptr); }
+            init_err = cudaGetDeviceCount(&ndev);
+            if (init_err == cudaSuccess)
+                for (int d : devs) { if (d < ndev && cudaSetDevice(d) == cudaSuccess) cudaFree(nullptr); }
+            t_init = wall_s() - t_load0;
         });
         struct Joiner { std::thread& t; ~Joiner() { if (t.joinable()) t.join(); } } ctx_join{ctx_thread};
+        auto require_devices = [&]() {
+            if (ctx_thread.joinable()) ctx_thread.join();
+            if (init_err != cudaSuccess || ndev < 1) {
+                cudaGetLastError();
+                throw CudaError(std::string("no CUDA device: libmoni_gpu has no CPU path") +
+                                (init_err != cudaSuccess ? std::string(" (") + cudaGetErrorString(init_err) + ")" : std::string()));
+            }
+        };
         HostImage img;
         // the two files are decoded and exported side by side (they fill disjoint members of the image)
         std::exception_ptr slp_err;
@@ -995,13 +1010,16 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             build_phi_tables(bwt, img);
         } catch (...) {
             slp_thread.join();
+            require_devices();
             throw;
         }
         slp_thread.join();
+        require_devices();
         if (slp_err) std::rethrow_exception(slp_err);
+        for (int d : devs)
+            if (d >= ndev) { g_err = "GPU ordinal out of range"; return MONI_GPU_EINVAL; }
         idx->hdr = img.hdr;
         idx->device_bytes = img.bytes() + sizeof(SymbolTables);
-        ctx_thread.join();
         const double t_load1 = wall_s();
         for (int g = 0; g < n_gpus; ++g) {
             std::unique_ptr<Replica> R(new Replica);
@@ -1011,16 +1029,26 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             R->lanes.resize(idx->opt.lanes);
             for (Lane& L : R->lanes) CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
             cudaStream_t st = R->stream();
-            upload(R->rows, img.rows, st);
-            upload(R->row_pos, img.row_pos, st);
-            upload(R->crun_row, img.crun_row, st);
-            upload(R->slots, img.slots, st);
-            upload(R->nodes, img.nodes, st);
-            upload(R->pool, img.pool, st);
-            upload(R->phi, img.phi, st);
-            upload(R->phi_inv, img.phi_inv, st);
-            upload(R->phi_dir, img.phi_dir, st);
-            upload(R->phi_inv_dir, img.phi_inv_dir, st);
+            const Replica* src = g ? idx->reps[0].get() : nullptr;      // replica 0 is complete (synchronized) by now
+            if (src && src->dev != R->dev) {                             // peer access lets the copy go GPU to GPU; failure is fine
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, R->dev, src->dev) == cudaSuccess && can) {
+                    const cudaError_t pe = cudaDeviceEnablePeerAccess(src->dev, 0);
+                    if (pe != cudaSuccess) cudaGetLastError();           // already enabled, or refused: the copy still works
+                }
+            }
+#define MONI_UP(member, table) upload(R->member, img.table, st, src ? &src->member : nullptr, src ? src->dev : 0, R->dev)
+            MONI_UP(rows, rows);
+            MONI_UP(row_pos, row_pos);
+            MONI_UP(crun_row, crun_row);
+            MONI_UP(slots, slots);
+            MONI_UP(nodes, nodes);
+            MONI_UP(pool, pool);
+            MONI_UP(phi, phi);
+            MONI_UP(phi_inv, phi_inv);
+            MONI_UP(phi_dir, phi_dir);
+            MONI_UP(phi_inv_dir, phi_inv_dir);
+#undef MONI_UP
             R->sym.reserve(sizeof(SymbolTables));
             CK(cudaMemcpyAsync(R->sym.p, &img.sym, sizeof(SymbolTables), cudaMemcpyHostToDevice, st));
             R->counters.reserve(sizeof(Counters));
@@ -1042,7 +1070,7 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             idx->reps.push_back(std::move(R));
         }
         if (idx->opt.verbose)
-            fprintf(stderr, "[moni-gpu] index load: driver init %.2f s, decode + export %.2f s, upload of %.2f GB to %d GPU(s) %.2f s\n", t_init,
+            fprintf(stderr, "[moni-gpu] index load: driver + contexts %.2f s beside decode + export %.2f s, upload of %.2f GB to %d GPU(s) %.2f s\n", t_init,
                     t_load1 - t_load0, (double)idx->device_bytes / 1e9, n_gpus, wall_s() - t_load1);
         *out = idx.release();
         return 0;
