@@ -324,6 +324,38 @@ def test_cli_reads_gzip_and_fasta(tmp_path):
     assert open(out + ".mems", "rb").read() == open(pre + ".mems", "rb").read()
 
 
+def test_cli_wide_results_for_reads_of_65536_bases_or_more(m, indexes, tmp_path):
+    """A batch with a read too long for the packed layouts goes through moni_gpu_ms / moni_gpu_mems inside the CLI; an empty
+    patterns file gives empty outputs.  Files equal the formatted results of the library calls (which the other tests pin)."""
+    import subprocess
+    pre = os.path.join(GOLDEN, "pan4")
+    names, seqs = read_fastq(pre + ".fq")
+    text = b"".join(bytes(s) for s in seqs)
+    long_read = (text * (70_000 // len(text) + 1))[:70_000]
+    names2, seqs2 = [b"short0", b"long", b"short1"], [bytes(seqs[0]), long_read, bytes(seqs[1])]
+    fq = tmp_path / "wide.fq"
+    with open(fq, "wb") as f:
+        for n, s in zip(names2, seqs2):
+            f.write(b"@" + n + b"\n" + s + b"\n+\n" + b"I" * len(s) + b"\n")
+    flat, offs = pack(seqs2)
+    ptr, ln = indexes["pan4"].matching_statistics(flat, offs)
+    mo, mp, ml = indexes["pan4"].maxrimal_exact_matches(flat, offs)
+    out = str(tmp_path / "o")
+    for exe in ("ms", "mems"):
+        r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", exe), pre + ".fa", "-p", str(fq), "-o", out, "-t", "4"], capture_output=True)
+        assert r.returncode == 0, r.stderr
+    assert open(out + ".pointers", "rb").read() == m.format_ms(names2, offs, ptr)
+    assert open(out + ".lengths", "rb").read() == m.format_ms(names2, offs, ln)
+    assert open(out + ".mems", "rb").read() == m.format_mems(names2, mo, mp, ml)
+    empty = tmp_path / "empty.fq"
+    empty.write_bytes(b"")
+    for exe in ("ms", "mems"):
+        r = subprocess.run([os.path.join(ROOT, "moni_align_b200", "bin", exe), pre + ".fa", "-p", str(empty), "-o", out + "e"], capture_output=True)
+        assert r.returncode == 0, r.stderr
+    for ext in (".pointers", ".lengths", ".mems"):
+        assert os.path.getsize(out + "e" + ext) == 0
+
+
 # ------------------------------------------------------------------------------ packed records, `moni align` front end
 def test_mems_packed_equals_mems(m, indexes):
     """moni_gpu_mems_packed: the same records as (query offset << 16) | length; refuses reads of 65536 bases or more."""
