@@ -93,7 +93,8 @@ int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offset
  * length (get_prev/next_occ_with_lcp :346-370; the bounded LCE of thirdparty/ShapedSlp/Common.hpp:250-295 is a direct
  * compare of the text in HBM).  Needs an index loaded from `<prefix>.thrbv.full.ms` (the Phi structures) with the text
  * resident.  max_per_direction bounds each walk (the reference's is unbounded); *truncated (may be NULL) is set to 1 if a
- * walk hit it.  Runs on the index's first GPU.  Capacity rule as for moni_gpu_mems.  moni_gpu_timing afterwards: t[0] seeds
+ * walk hit it (with max_per_direction <= 4096 and room for 2 * max + 1 staged positions per seed the lists come from a single
+ * walk; otherwise a counting walk and a filling walk).  Runs on the index's first GPU.  Capacity rule as for moni_gpu_mems.  moni_gpu_timing afterwards: t[0] seeds
  * in, t[1] counting walk + scan, t[2] filling walk, t[4] positions out, t[5] whole call. */
 int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
                        uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity, int* truncated);

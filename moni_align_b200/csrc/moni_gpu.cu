@@ -297,6 +297,29 @@ __global__ void __launch_bounds__(kBlock) k_occ_fill(ImageView v, const uint64_t
     occ_walk(v, ref[i], len[i], cap, occs + off[i], nullptr);
 }
 
+// One walk instead of two when the per-direction cap bounds a seed's list: positions go to a fixed-stride staging area
+// (stride = 2 cap + 1; HBM has the room), and a streaming pass packs them once the offsets are known.
+__global__ void __launch_bounds__(kBlock) k_occ_walk_staged(ImageView v, const uint64_t* __restrict__ ref, const uint32_t* __restrict__ len,
+                                                            uint64_t n_seeds, uint64_t cap, uint64_t stride, uint64_t* __restrict__ counts,
+                                                            uint64_t* __restrict__ staging, uint32_t* __restrict__ truncated) {
+    const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (i > n_seeds) return;
+    if (i == n_seeds) { counts[i] = 0; return; }
+    bool tr = false;
+    counts[i] = occ_walk(v, ref[i], len[i], cap, staging + i * stride, &tr);
+    if (tr) atomicOr(truncated, 1u);
+}
+
+__global__ void __launch_bounds__(kBlock) k_occ_pack(const uint64_t* __restrict__ staging, uint64_t stride, const uint64_t* __restrict__ off,
+                                                     uint64_t n_seeds, uint64_t* __restrict__ occs) {
+    const uint64_t i = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;      // a warp per seed
+    const uint32_t lane = threadIdx.x & 31;
+    if (i >= n_seeds) return;
+    const uint64_t a = off[i], cnt = off[i + 1] - a;
+    const uint64_t* src = staging + i * stride;
+    for (uint64_t k = lane; k < cnt; k += 32) occs[a + k] = src[k];
+}
+
 __global__ void k_widen_counts(const uint32_t* __restrict__ c, uint64_t* __restrict__ out, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = c[i];
@@ -426,7 +449,7 @@ struct Replica {
     std::vector<Lane> lanes;
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
     DevBuf phi, phi_inv, phi_dir, phi_inv_dir;            // `moni align` indexes only
-    DevBuf occ_ref, occ_len, occ_off, occ_out, occ_flag, occ_cub;   // moni_gpu_seed_occs scratch
+    DevBuf occ_ref, occ_len, occ_off, occ_out, occ_flag, occ_cub, occ_stage;   // moni_gpu_seed_occs scratch
     DevBuf shard_off, shard_pos, shard_len, shard_ref;   // multi-GPU mems: a shard's records wait here for their global offset
     ImageView view;
     std::mutex mu;
@@ -437,7 +460,7 @@ struct Replica {
         rows.release(); row_pos.release(); crun_row.release(); slots.release(); nodes.release(); pool.release();
         sym.release(); counters.release();
         phi.release(); phi_inv.release(); phi_dir.release(); phi_inv_dir.release();
-        occ_ref.release(); occ_len.release(); occ_off.release(); occ_out.release(); occ_flag.release(); occ_cub.release();
+        occ_ref.release(); occ_len.release(); occ_off.release(); occ_out.release(); occ_flag.release(); occ_cub.release(); occ_stage.release();
         shard_off.release(); shard_pos.release(); shard_len.release(); shard_ref.release();
         for (Lane& L : lanes) {
             L.scratch.release();
@@ -1245,8 +1268,22 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
         CK(cudaMemsetAsync(R.occ_flag.p, 0, 4, st));
         CK(cudaEventRecord(e[1], st));
         const unsigned blocks = (unsigned)((n_seeds + 1 + kBlock - 1) / kBlock);
-        k_occ_count<<<blocks, kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds, max_per_direction,
-                                               R.occ_off.as<uint64_t>(), R.occ_flag.as<uint32_t>());
+        // staged single walk when 2 cap + 1 positions per seed fit a bounded share of the free HBM; else count, then fill
+        uint64_t stride = 0;
+        if (max_per_direction <= 4096) {
+            const uint64_t want = (2 * max_per_direction + 1) * 8 * n_seeds;
+            size_t free_b = 0, total_b = 0;
+            CK(cudaMemGetInfo(&free_b, &total_b));
+            if (want <= R.occ_stage.cap || want <= std::min<uint64_t>((uint64_t)free_b / 4, 8ull << 30)) stride = 2 * max_per_direction + 1;
+        }
+        if (stride) {
+            R.occ_stage.reserve(stride * 8 * n_seeds);
+            k_occ_walk_staged<<<blocks, kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds, max_per_direction,
+                                                         stride, R.occ_off.as<uint64_t>(), R.occ_stage.as<uint64_t>(), R.occ_flag.as<uint32_t>());
+        } else {
+            k_occ_count<<<blocks, kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds, max_per_direction,
+                                                   R.occ_off.as<uint64_t>(), R.occ_flag.as<uint32_t>());
+        }
         g_launches++;
         size_t tmp = 0;
         CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, R.occ_off.as<uint64_t>(), R.occ_off.as<uint64_t>(), (int)(n_seeds + 1), st));
@@ -1265,8 +1302,12 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
             return MONI_GPU_ENOMEM;
         }
         R.occ_out.reserve(total * 8 + 16);
-        k_occ_fill<<<(unsigned)((n_seeds + kBlock - 1) / kBlock), kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds,
-                                                                               max_per_direction, R.occ_off.as<uint64_t>(), R.occ_out.as<uint64_t>());
+        if (stride)
+            k_occ_pack<<<(unsigned)((n_seeds * 32 + kBlock - 1) / kBlock), kBlock, 0, st>>>(R.occ_stage.as<uint64_t>(), stride, R.occ_off.as<uint64_t>(),
+                                                                                         n_seeds, R.occ_out.as<uint64_t>());
+        else
+            k_occ_fill<<<(unsigned)((n_seeds + kBlock - 1) / kBlock), kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds,
+                                                                                   max_per_direction, R.occ_off.as<uint64_t>(), R.occ_out.as<uint64_t>());
         g_launches++;
         CK(cudaGetLastError());
         CK(cudaEventRecord(e[3], st));
