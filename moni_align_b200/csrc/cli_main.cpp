@@ -57,7 +57,7 @@ struct SeqReader {
     std::vector<unsigned char> buf;
     size_t pos = 0, len = 0;
     int last = 0;   // the record marker already consumed ('>' or '@'), 0 = none yet
-    std::string header, qual;
+    std::string header;
     bool eof = false;
     explicit SeqReader(const std::string& path) : buf(1 << 20) {
         f = gzopen(path.c_str(), "r");
@@ -94,6 +94,21 @@ struct SeqReader {
             if (nl) return '\n';
         }
     }
+    // skips the rest of the current line; n = its characters other than carriage returns
+    int skip_line(size_t& n) {
+        n = 0;
+        for (;;) {
+            if (pos >= len && !fill()) return -1;
+            const unsigned char* s = buf.data() + pos;
+            const size_t avail = len - pos;
+            const unsigned char* nl = (const unsigned char*)memchr(s, '\n', avail);
+            const size_t k = nl ? (size_t)(nl - s) : avail;
+            n += k;
+            if (k && memchr(s, '\r', k)) for (size_t i = 0; i < k; ++i) n -= s[i] == '\r';
+            pos += k + (nl ? 1 : 0);
+            if (nl) return '\n';
+        }
+    }
     // Reads one record; name cut at first whitespace.  Returns false at end of file.
     bool next(std::string& name, std::string& seq) {
         int c;
@@ -118,10 +133,10 @@ struct SeqReader {
         if (c != '+') { if (c < 0) last = 0, eof = true; return true; }
         line(nullptr);                                   // rest of the '+' line
         size_t q = 0;
-        while (q < seq.size()) {                          // quality: as many characters as bases
-            qual.clear();
-            const int d = line(&qual);
-            q += qual.size();
+        while (q < seq.size()) {                          // quality: as many characters as bases (counted, not kept)
+            size_t k = 0;
+            const int d = skip_line(k);
+            q += k;
             if (d < 0) break;
         }
         last = 0;
@@ -174,12 +189,13 @@ struct Slot {
         seqs = nullptr; lo = nullptr; hi = nullptr; len16 = nullptr; cap = 0;
     }
     // grows the pinned buffers to hold `bases` (keeps the sequence bytes already there)
-    void ensure(uint64_t bases, bool mems) {
+    void ensure(uint64_t bases, bool mems, bool fatal = true) {
         if (bases <= cap) return;
         // doubling up to one full batch (+ room for the read that crosses the limit); beyond that only a single huge read grows it
         const uint64_t soft = (64u << 20) + (1u << 20);
         const uint64_t ncap = bases <= soft ? std::min<uint64_t>(std::max<uint64_t>(cap * 2, bases), soft) : std::max<uint64_t>(bases, cap * 2);
         char* ns = (char*)moni_gpu_host_alloc(ncap + 16);
+        if (!ns && !fatal) return;                 // pre-allocation beside the index load: the load reports what is wrong
         if (!ns) die("cannot allocate pinned host memory for the read batch");
         if (seqs) memcpy(ns, seqs, total());
         moni_gpu_host_free(seqs); moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(len16);
@@ -187,7 +203,11 @@ struct Slot {
         lo = (uint32_t*)moni_gpu_host_alloc((ncap + 4) * 4);
         hi = mems ? nullptr : (uint8_t*)moni_gpu_host_alloc(ncap + 16);
         len16 = mems ? nullptr : (uint16_t*)moni_gpu_host_alloc((ncap + 8) * 2);
-        if (!lo || (!mems && (!hi || !len16))) die("cannot allocate pinned host memory for the results");
+        if (!lo || (!mems && (!hi || !len16))) {
+            if (!fatal) { cap = 0; moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(len16); moni_gpu_host_free(seqs);
+                          lo = nullptr; hi = nullptr; len16 = nullptr; seqs = nullptr; return; }
+            die("cannot allocate pinned host memory for the results");
+        }
         cap = ncap;
     }
     void add(const std::string& name, const std::string& seq, bool mems) {
@@ -370,10 +390,31 @@ int main(int argc, char** argv) {
     }
     if (gpus.empty()) gpus.push_back(0);
 
+    // Batch slots of the processing pipeline (below).  Their pinned buffers are sized once from the file size (a FASTQ holds
+    // about one base per two bytes, a gzip four times that) and page-locked on a helper thread while the index loads:
+    // page-locking is slow enough that doing it batch by batch would show in the parse stage.
+    constexpr int kSlots = 3;
+    const uint64_t kBatchBases = 64u << 20, kBatchReads = 2u << 20;
+    Slot slots[kSlots];
+    uint64_t first_cap = 1u << 20;
+    {
+        struct stat st;
+        if (stat(patterns.c_str(), &st) == 0) {
+            const bool gz = patterns.size() > 3 && patterns.compare(patterns.size() - 3, 3, ".gz") == 0;
+            first_cap = std::min<uint64_t>(kBatchBases + (1u << 20), std::max<uint64_t>(first_cap, (uint64_t)st.st_size * (gz ? 4 : 1)));
+        }
+    }
+    const bool early = !getenv("MONI_CLI_NO_PREALLOC");
+    std::thread prealloc([&]() {
+        if (early) for (auto& sl : slots) sl.ensure(first_cap, mems, false);
+    });
+
     info("Construction of the matching statistics data structure");
     double t0 = now_s();
     moni_gpu_index* idx = nullptr;
-    if (moni_gpu_index_load(index.c_str(), gpus.data(), (int)gpus.size(), &idx) != 0) die(moni_gpu_last_error());
+    const int load_rc = moni_gpu_index_load(index.c_str(), gpus.data(), (int)gpus.size(), &idx);
+    prealloc.join();
+    if (load_rc != 0) die(moni_gpu_last_error());
     printf("[INFO] Elapsed time (s): %g\n", now_s() - t0);
 
     std::vector<char> ibuf(index.begin(), index.end());
@@ -391,12 +432,10 @@ int main(int argc, char** argv) {
 
     info("Processing patterns");
     t0 = now_s();
+    const double t_proc0 = t0;
     // Three stages on three threads, batches of ~64 M bases in a ring of slots: while the GPUs work on one batch the next
     // is being parsed and the previous one formatted and written (the reference splits the file and runs a worker per
     // part instead, src/matching_statistics.cpp:311-426; records come out in input order either way).
-    constexpr int kSlots = 3;
-    const uint64_t kBatchBases = 64u << 20, kBatchReads = 2u << 20;
-    Slot slots[kSlots];
     int state[kSlots] = {0, 0, 0};            // 0 = free, 1 = parsed, 2 = results ready
     std::mutex mu;
     std::condition_variable cv;
@@ -411,16 +450,6 @@ int main(int argc, char** argv) {
     uint64_t n_reads = 0, n_bases = 0;
     double t_parse = 0, t_gpu = 0, t_out = 0;
 
-    // pinned buffers are sized once from the file size (a FASTQ holds about one base per two bytes, a gzip four times that):
-    // page-locking is slow enough that growing by doubling would show in the parse stage
-    uint64_t first_cap = 1u << 20;
-    {
-        struct stat st;
-        if (stat(patterns.c_str(), &st) == 0) {
-            const bool gz = patterns.size() > 3 && patterns.compare(patterns.size() - 3, 3, ".gz") == 0;
-            first_cap = std::min<uint64_t>(kBatchBases + (1u << 20), std::max<uint64_t>(first_cap, (uint64_t)st.st_size * (gz ? 4 : 1)));
-        }
-    }
     std::thread parser([&]() {
         SeqReader rd(patterns);
         std::string name, seq;
@@ -479,6 +508,7 @@ int main(int argc, char** argv) {
         wait_for(k, 2);
         Slot& B = slots[k];
         const double ts = now_s();
+        if (getenv("MONI_GPU_VERBOSE")) fprintf(stderr, "[moni-gpu] cli batch ready at %.3f s: %zu reads\n", ts - t_proc0, B.n_reads());
         if (B.n_reads()) {
             n_reads += B.n_reads();
             n_bases += B.total();
@@ -494,11 +524,14 @@ int main(int argc, char** argv) {
         set_state(k, 0);
         if (last) break;
     }
+    const double t_tail0 = now_s();
     parser.join();
     caller.join();
     out1.close_file();
     out2.close_file();
+    const double t_tail1 = now_s();
     for (auto& sl : slots) sl.release();
+    if (getenv("MONI_GPU_VERBOSE")) fprintf(stderr, "[moni-gpu] cli tail: join + close %.3f s, unpin %.3f s\n", t_tail1 - t_tail0, now_s() - t_tail1);
     printf("[INFO] Elapsed time (s): %g\n", now_s() - t0);
     printf("[INFO] reads %llu bases %llu gpu-call time (s) %g parse (s) %g format+write (s) %g gpus %zu\n", (unsigned long long)n_reads,
            (unsigned long long)n_bases, t_gpu, t_parse, t_out, gpus.size());
