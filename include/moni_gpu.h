@@ -76,6 +76,11 @@ int moni_gpu_mems32(moni_gpu_index* idx, const char* seqs, const uint64_t* offse
 int moni_gpu_mems_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
                          uint64_t* mem_offsets, uint32_t* mem_rec, uint64_t mem_capacity);
 
+/* Same records as one 16-bit word each, (query offset << 8) | length: for batches whose reads are all shorter than 256 bases
+ * (short-read sequencing; else MONI_GPU_EINVAL).  2 bytes per record leave the device. */
+int moni_gpu_mems_packed16(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
+                           uint64_t* mem_offsets, uint16_t* mem_rec, uint64_t mem_capacity);
+
 /* Replaces seed_finder<slp_t, ms_t>::find_mems(const kseq_t*, std::vector<mem_t>&, r_offset, mate)
  * (include/aligner/seed_finder.hpp:126-166), the seed stage of `moni align`, for a whole batch: same two passes, with the
  * record rule of :148 -- l >= pl and n_Ns < l and l >= min_len (n_Ns = the run of 'N' ending the characters matched so

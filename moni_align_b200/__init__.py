@@ -38,7 +38,7 @@ class MoniGpuError(RuntimeError):
 
 
 EXPORTS = [
-    "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems", "moni_gpu_mems32",
+    "moni_gpu_index_load", "moni_gpu_index_free", "moni_gpu_index_info", "moni_gpu_ms", "moni_gpu_mems", "moni_gpu_mems32", "moni_gpu_mems_packed16",
     "moni_gpu_mems_packed", "moni_gpu_seeds", "moni_gpu_seed_occs", "moni_gpu_ms_packed", "moni_gpu_host_alloc_near", "moni_gpu_numa_node",
     "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
@@ -65,6 +65,7 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_mems.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, _u64p, _u64p, ctypes.c_uint64]
     L.moni_gpu_mems32.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, ctypes.c_uint64]
     L.moni_gpu_mems_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, ctypes.c_uint64]
+    L.moni_gpu_mems_packed16.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, ctypes.c_uint64]
     L.moni_gpu_seeds.argtypes = [vp, vp, _u64p, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, vp, vp, ctypes.c_uint64]
     L.moni_gpu_seed_occs.argtypes = [vp, _u64p, vp, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, ctypes.c_uint64, ctypes.POINTER(ci)]
     L.moni_gpu_counters.argtypes = [vp, _u64p, ci]
@@ -228,6 +229,20 @@ class MoniIndex:
             _check(self._L.moni_gpu_mems(self._h, _ptr(seqs), _u64(offsets), nr, _u64(mo), _u64(mp), _u64(ml), mp.shape[0]))
         k = int(mo[nr])
         return mo, mp[:k], ml[:k]
+
+    def maxrimal_exact_matches_packed16(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
+        """(mem_offsets uint64[n+1], mem_rec uint16[k]) with mem_rec = (query offset << 8) | length -- moni_gpu_mems_packed16;
+        every read must be shorter than 256 bases."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        nr = offsets.shape[0] - 1
+        if out is None:
+            mo = np.empty(nr + 1, dtype=np.uint64)
+            rec = np.empty(max(int(offsets[-1]), 1), dtype=np.uint16)
+        else:
+            mo, rec = out
+        _check(self._L.moni_gpu_mems_packed16(self._h, _ptr(seqs), _u64(offsets), nr, _u64(mo), _ptr(rec), rec.shape[0]))
+        return mo, rec[:int(mo[nr])]
 
     def maxrimal_exact_matches_packed(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
         """(mem_offsets uint64[n+1], mem_rec uint32[k]) with mem_rec = (query offset << 16) | length -- moni_gpu_mems_packed;

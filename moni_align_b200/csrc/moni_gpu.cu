@@ -264,16 +264,18 @@ __global__ void __launch_bounds__(kBlock) k_seed_gather(const uint64_t* __restri
     }
 }
 
-// Same, one 32-bit word per record: (query offset << 16) | length.  Only for chunks whose reads are shorter than 2^16.
+// Same, one word per record: (query offset << SHIFT) | length -- 32-bit words with SHIFT 16 for chunks whose reads are shorter
+// than 2^16, 16-bit words with SHIFT 8 for reads shorter than 2^8 (what bounds the call is the bytes that leave the device).
+template <typename RecT, int SHIFT>
 __global__ void __launch_bounds__(kBlock) k_mem_gather_packed(const uint64_t* __restrict__ rec, const uint64_t* __restrict__ offs,
                                                               uint64_t base, uint32_t n_reads, const uint64_t* __restrict__ moff,
-                                                              uint32_t* __restrict__ mem_rec) {
+                                                              RecT* __restrict__ mem_rec) {
     const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (r >= n_reads) return;
     const uint64_t o = offs[r] - base, a = moff[r], cnt = moff[r + 1] - a;
     for (uint64_t k = lane; k < cnt; k += 32) {
         const uint64_t x = rec[o + k];
-        mem_rec[a + k] = ((uint32_t)(x >> 32) << 16) | (uint32_t)(x & 0xFFFFu);
+        mem_rec[a + k] = (RecT)(((uint32_t)(x >> 32) << SHIFT) | (uint32_t)(x & ((1u << SHIFT) - 1)));
     }
 }
 
@@ -609,8 +611,11 @@ void launch_compact(Scratch& S, const ChunkPlan& p, int rec_bytes, cudaStream_t 
         k_seed_gather<<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.rec_ref.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
                                                  S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>(), S.mem_ref.as<uint64_t>());
     else if (rec_bytes == 2)
-        k_mem_gather_packed<<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
-                                                       S.mem_pos.as<uint32_t>());
+        k_mem_gather_packed<uint32_t, 16><<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                                     S.mem_pos.as<uint32_t>());
+    else if (rec_bytes == 1)
+        k_mem_gather_packed<uint16_t, 8><<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                                    S.mem_pos.as<uint16_t>());
     else if (rec_bytes == 4)
         k_mem_gather<uint32_t><<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
                                                           S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>());
@@ -745,6 +750,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
         launch_pass1(R, S, p, L.stream);
         CK(cudaEventRecord(e[2], L.stream));
         if (out.fmt == 2 && mems && p.max_len > 0xFFFFull) throw BadBatch("packed MEM records need reads shorter than 65536 bases");
+        if (out.fmt == 1 && mems && p.max_len > 0xFFull) throw BadBatch("16-bit MEM records need reads shorter than 256 bases");
         launch_pass2(R, S, p, mode, L.stream, out.min_len);
         CK(cudaEventRecord(e[3], L.stream));
         if (mems) {
@@ -1233,6 +1239,11 @@ int moni_gpu_mems32(moni_gpu_index* idx, const char* seqs, const uint64_t* offse
 int moni_gpu_mems_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
                          uint32_t* mem_rec, uint64_t mem_capacity) {
     return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_rec, 4, nullptr, 0, nullptr, 0, mem_capacity, 2));
+}
+
+int moni_gpu_mems_packed16(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
+                           uint16_t* mem_rec, uint64_t mem_capacity) {
+    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_rec, 2, nullptr, 0, nullptr, 0, mem_capacity, 1));
 }
 
 int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t min_len,

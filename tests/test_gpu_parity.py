@@ -544,3 +544,38 @@ def test_numa_near_pinned_buffers(m, indexes):
     a[:] = 7
     assert int(a.sum()) == 7000
     assert m.load_library().moni_gpu_numa_node(0) >= -1
+
+
+def test_mems_packed16_equals_mems(m, indexes):
+    """moni_gpu_mems_packed16: the same records as (query offset << 8) | length for reads shorter than 256 bases (one call, small
+    chunks, three replicas); a longer read is refused."""
+    for case in CASES:
+        names, seqs = read_fastq(os.path.join(GOLDEN, case + ".fq"))
+        short = [s for s in seqs if len(s) < 256]
+        assert len(short) > 20
+        flat, offs = pack(short)
+        a = indexes[case].maxrimal_exact_matches(flat, offs)
+        mo, rec = indexes[case].maxrimal_exact_matches_packed16(flat, offs)
+        assert rec.dtype == np.uint16
+        assert np.array_equal(a[0], mo) and np.array_equal(a[1], rec >> 8) and np.array_equal(a[2], rec & 0xFF)
+    names, seqs = read_fastq(os.path.join(GOLDEN, "pan4.fq"))
+    short = [s for s in seqs if len(s) < 256]
+    flat, offs = pack(short)
+    three = m.MoniIndex(os.path.join(GOLDEN, "pan4.fa"), gpus=[0, 0, 0])
+    a = three.maxrimal_exact_matches(flat, offs)
+    m.set_option("chunk_bases", 1000)
+    m.set_option("chunk_min_reads", 0)
+    try:
+        small = m.MoniIndex(os.path.join(GOLDEN, "pan4.fa"))
+    finally:
+        m.set_option("chunk_bases", 1 << 24)
+        m.set_option("chunk_min_reads", 98304)
+    for ix in (three, small):
+        mo, rec = ix.maxrimal_exact_matches_packed16(flat, offs)
+        assert np.array_equal(a[0], mo) and np.array_equal(a[1], rec >> 8) and np.array_equal(a[2], rec & 0xFF)
+    flat, offs = pack(short + [b"A" * 256])
+    with pytest.raises(m.MoniGpuError) as e:
+        small.maxrimal_exact_matches_packed16(flat, offs)
+    assert e.value.code == -1
+    three.close()
+    small.close()
