@@ -1,20 +1,27 @@
 #!/usr/bin/env python
-"""bench.py -- `moni mems` hot path on B200 (BASELINE.json metric: MS+MEM reads/s, bases/s, % of HBM roofline).
+"""bench.py -- `moni ms` / `moni mems` hot path on B200 (BASELINE.json metric: MS+MEM reads/s, bases/s, % of the HBM
+random-access roofline).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|small]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg3|cfg2s|cfg1|cfg4s|small]
 
-One "step" = one pass of the hot path (MS pointers -> MS lengths -> MEM records) over one batch of synthetic
-reads.  Default workload: BASELINE.json configs[1] stand-in (tools/workloads.py: 61.4 Mbp x 7 haplotypes,
-1M x 2 x 150 bp paired-end reads per GPU).  N > 1 is launched by torchrun, one rank per GPU; the index is
-replicated, every rank processes its own batch (weak scaling), no collective on the data path; torch.distributed
-carries only the barrier and the max-over-ranks of the device times.
+One "step" = one pass of the hot path over one batch of synthetic reads: MS pointers -> MS lengths -> MEM records (`mems`,
+the headline `value`), and the same two passes with full pointer/length arrays as the result (`ms`, reported under "ms").
+Default workload at N = 1: BASELINE.json configs[2], the largest single-GPU configuration (tools/workloads.py "cfg3":
+40 Mbp x 32 haplotypes, n = 1.28 G; 2 M reads per step = the first 1 M pairs of the 10 M-read set).  N > 1 is launched by
+torchrun, one rank per GPU: the index is replicated, every rank processes its own batch (weak scaling), no collective on the
+data path; torch.distributed carries only the barrier and the max-over-ranks of the device times.
 
-`value`   whole-job reads/s with the reads already resident in HBM (kernels only, CUDA events on the library's
-          launching stream, summed over the K timed steps, max over ranks).
-`e2e`     the same metric through the public C-ABI call moni_gpu_mems() with pinned HOST buffers: host->device
-          copy of the reads and device->host copy of the MEM records inside the timed region.
-`--impl reference` times the UNMODIFIED reference `mems` binary (oracle/_ref/bin, built from /root/reference) on the
-          host cores with -t nproc, on a bounded sample of the same workload.
+`value`        whole-job reads/s with the reads already resident in HBM (kernels only, CUDA events on the library's launching
+               stream, summed over the K timed steps, max over ranks).
+`e2e`          the same metric through the public C-ABI call with pinned HOST buffers: host->device copy of the reads and
+               device->host copy of the results inside the timed region.  `e2e` is the call that returns the reference's own
+               record type (u64 pairs, moni_gpu_mems); the packed-record variants are reported beside it.
+`parity_sample` the reference `ms` / `mems` binaries run on a sample of this very batch (the `cpu_baseline` leg) and their
+               output files are compared number by number with what the GPU returned for those reads.
+`roofline`     dominant kernel against the streaming HBM peak (MEASURED_PEAKS.json) and against the random-line rate of the
+               box measured in this process (moni_gpu_probe_random_lines).
+`--impl reference` times the UNMODIFIED reference `mems` binary (oracle/_ref/bin, built from /root/reference) on the host
+               cores with -t nproc, on a bounded sample of the same workload.
 """
 from __future__ import annotations
 
@@ -33,7 +40,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
-
+DEFAULT_WORKLOAD = "cfg3"
 _REAL_STDOUT = None
 
 
@@ -99,22 +106,28 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------------ reference arm
-def write_sample_fastq(reads: np.ndarray, path: str) -> None:
-    import synth
-    synth.write_fastq_matrix(path, reads)
-
-
-def run_reference_mems(prefix: str, fastq: str, threads: int) -> float:
-    """Seconds of the reference's own 'Processing patterns' phase (src/mems.cpp dispatcher timer)."""
+def run_reference(cmd: str, prefix: str, fastq: str, threads: int, out_prefix: str) -> float:
+    """Seconds of the reference's own 'Processing patterns' phase (src/matching_statistics.cpp:500-524, src/mems.cpp dispatcher)."""
     import build_index
-    with tempfile.TemporaryDirectory() as td:
-        r = build_index.run_reference("mems", prefix, fastq, os.path.join(td, "out"), threads=threads)
+    r = build_index.run_reference(cmd, prefix, fastq, out_prefix, threads=threads)
     if r["phase"] is None:
         raise RuntimeError("could not parse the reference's phase timer:\n" + r["stdout"][-800:])
     return float(r["phase"])
 
 
+def sample_rows(n_reads: int, k: int) -> np.ndarray:
+    """Rows of a [R1 block | R2 block] batch that make a k-read sample: the first k/2 pairs, both mates."""
+    half = n_reads // 2
+    k2 = max(1, min(k // 2, half))
+    return np.concatenate([np.arange(k2), half + np.arange(k2)])
+
+
+def bench_pairs(w: dict, args) -> int:
+    return args.pairs or w.get("bench_pairs", w["pairs"])
+
+
 def reference_arm(args) -> None:
+    import synth
     import workloads
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -125,14 +138,14 @@ def reference_arm(args) -> None:
     w = workloads.WORKLOADS[args.workload]
     prefix = workloads.ensure_index(args.workload)
     cores = os.cpu_count() or 1
-    pairs = max(1000, args.ref_reads // 2)
+    pairs = max(500, args.ref_reads // 2)
     reads = workloads.reads_of(args.workload, pairs=pairs)
     with tempfile.TemporaryDirectory() as td:
         fq = os.path.join(td, "sample.fq")
-        write_sample_fastq(reads, fq)
+        synth.write_fastq_matrix(fq, reads)
         times = []
         for s in range(args.warmup + args.steps):
-            t = run_reference_mems(prefix, fq, cores)
+            t = run_reference("mems", prefix, fq, cores, os.path.join(td, "out"))
             log(f"reference step {s}: {t:.2f} s for {reads.shape[0]} reads on {cores} threads")
             if s >= args.warmup:
                 times.append(t)
@@ -174,6 +187,66 @@ def bind_near_gpu(local: int) -> str:
         return f"skipped: {type(e).__name__}: {e}"
 
 
+# ------------------------------------------------------------------------------------------ checker: reference on a sample
+def cpu_baseline_and_parity(args, prefix, reads_flat, n_reads, read_len, gpu_mems, gpu_ms):
+    """Runs the unmodified reference `mems` and `ms` on a sample of the batch (all host cores) and compares their output files
+    with the GPU results for the same reads.  gpu_mems = (mem_offsets, mem_pos, mem_len) of the whole batch, gpu_ms = (pointers,
+    lengths).  Returns (cpu_baseline, parity_sample)."""
+    import refparse
+    import synth
+    if _ORIG_AFFINITY:      # the reference gets every host core the process was given, not only the GPU's neighbours
+        os.sched_setaffinity(0, _ORIG_AFFINITY[0])
+    cores = os.cpu_count() or 1
+    rows = sample_rows(n_reads, args.ref_reads)
+    sample = reads_flat.reshape(n_reads, read_len)[rows]
+    par = {"reads": int(rows.shape[0]), "against": "output files of the unmodified reference binaries (oracle/_ref/bin/{mems,ms})"}
+    with tempfile.TemporaryDirectory() as td:
+        fq = os.path.join(td, "sample.fq")
+        synth.write_fastq_matrix(fq, sample)
+        sec = run_reference("mems", prefix, fq, cores, os.path.join(td, "ref"))
+        cpu = {"value": rows.shape[0] / sec, "unit": "reads/s", "cores": cores, "kind": "reference",
+               "sample": f"{rows.shape[0]} reads of this batch, reference `mems -t {cores}`, its own processing-phase timer ({sec:.2f} s)"}
+        _, cnt, qoff, qlen = refparse.parse_mems(os.path.join(td, "ref.mems"))
+        mo, mp, ml = gpu_mems
+        a, b = mo[rows].astype(np.int64), mo[rows + 1].astype(np.int64)
+        same_counts = bool(np.array_equal(cnt.astype(np.int64), b - a))
+        if same_counts:
+            idx = np.concatenate([np.arange(x, y) for x, y in zip(a.tolist(), b.tolist())]) if rows.shape[0] else np.zeros(0, np.int64)
+            par["mems_identical"] = bool(np.array_equal(mp[idx], qoff) and np.array_equal(ml[idx], qlen))
+        else:
+            par["mems_identical"] = False
+        par["mems_records"] = int(cnt.sum())
+        if gpu_ms is not None:
+            sec_ms = run_reference("ms", prefix, fq, cores, os.path.join(td, "refms"))
+            cpu["ms"] = {"value": rows.shape[0] / sec_ms, "unit": "reads/s", "sample": f"same reads, reference `ms -t {cores}` ({sec_ms:.2f} s)"}
+            _, _, pv = refparse.parse_values(os.path.join(td, "refms.pointers"))
+            _, _, lv = refparse.parse_values(os.path.join(td, "refms.lengths"))
+            ptr, ln = gpu_ms
+            g_ptr = ptr.reshape(n_reads, read_len)[rows].reshape(-1)
+            g_len = ln.reshape(n_reads, read_len)[rows].reshape(-1)
+            par["pointers_identical"] = bool(np.array_equal(g_ptr, pv))
+            par["lengths_identical"] = bool(np.array_equal(g_len, lv))
+    par["identical"] = bool(par.get("mems_identical") and par.get("pointers_identical", True) and par.get("lengths_identical", True))
+    return cpu, par
+
+
+def random_line_peak(m, local: int) -> dict:
+    """The random-access roofline of this GPU, measured now (dependent random 32-byte accesses over a 3 GiB table)."""
+    out = {"table_bytes": 3 << 30, "unit": "lines/s", "line_bytes": 128, "points": []}
+    best = 0.0
+    for shape, k, b in ((0, 1, 6), (0, 2, 6), (0, 4, 4), (2, 8, 8)):
+        try:
+            r = m.probe_random_lines(local, 3 << 30, shape, k, b, 384)
+            out["points"].append({"shape": r["shape"], "chains_per_sm": r["chains_per_sm"], "lines_per_s": r["lines_per_s"]})
+            best = max(best, r["lines_per_s"])
+        except Exception as e:
+            out["points"].append({"shape": shape, "chains_per_thread": k, "error": str(e)})
+    m.probe_release()
+    out["value"] = best
+    out["as_line_traffic_gb_per_s"] = best * 128 / 1e9
+    return out
+
+
 # ------------------------------------------------------------------------------------------ our arm
 def ours_arm(args) -> None:
     import torch
@@ -195,7 +268,7 @@ def ours_arm(args) -> None:
         dist.init_process_group("nccl", device_id=dev)
     w = workloads.WORKLOADS[args.workload]
     if rank == 0:
-        prefix = workloads.ensure_index(args.workload)
+        workloads.ensure_index(args.workload)
     if world > 1:
         dist.barrier()
     prefix = workloads.index_prefix(args.workload)
@@ -210,20 +283,22 @@ def ours_arm(args) -> None:
     t_load = time.time() - t0
     log(f"rank {rank}: index n={ix.n} r={ix.r} image {ix.device_bytes / 1e9:.2f} GB loaded in {t_load:.1f} s")
 
+    t0 = time.time()
     text = workloads.text_of(args.workload)
-    reads = workloads.reads_of(args.workload, text=text, pairs=args.pairs or w["pairs"], seed_shift=1000 * rank)
+    reads = workloads.reads_of(args.workload, text=text, pairs=bench_pairs(w, args), seed_shift=1000 * rank)
     del text
     n_reads, read_len = reads.shape
     total = n_reads * read_len
-    # pinned host buffers for the end-to-end leg
+    log(f"rank {rank}: {n_reads} reads of {read_len} bases prepared in {time.time() - t0:.1f} s")
+    # pinned host buffers for the end-to-end legs: two result pools, every leg uses views of them
     h_seqs = m.pinned_empty(total, np.uint8, gpu=local)
     h_seqs[:] = reads.reshape(-1)
+    del reads
     h_offs = m.pinned_empty(n_reads + 1, np.uint64, gpu=local)
     h_offs[:] = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(read_len)
     h_mo = m.pinned_empty(n_reads + 1, np.uint64, gpu=local)
-    h_mp = m.pinned_empty(total, np.uint64, gpu=local)
-    h_ml = m.pinned_empty(total, np.uint64, gpu=local)
-    del reads
+    pool_a = m.pinned_empty(total, np.uint64, gpu=local)
+    pool_b = m.pinned_empty(total, np.uint64, gpu=local)
 
     def barrier():
         if world > 1:
@@ -238,33 +313,33 @@ def ours_arm(args) -> None:
     cnt = ix.counters(reset=True)
     m.set_option("count", 0)
 
-    # ---- kernel-only leg (inputs resident in HBM)
-    for _ in range(args.warmup):
-        rb.run("mems")
-    barrier()
+    # ---- kernel-only legs (inputs resident in HBM): mems is the headline, ms beside it
+    def resident_leg(what):
+        for _ in range(args.warmup):
+            rb.run(what)
+        barrier()
+        l0 = m.launch_count()
+        k_ms = np.zeros(3)
+        for _ in range(args.steps):
+            t = rb.run(what)
+            k_ms += np.array([t["pass1_ms"], t["pass2_ms"], t["compact_ms"]])
+        barrier()
+        return k_ms, m.launch_count() - l0
+
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
-    launches0 = m.launch_count()
-    k_ms = np.zeros(3)
-    for _ in range(args.steps):
-        t = rb.run("mems")
-        k_ms += np.array([t["pass1_ms"], t["pass2_ms"], t["compact_ms"]])
-    barrier()
-    launches = m.launch_count() - launches0
+    k_ms, launches = resident_leg("mems")
     dev_ms = max_over_ranks(float(k_ms.sum()), dev)
     mo, mp, ml = rb.fetch_mems()
     n_mems = int(mo[-1])
+    kms_ms, launches_ms = resident_leg("ms")
+    dev_ms_ms = max_over_ranks(float(kms_ms.sum()), dev)
+    r_ptr, r_len = rb.fetch_ms()
     rb.close()
 
-    # ---- end-to-end leg through the C ABI with host buffers: moni_gpu_mems32 (32-bit record fields) is the headline,
-    # moni_gpu_mems (64-bit fields, twice the device->host bytes) is reported beside it
-    h_mp32 = m.pinned_empty(total, np.uint32, gpu=local)
-    h_ml32 = m.pinned_empty(total, np.uint32, gpu=local)
-
-    def e2e_leg(out):
-        call = (ix.maxrimal_exact_matches if len(out) == 3 else
-                ix.maxrimal_exact_matches_packed16 if out[1].dtype == np.uint16 else ix.maxrimal_exact_matches_packed)
+    # ---- end-to-end legs through the C ABI with pinned host buffers
+    def e2e_leg(call, out):
         for _ in range(args.warmup):
             call(h_seqs, h_offs, out=out)
         barrier()
@@ -277,37 +352,57 @@ def ours_arm(args) -> None:
             stage += np.array([tt[k] for k in ("h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms")])
         barrier()
         wall = (time.perf_counter() - t_wall) * 1e3
-        return max_over_ranks(dev_sum, dev), max_over_ranks(wall, dev), stage
+        return {"dev": max_over_ranks(dev_sum, dev), "wall": max_over_ranks(wall, dev), "stage": stage}
 
-    e2e64_dev_ms, e2e64_wall_ms, stage64 = e2e_leg((h_mo, h_mp, h_ml))
-    same64 = bool(np.array_equal(h_mo, mo) and np.array_equal(h_mp[:n_mems], mp) and np.array_equal(h_ml[:n_mems], ml))
+    legs = {}
+    # mems, u64 records: the reference's own record type (std::pair<size_t,size_t>, src/mems.cpp:277-279)
+    legs["mems_u64"] = e2e_leg(ix.maxrimal_exact_matches, (h_mo, pool_a, pool_b))
+    same = {"mems_u64": bool(np.array_equal(h_mo, mo) and np.array_equal(pool_a[:n_mems], mp) and np.array_equal(pool_b[:n_mems], ml))}
+    gpu_mems = (h_mo.copy(), pool_a[:n_mems].copy(), pool_b[:n_mems].copy())      # for the parity sample: what the ABI call returned
+    a32, b32 = pool_a.view(np.uint32)[:total], pool_b.view(np.uint32)[:total]
     h_mo[:] = 0
-    e2e32_dev_ms, e2e32_wall_ms, stage32 = e2e_leg((h_mo, h_mp32, h_ml32))
-    same32 = bool(np.array_equal(h_mo, mo) and np.array_equal(h_mp32[:n_mems], mp) and np.array_equal(h_ml32[:n_mems], ml))
-    # one packed 32-bit word per record (reads are shorter than 65536 bases)
+    legs["mems_u32"] = e2e_leg(ix.maxrimal_exact_matches, (h_mo, a32, b32))
+    same["mems_u32"] = bool(np.array_equal(h_mo, mo) and np.array_equal(a32[:n_mems], mp) and np.array_equal(b32[:n_mems], ml))
     h_mo[:] = 0
-    h_rec = h_mp32
-    e2e_dev_ms, e2e_wall_ms, stage = e2e_leg((h_mo, h_rec))
-    same = bool(same64 and same32 and np.array_equal(h_mo, mo) and np.array_equal(h_rec[:n_mems] >> 16, mp)
-                and np.array_equal(h_rec[:n_mems] & 0xFFFF, ml))
-    e2e_api, rec_bytes, e2e_p32 = "moni_gpu_mems_packed", 4, None
+    legs["mems_packed32"] = e2e_leg(ix.maxrimal_exact_matches_packed, (h_mo, a32))
+    same["mems_packed32"] = bool(np.array_equal(h_mo, mo) and np.array_equal(a32[:n_mems] >> 16, mp) and np.array_equal(a32[:n_mems] & 0xFFFF, ml))
     if int(read_len) < 256:
-        # headline for short reads: one packed 16-bit word per record (query offset << 8 | length), half the bytes again
-        e2e_p32 = (e2e_dev_ms, e2e_wall_ms)
         h_mo[:] = 0
-        h_rec16 = h_ml32.view(np.uint16)
-        e2e_dev_ms, e2e_wall_ms, stage = e2e_leg((h_mo, h_rec16))
-        same = bool(same and np.array_equal(h_mo, mo) and np.array_equal(h_rec16[:n_mems] >> 8, mp) and np.array_equal(h_rec16[:n_mems] & 0xFF, ml))
-        e2e_api, rec_bytes = "moni_gpu_mems_packed16", 2
+        a16 = pool_a.view(np.uint16)[:total]
+        legs["mems_packed16"] = e2e_leg(ix.maxrimal_exact_matches_packed16, (h_mo, a16))
+        same["mems_packed16"] = bool(np.array_equal(h_mo, mo) and np.array_equal(a16[:n_mems] >> 8, mp) and np.array_equal(a16[:n_mems] & 0xFF, ml))
+    # ms, u64 pointers and lengths (the reference's std::vector<size_t> pair), then the 7-byte-per-base form
+    legs["ms_u64"] = e2e_leg(ix.matching_statistics, (pool_a, pool_b))
+    same["ms_u64"] = bool(np.array_equal(pool_a[:total], r_ptr) and np.array_equal(pool_b[:total], r_len))
+    gpu_ms = (pool_a[:total].copy(), pool_b[:total].copy()) if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
+    lo, hi, l16 = pool_a.view(np.uint32)[:total], pool_b.view(np.uint8)[:total], pool_b.view(np.uint16)[total:2 * total]
+    legs["ms_packed"] = e2e_leg(ix.matching_statistics_packed, (lo, hi, l16))
+    same["ms_packed"] = bool(np.array_equal(m.unpack_pointers(lo, hi), r_ptr) and np.array_equal(l16, r_len))
     clocks = sampler.summary() if sampler else None
     all_reads = sum_over_ranks(float(n_reads), dev)
     if rank != 0:
         if world > 1:
+            dist.barrier()          # rank 0 may still be running its reference sample
             dist.destroy_process_group()
         return
 
     value = all_reads * args.steps / (dev_ms / 1e3)
-    e2e_value = all_reads * args.steps / (e2e_wall_ms / 1e3)
+    value_ms = all_reads * args.steps / (dev_ms_ms / 1e3)
+    rate = lambda leg: all_reads * args.steps / (legs[leg]["wall"] / 1e3)
+    stage_names = ["h2d", "pass1", "pass2", "compact", "d2h", "total"]
+    d2h = {"mems_u64": 8 * (n_reads + 1) + 16 * n_mems, "mems_u32": 8 * (n_reads + 1) + 8 * n_mems,
+           "mems_packed32": 8 * (n_reads + 1) + 4 * n_mems, "mems_packed16": 8 * (n_reads + 1) + 2 * n_mems,
+           "ms_u64": 16 * total, "ms_packed": 7 * total}
+    api = {"mems_u64": "moni_gpu_mems", "mems_u32": "moni_gpu_mems32", "mems_packed32": "moni_gpu_mems_packed",
+           "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed"}
+    h2d = int(total + 8 * (n_reads + 1))
+
+    def leg_json(leg):
+        return {"value": rate(leg), "unit": "reads/s", "api": api[leg], "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h[leg]),
+                "ms_per_step_wall": legs[leg]["wall"] / args.steps, "ms_per_step_device": legs[leg]["dev"] / args.steps,
+                "same_bits_as_resident_run": same[leg],
+                "stage_busy_ms_per_step": dict(zip(stage_names, (legs[leg]["stage"] / args.steps).tolist()))}
+
     # roofline of the dominant kernel: B200 fetches one 128-byte DRAM line per random access, so
     #   pass 1 = 137 B per base (row line 128 + pointer store 8 + read byte 1)
     #   pass 2 = 128 B per LCE restart that touches text + 16 B per grammar node visited + 9 B per base + 8 B per MEM record
@@ -317,75 +412,78 @@ def ours_arm(args) -> None:
     survey = {"pass1": 32.0 * (5 * cnt["bases"] + 6 * cnt["jumps"]), "pass2": 32.0 * (cnt["restart_depth"] + 2 * cnt["chars"])}
     per = {"pass1": k_ms[0] / args.steps, "pass2": k_ms[1] / args.steps}
     dom = "pass1" if per["pass1"] >= per["pass2"] else "pass2"
+    oth = "pass2" if dom == "pass1" else "pass1"
+    kname = {"pass1": "k_ms_pointers", "pass2": "k_ms_lengths"}
     peak, peak_src = measured_peak_gbs()
     achieved = alg[dom] / (per[dom] / 1e3) / 1e9
+    rl = None
+    try:
+        rl = random_line_peak(m, local)
+    except Exception as e:
+        log("random-line probe failed:", e)
+    # random lines the dominant kernel must fetch: one per LF step in pass 1, one per LCE restart that touches text in pass 2
+    lines = {"pass1": float(cnt["bases"]), "pass2": float(cnt["descents"])}
+    lines_per_s = lines[dom] / (per[dom] / 1e3)
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get(dom)
+            tj = json.load(open(tp))
+            if tj.get("workload") == args.workload:
+                traffic = tj.get(dom)
         except Exception:
             traffic = None
-    cpu = None
+    cpu = par = None
     if not args.no_cpu_baseline and world == 1 and os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "mems")):
         try:
-            if _ORIG_AFFINITY:      # the reference gets every host core the process was given, not only the GPU's neighbours
-                os.sched_setaffinity(0, _ORIG_AFFINITY[0])
-            pairs = max(1000, args.ref_reads // 2)
-            sample = workloads.reads_of(args.workload, pairs=pairs)
-            cores = os.cpu_count() or 1
-            with tempfile.TemporaryDirectory() as td:
-                fq = os.path.join(td, "sample.fq")
-                write_sample_fastq(sample, fq)
-                sec = run_reference_mems(prefix, fq, cores)
-            cpu = {"value": sample.shape[0] / sec, "unit": "reads/s", "cores": cores, "kind": "reference",
-                   "sample": f"{sample.shape[0]} reads of the same workload, reference `mems -t {cores}`, its own processing-phase timer ({sec:.2f} s)"}
+            cpu, par = cpu_baseline_and_parity(args, prefix, h_seqs, n_reads, read_len, gpu_mems, gpu_ms)
         except Exception as e:  # the baseline is reported, never required
+            import traceback
+            traceback.print_exc()
             cpu = {"value": None, "unit": "reads/s", "cores": os.cpu_count(), "kind": "reference", "sample": f"failed: {e}"}
     line = {
         "metric": "mems_reads_per_s", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
         "data": "synthetic", "bases_per_s": value * read_len,
-        "config": {"workload": w["desc"], "reads_per_gpu_per_step": int(n_reads), "read_len": int(read_len), "index_n": ix.n,
-                   "index_runs": ix.r, "hbm_image_bytes": ix.device_bytes, "l2": "inputs larger than L2 (index image and read batch)",
+        "config": {"workload": w["desc"], "workload_key": args.workload, "reads_per_gpu_per_step": int(n_reads), "read_len": int(read_len),
+                   "index_n": ix.n, "index_runs": ix.r, "hbm_image_bytes": ix.device_bytes,
+                   "l2": "inputs larger than L2 (index image and read batch)",
                    "parallelism": f"reads sharded x{world}, index replicated, no collective"},
         "stage_ms_per_step": {"pass1": per["pass1"], "pass2": per["pass2"], "compact": k_ms[2] / args.steps},
-        "roofline": {"bound": "hbm", "kernel": "k_ms_pointers" if dom == "pass1" else "k_ms_lengths", "achieved": achieved,
-                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": alg[dom], "algorithmic_bytes_per_base": alg[dom] / max(cnt["bases"], 1),
-                     "survey_model_bytes": survey[dom],
-                     "other_kernel": {"kernel": "k_ms_lengths" if dom == "pass1" else "k_ms_pointers",
-                                      "achieved": alg["pass2" if dom == "pass1" else "pass1"] / (per["pass2" if dom == "pass1" else "pass1"] / 1e3) / 1e9}},
+        "roofline": {"bound": "hbm", "kernel": kname[dom], "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "traffic_source": "profiles/traffic.json (ncu capture of this workload, not this run)" if traffic else None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom],
+                     "algorithmic_bytes_per_base": alg[dom] / max(cnt["bases"], 1), "survey_model_bytes": survey[dom],
+                     "random_line_peak": rl, "random_lines_per_launch": lines[dom], "random_lines_per_s": lines_per_s,
+                     "frac_random": (lines_per_s / rl["value"]) if rl and rl.get("value") else None,
+                     "other_kernel": {"kernel": kname[oth], "achieved": alg[oth] / (per[oth] / 1e3) / 1e9,
+                                      "frac": alg[oth] / (per[oth] / 1e3) / 1e9 / peak}},
         "counters_per_step": cnt,
-        "e2e": {"value": e2e_value, "unit": "reads/s", "api": e2e_api, "h2d_bytes_per_step": int(total + 8 * (n_reads + 1)),
-                "d2h_bytes_per_step": int(8 * (n_reads + 1) + rec_bytes * n_mems), "ms_per_step_wall": e2e_wall_ms / args.steps,
-                "ms_per_step_device": e2e_dev_ms / args.steps, "same_bits_as_resident_run": same,
-                "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage / args.steps).tolist()))},
-        **({"e2e_packed32": {"value": all_reads * args.steps / (e2e_p32[1] / 1e3), "unit": "reads/s", "api": "moni_gpu_mems_packed",
-                             "d2h_bytes_per_step": int(8 * (n_reads + 1) + 4 * n_mems), "ms_per_step_wall": e2e_p32[1] / args.steps,
-                             "ms_per_step_device": e2e_p32[0] / args.steps}} if e2e_p32 else {}),
-        "e2e_u32": {"value": all_reads * args.steps / (e2e32_wall_ms / 1e3), "unit": "reads/s", "api": "moni_gpu_mems32",
-                    "d2h_bytes_per_step": int(8 * (n_reads + 1) + 8 * n_mems), "ms_per_step_wall": e2e32_wall_ms / args.steps,
-                    "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage32 / args.steps).tolist()))},
-        "e2e_u64": {"value": all_reads * args.steps / (e2e64_wall_ms / 1e3), "unit": "reads/s", "api": "moni_gpu_mems",
-                    "d2h_bytes_per_step": int(8 * (n_reads + 1) + 16 * n_mems), "ms_per_step_wall": e2e64_wall_ms / args.steps,
-                    "stage_busy_ms_per_step": dict(zip(["h2d", "pass1", "pass2", "compact", "d2h", "total"], (stage64 / args.steps).tolist()))},
+        "e2e": leg_json("mems_u64"),
+        **{"e2e_" + k: leg_json(k) for k in legs if k.startswith("mems_") and k != "mems_u64"},
+        "ms": {"value": value_ms, "unit": "reads/s", "bases_per_s": value_ms * read_len, "ms_per_step": dev_ms_ms / args.steps,
+               "stage_ms_per_step": {"pass1": kms_ms[0] / args.steps, "pass2": kms_ms[1] / args.steps, "untranspose": kms_ms[2] / args.steps},
+               "e2e": leg_json("ms_u64"), "e2e_packed": leg_json("ms_packed")},
         "mem_records_per_step": n_mems,
-        "gpu_launches": int(launches), "options": args.opt, "cpu_placement": numa_note, "host_buffers": f"pinned, NUMA node of the GPU ({m.load_library().moni_gpu_numa_node(local)})", "clocks": clocks, "cpu_baseline": cpu, "index_load_s": t_load,
+        "gpu_launches": int(launches), "gpu_launches_ms_leg": int(launches_ms), "options": args.opt, "cpu_placement": numa_note,
+        "host_buffers": f"pinned, NUMA node of the GPU ({m.load_library().moni_gpu_numa_node(local)})", "clocks": clocks,
+        "cpu_baseline": cpu, "parity_sample": par, "index_load_s": t_load,
     }
     emit(line)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
 def main():
+    import workloads
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2s", choices=["cfg2", "cfg2s", "small"])
-    ap.add_argument("--pairs", type=int, default=0, help="read pairs per GPU per step (default: the workload's)")
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(workloads.WORKLOADS))
+    ap.add_argument("--pairs", type=int, default=0, help="read pairs per GPU per step (default: the workload's bench_pairs)")
     ap.add_argument("--ref-reads", type=int, default=100_000, help="reads in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not pin each rank to the CPUs local to its GPU")

@@ -155,6 +155,17 @@ int moni_gpu_batch_fetch_mems(moni_gpu_batch* b, uint64_t* mem_offsets, uint64_t
                               uint64_t mem_capacity);
 void moni_gpu_batch_free(moni_gpu_batch* b);
 
+/* Diagnostics: the random-access roofline of CUDA device `gpu` ("measured random-sector bandwidth of the box,
+ * obtained by a gather micro-benchmark").  Dependent chains over a `table_bytes` table (next granule = hash of the words just
+ * loaded: the access pattern of an LF step over the move table, include/ms/ms_pointers.hpp:476-481 + rle_string::rank); a miss
+ * costs one 128-byte DRAM line on B200, so the result is random lines per second.  shape: 0 = one 32-byte load per access into
+ * registers (what pass 1 does), 1 = one 16-byte load into registers, 2 = one 16-byte cp.async into shared memory;
+ * chains_per_thread x (blocks_per_sm x 256 threads) chains are resident per SM; only the combinations the library was compiled
+ * with are accepted (else MONI_GPU_EINVAL).  Not on the product path. */
+int moni_gpu_probe_random_lines(int gpu, uint64_t table_bytes, int shape, int chains_per_thread, int blocks_per_sm, int iters,
+                                double* lines_per_s, int* threads_per_sm);
+void moni_gpu_probe_release(void);
+
 /* Number of kernel launches issued by this process so far (all indexes). */
 uint64_t moni_gpu_launch_count(void);
 

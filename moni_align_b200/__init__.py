@@ -43,6 +43,7 @@ EXPORTS = [
     "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
+    "moni_gpu_probe_random_lines", "moni_gpu_probe_release",
 ]
 
 
@@ -86,6 +87,8 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_batch_free.argtypes = [vp]
     L.moni_gpu_batch_free.restype = None
     L.moni_gpu_launch_count.restype = ctypes.c_uint64
+    L.moni_gpu_probe_random_lines.argtypes = [ci, ctypes.c_uint64, ci, ci, ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ci)]
+    L.moni_gpu_probe_release.restype = None
     L.moni_gpu_last_error.restype = cc
     L.moni_gpu_version.restype = cc
     _lib = L
@@ -129,6 +132,22 @@ def release_pinned() -> None:
 
 
 _PINNED: dict = {}
+
+
+def probe_random_lines(gpu: int = 0, table_bytes: int = 3 << 30, shape: int = 0, chains_per_thread: int = 1, blocks_per_sm: int = 6,
+                       iters: int = 512) -> dict:
+    """Random 128-byte lines per second of dependent chains over a table in HBM (moni_gpu_probe_random_lines): the roofline
+    denominator of SURVEY.md 8(d).  Returns {"lines_per_s", "threads_per_sm", "chains_per_sm"}."""
+    L = load_library()
+    v, t = ctypes.c_double(0), ctypes.c_int(0)
+    _check(L.moni_gpu_probe_random_lines(int(gpu), int(table_bytes), int(shape), int(chains_per_thread), int(blocks_per_sm), int(iters),
+                                         ctypes.byref(v), ctypes.byref(t)))
+    return {"lines_per_s": float(v.value), "threads_per_sm": int(t.value), "chains_per_sm": int(t.value) * int(chains_per_thread),
+            "shape": ["ldg256", "ldg128", "cp.async16"][shape], "table_bytes": int(table_bytes)}
+
+
+def probe_release() -> None:
+    load_library().moni_gpu_probe_release()
 
 
 def pack_reads(reads) -> tuple[np.ndarray, np.ndarray]:

@@ -35,10 +35,22 @@
 
 namespace {
 
+// Output files opened so far: a failed run removes them instead of leaving truncated results behind.
+std::mutex g_partial_mu;
+std::vector<std::string> g_partial;
+
 [[noreturn]] void die(const std::string& msg) {
-    // the reference's error(): "[ERROR] ..." on stderr, exit(1)   (include/common/common.hpp:108-117)
+    // the reference's error(): "[ERROR] ..." on stderr, exit(1)   (include/common/common.hpp:108-117).  Any pipeline thread may
+    // end up here while the others are inside CUDA calls or pwrite, so the process leaves through _exit: no static destructors
+    // and no CUDA teardown run beside live work.
     fprintf(stderr, "[ERROR] %s\n", msg.c_str());
-    exit(1);
+    fflush(stderr);
+    fflush(stdout);
+    {
+        std::lock_guard<std::mutex> lk(g_partial_mu);
+        for (const std::string& p : g_partial) unlink(p.c_str());
+    }
+    _exit(1);
 }
 
 void info(const char* msg) {
@@ -140,6 +152,9 @@ struct SeqReader {
             if (d < 0) break;
         }
         last = 0;
+        // kseq_read returns -2 for a quality string shorter than the sequence (thirdparty/klib/kseq.h) and the reference's read
+        // loop stops there (`while (kseq_read(seq) >= 0)`): the truncated record is not processed
+        if (q < seq.size()) { eof = true; return false; }
         return true;
     }
 };
@@ -285,6 +300,8 @@ struct Writer {
     void open_file(const std::string& path) {
         fd = ::open(path.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
         if (fd < 0) die("open() file " + path + " failed");
+        std::lock_guard<std::mutex> lk(g_partial_mu);
+        g_partial.push_back(path);
     }
     void close_file() { if (fd >= 0) ::close(fd); fd = -1; }
     template <typename F>
@@ -404,6 +421,8 @@ int main(int argc, char** argv) {
             first_cap = std::min<uint64_t>(kBatchBases + (1u << 20), std::max<uint64_t>(first_cap, (uint64_t)st.st_size * (gz ? 4 : 1)));
         }
     }
+    // a bad -p path is reported now, not after seconds of index loading (an empty path reads nothing, like the reference)
+    if (!patterns.empty() && access(patterns.c_str(), R_OK) != 0) die("cannot open patterns file " + patterns);
     const bool early = !getenv("MONI_CLI_NO_PREALLOC");
     std::thread prealloc([&]() {
         if (early) for (auto& sl : slots) sl.ensure(first_cap, mems, false);

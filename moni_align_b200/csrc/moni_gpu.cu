@@ -952,13 +952,21 @@ void* moni_gpu_host_alloc_near(int gpu, uint64_t bytes) {
     // places the buffer on the GPU's NUMA node: the PCIe copies then do not cross the socket interconnect.
     const int node = gpu_numa_node(gpu);
     bool policy_set = false;
+    int old_mode = 0;
+    unsigned long old_mask[16] = {0};
     if (node >= 0 && node < 1024) {
+        // the caller's own policy is put back afterwards (get_mempolicy with flags 0 returns the thread's policy)
+        const bool have_old = syscall(SYS_get_mempolicy, &old_mode, old_mask, (unsigned long)(sizeof(old_mask) * 8), nullptr, 0ul) == 0;
         unsigned long mask[16] = {0};
         mask[node / (8 * sizeof(unsigned long))] = 1ul << (node % (8 * sizeof(unsigned long)));
-        policy_set = syscall(SYS_set_mempolicy, 1 /* MPOL_PREFERRED */, mask, (unsigned long)(sizeof(mask) * 8)) == 0;
+        policy_set = have_old && syscall(SYS_set_mempolicy, 1 /* MPOL_PREFERRED */, mask, (unsigned long)(sizeof(mask) * 8)) == 0;
     }
     void* p = moni_gpu_host_alloc(bytes);
-    if (policy_set) syscall(SYS_set_mempolicy, 0 /* MPOL_DEFAULT */, nullptr, 0ul);
+    if (policy_set) {
+        bool any = false;
+        for (unsigned long w : old_mask) any = any || w != 0;
+        syscall(SYS_set_mempolicy, old_mode, any ? old_mask : nullptr, any ? (unsigned long)(sizeof(old_mask) * 8) : 0ul);
+    }
     return p;
 }
 
@@ -1258,6 +1266,11 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
     if (truncated) *truncated = 0;
     if (n_seeds == 0) { occ_offsets[0] = 0; return 0; }
     if (!occs && occ_capacity) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    // the reference asserts len > 0 in find_MEM_above / find_MEM_below (include/aligner/seed_finder.hpp:171,203): a zero-length seed
+    // would "match" every suffix and walk the whole suffix array; a cap beyond 2^32 positions per direction cannot be stored anyway
+    if (max_per_direction > (1ull << 32)) { g_err = "max_per_direction must be at most 2^32"; return MONI_GPU_EINVAL; }
+    for (uint64_t i = 0; i < n_seeds; ++i)
+        if (seed_len[i] == 0) { g_err = "seed " + std::to_string(i) + " has length 0 (the reference requires len > 0)"; return MONI_GPU_EINVAL; }
     if (idx->hdr.phi_n == 0) { g_err = "this index has no Phi structures: load <prefix>.thrbv.full.ms (the `moni align` index)"; return MONI_GPU_EINVAL; }
     if (!(idx->hdr.root_ref & kLeafBit)) { g_err = "occurrence enumeration needs the text in HBM (leaf_len = 0 / text_budget)"; return MONI_GPU_EINVAL; }
     return guarded([&]() -> int {

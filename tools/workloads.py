@@ -38,14 +38,19 @@ WORKLOADS = {
     # BASELINE.json configs[2]: "synthetic 32-haplotype chr21-scale pangenome, MS+MEMs on 10M 150 bp reads, 1 B200".  The index
     # (~1.28 Gbp) is too large for the gpurun snapshot, so it is built on the GPU box by tests/scale/scale_run.py.
     "cfg3": dict(base_len=40_000_000, haplotypes=32, seed=301, snp=1e-3, indel=1e-4, read_seed=302, read_len=150,
-                 pairs=5_000_000, insert=(400, 50), err=0.01,
+                 pairs=5_000_000, bench_pairs=1_000_000, insert=(400, 50), err=0.01,
                  desc="cfg3: 40 Mbp x 32 haplotypes (SNP 1e-3, indel 1e-4), 10M x 150 bp reads, 1% substitutions"),
     # BASELINE.json configs[3]/[4]: "synthetic 128-haplotype human-chromosome-scale pangenome (~6 Gbp text), 100M reads" and
     # "same index, 10 kbp ONT-like reads".  A 6 Gbp index takes the reference's CPU builder hours and ~100 GB of RAM, so the
     # haplotype count and the read counts are kept and the chromosome is scaled down: 128 x 4 Mbp = 512 Mbp.
     "cfg4s": dict(base_len=4_000_000, haplotypes=128, seed=401, snp=1e-3, indel=1e-4, read_seed=402, read_len=150,
-                  pairs=50_000_000, insert=(400, 50), err=0.01,
+                  pairs=50_000_000, bench_pairs=1_000_000, insert=(400, 50), err=0.01,
                   desc="cfg4 scaled: 4 Mbp x 128 haplotypes (SNP 1e-3, indel 1e-4), 100M x 150 bp reads, 1% substitutions"),
+    # n >= 2^32: the configs[3]/[4] regime of 40-bit positions (reference include/common/common.hpp:64-65, include/ms/ms_pointers.hpp:164-200)
+    # on a text the reference's CPU builder finishes in tens of minutes: 4096 near-identical copies of a 1.1 Mbp base, n = 4.5 G.
+    "cfg4x": dict(base_len=1_100_000, haplotypes=4096, seed=411, snp=1e-4, indel=1e-5, read_seed=412, read_len=150,
+                  pairs=1_000_000, bench_pairs=1_000_000, insert=(400, 50), err=0.01,
+                  desc="cfg4x: 1.1 Mbp x 4096 haplotypes (SNP 1e-4, indel 1e-5), n = 4.5 G > 2^32, 150 bp reads, 1% substitutions"),
     "small": dict(base_len=2_000_000, haplotypes=4, seed=5, snp=2e-3, indel=2e-4, read_seed=6, read_len=150,
                   pairs=100_000, insert=(400, 50), err=0.01, desc="functional check: 2 Mbp x 4 haplotypes"),
 }
