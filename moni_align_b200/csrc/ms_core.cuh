@@ -223,58 +223,118 @@ MONI_HD uint32_t first_diff_byte(uint64_t x) {      // x != 0
 #endif
 }
 
-// Pass 2 as a per-read state machine.  The reference's loop (src/matching_statistics.cpp:246-255) is
+// ---- restart runs: what pass 1 hands to pass 2 ---------------------------------------------------
+// The reference's length loop (src/matching_statistics.cpp:246-255) only does work at query offsets i where
+// `i == 0 || pointers[i] != pointers[i-1] + 1` (u64 arithmetic): call them restarts.  Everywhere else the pointer is the
+// previous one plus one and the length the previous one minus one (floor 0).  So pass 1 emits, per read,
+//   flags : one bit per query offset, set at the restarts (word w of the read holds offsets 32 w .. 32 w + 31)
+//   rptr  : pointers[i] of the restarts, in the order the backward scan meets them (descending i; the last entry is i = 0)
+// and pass 2 walks the restarts only.  The full arrays are rebuilt from (flags, rptr, lengths at the restarts) where an
+// interface wants them (expand_runs below; k_ms_expand on the device).
+//
+// Flag words of read r (r-th of its chunk, chunk-relative offset o) start at word (o >> 5) + r: disjoint for distinct reads
+// (floor((o + m) / 32) - floor(o / 32) + 1 >= ceil(m / 32)), at most bases / 32 + n_reads + 1 words per chunk.
+MONI_HD uint64_t flag_base(uint64_t o, uint64_t r) { return (o >> 5) + r; }
+
+struct RunSink {
+    uint32_t acc = 0;       // flag bits of the word being filled
+    uint32_t k = 0;         // restarts written so far
+};
+
+// To be called after the backward scan consumed base j (from m - 1 down to 0): `old` is the sample before the step
+// (= pointers[j + 1]), `now` the sample after it (= pointers[j]).  rptr / flags point at the read's own areas.
+MONI_HD void run_note(RunSink& rs, uint32_t j, uint32_t m, uint64_t old, uint64_t now, uint64_t* rptr, uint32_t* flags) {
+    const uint32_t i = j + 1;
+    if (i < m) {
+        if (old != now + 1) { rptr[rs.k++] = old; rs.acc |= 1u << (i & 31u); }
+        if ((i & 31u) == 0) { flags[i >> 5] = rs.acc; rs.acc = 0; }          // offsets i .. i + 31 are decided
+    }
+    if (j == 0) { rptr[rs.k++] = now; flags[0] = rs.acc | 1u; }
+}
+
+MONI_HD uint32_t ctz32(uint32_t x) {     // x != 0
+#if defined(__CUDA_ARCH__)
+    return (uint32_t)(__ffs((int)x) - 1);
+#else
+    return (uint32_t)__builtin_ctz(x);
+#endif
+}
+
+// Pass 2 as a per-read state machine over the restarts.  The reference's loop is
 //     for i: pos = ptr[i]; while (i+l < m && pos+l < N && restart(i) && read[i+l] == charAt(pos+l)) ++l; len[i] = l; l -= (l != 0)
-// with charAt = PlainSlp::charAt (thirdparty/ShapedSlp/PlainSlp.hpp:101-126), one root-to-leaf descent per
-// character.  Here one descent reaches a literal block that is compared eight bytes at a time, and the
-// work is cut into micro-steps -- ADVANCE to the next query offset, DESCEND to a literal block, COMPARE
-// one word -- so that the 32 reads of a warp each take whatever micro-step they need in the same
-// loop iteration instead of waiting for each other's inner loops.
-struct LenState {
-    enum : uint32_t { ADVANCE = 0, DESCEND = 1, COMPARE = 2 };
-    uint32_t i = 0, l = 0, prev_len = 0, n_mems = 0, mode = ADVANCE;
+// with charAt = PlainSlp::charAt (thirdparty/ShapedSlp/PlainSlp.hpp:101-126), one root-to-leaf descent per character.  Here
+// the offsets between two restarts are skipped arithmetically (l entering restart i = max(L' - (i - i'), 0) for the previous
+// restart (i', L')), one descent reaches a literal block that is compared eight bytes at a time, and the work is cut into
+// micro-steps -- NEXT restart, DESCEND to a literal block, COMPARE one word -- so that the 32 reads of a warp each take
+// whatever micro-step they need in the same loop trip.  With the text in HBM a restart is normally one trip: NEXT falls through
+// DESCEND (nothing to do) into COMPARE, whose first word already holds the mismatch.
+struct RunState {
+    enum : uint32_t { NEXT = 0, DESCEND = 1, COMPARE = 2, FINISHED = 3 };
+    uint32_t mode = NEXT;
+    uint32_t k = 0;                 // restarts finished
+    uint32_t w = 0, bits = 0;       // flag cursor: bits = flags of word w not yet visited
+    uint32_t ip = 0, Lp = 0;        // previous restart and its length
+    uint32_t i = 0, l = 0, prev_len = 0, n_mems = 0;
     uint32_t n_Ns = 0;              // seeds only: length of the run of 'N' that ends the characters compared so far
     uint32_t ref = 0;               // DESCEND: current grammar reference
-    uint64_t pos = 0, prev_ptr = 0;
-    uint64_t nxt = 0;               // pointer of query offset i, loaded one step ahead (valid once primed)
+    uint64_t pos = 0;
+    uint64_t nxt = 0;               // pointer of the next restart, loaded one micro-step ahead (valid once primed)
     bool primed = false;
     uint64_t span = 0, p = 0;       // DESCEND: expansion length of ref, offset inside it
     const uint8_t* t = nullptr;     // COMPARE: next text byte
     uint64_t rem = 0;               // COMPARE: text bytes left in the literal block
 };
 
-// One micro-step of read `seq[0..m)`.  The pointer of query offset i is ptr[i * ptr_stride] (the kernels
-// keep pointers warp-transposed: stride -32; +1 on a plain array).  When a query offset is finished,
-// writes ptr_out[i] / len[i * len_stride] (if not null) and the MEM record (packed (i << 32) | len, if mem_out != null).
+// One micro-step of read `seq[0..m)`, m >= 1.  flags = the read's flag words, rlast = &rptr[cnt - 1] (the entry of restart i = 0;
+// the k-th restart in increasing query offset is rlast[-k]), cnt = number of restarts.  When a restart is finished, writes
+// rrec_last[-k] = (i << 32) | len (if not null) and the MEM record(s) (packed (i << 32) | len, if mem_out != null): the
+// reference's rule `i == 0 || len[i] >= len[i-1]` (src/mems.cpp:257-258) also fires at offsets between restarts whose
+// predecessor has length 0 (then len stays 0): those (i, 0) records are written on the way to the next restart.
 // SEEDS: the record rule is seed_finder::find_mems' (include/aligner/seed_finder.hpp:148): l >= pl and n_Ns < l and
-// l >= min_len, where n_Ns counts the consecutive 'N' at the end of the characters matched so far (:139-143; it is
-// only touched when a character is compared and matches); ref_out[k] receives the record's text position pointers[i].
-// Call while st.i < m.  m < 2^31.
-template <typename LenT, bool SEEDS = false>
-MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, const uint64_t* ptr, int64_t ptr_stride,
-                          uint64_t* ptr_out, LenT* len, uint64_t* mem_out, LenState& st, Counters* cnt,
-                          uint64_t* ref_out = nullptr, uint32_t min_len = 0, int64_t len_stride = 1) {
+// l >= min_len, where n_Ns counts the consecutive 'N' at the end of the characters matched so far (:139-143; it is only
+// touched when a character is compared and matches), which can only hold at a restart; ref_out[k] receives pointers[i].
+// Call while st.mode != FINISHED.  m < 2^31.
+template <bool SEEDS = false>
+MONI_HD void runs_step(const ImageView& v, const uint8_t* seq, uint32_t m, const uint32_t* flags, const uint64_t* rlast, uint32_t cnt,
+                       uint64_t* rrec_last, uint64_t* mem_out, RunState& st, Counters* ctr, uint64_t* ref_out = nullptr,
+                       uint32_t min_len = 0) {
     const uint64_t N = v.hdr.text_len;
     bool done = false;
-    if (st.mode == LenState::ADVANCE) {
-        // the pointer of the NEXT offset is requested now and consumed one micro-step later, so its latency hides behind
-        // this offset's text access
-        if (!st.primed) { st.nxt = ld(ptr + (int64_t)st.i * ptr_stride); st.primed = true; }
+    if (st.mode == RunState::NEXT) {
+        if (st.k == cnt) {                                        // offsets after the last restart: lengths run down to 0, then (i, 0) records
+            if (!SEEDS && mem_out)
+                for (uint64_t q = (uint64_t)st.ip + st.Lp + 1; q < m; ++q) mem_out[st.n_mems++] = q << 32;
+            st.mode = RunState::FINISHED;
+            return;
+        }
+        if (!st.primed) { st.bits = ld(flags); st.nxt = ld(rlast); st.primed = true; }
+        while (st.bits == 0) st.bits = ld(flags + (++st.w));
+        const uint32_t i = 32u * st.w + ctz32(st.bits);
+        st.bits &= st.bits - 1u;
         st.pos = st.nxt;
-        if (st.i + 1 < m) st.nxt = ld(ptr + (int64_t)(st.i + 1) * ptr_stride);
+        if (st.k + 1 < cnt) st.nxt = ld(rlast - (int64_t)(st.k + 1));    // consumed one restart later: hides behind this restart's text access
+        if (st.k) {
+            if (!SEEDS && mem_out)
+                for (uint64_t q = (uint64_t)st.ip + st.Lp + 1; q < i; ++q) mem_out[st.n_mems++] = q << 32;
+            const uint32_t d = i - st.ip;                         // >= 1
+            st.prev_len = st.Lp > d - 1u ? st.Lp - (d - 1u) : 0u;   // len[i - 1]
+            st.l = st.Lp > d ? st.Lp - d : 0u;                    // the l the reference carries into offset i
+        } else {
+            st.prev_len = 0;
+            st.l = 0;
+        }
+        st.i = i;
+        if (ctr) ctr->restarts++;
         done = true;
-        if (st.i == 0 || st.pos != st.prev_ptr + 1) {            // otherwise the loop body never runs: l carries over
-            if (cnt) cnt->restarts++;
-            if (st.i + st.l < m && st.pos + st.l < N) {           // u64 add wraps exactly as in the reference
-                st.mode = LenState::DESCEND;
-                st.ref = v.hdr.root_ref;
-                st.span = N;
-                st.p = st.pos + st.l;
-                done = false;
-            }
+        if (i + st.l < m && st.pos + st.l < N) {                  // u64 add wraps exactly as in the reference
+            st.mode = RunState::DESCEND;
+            st.ref = v.hdr.root_ref;
+            st.span = N;
+            st.p = st.pos + st.l;
+            done = false;
         }
     }
-    if (st.mode == LenState::DESCEND) {
+    if (st.mode == RunState::DESCEND) {
         // tight loop on purpose: a level is ~10 instructions, far less than one trip through this function
         while (!(st.ref & kLeafBit)) {
 #if defined(__CUDA_ARCH__)
@@ -286,14 +346,14 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
             const uint64_t ll = v.nodes[st.ref].left_len;
 #endif
             if (st.p < ll) { st.ref = lc; st.span = ll; } else { st.p -= ll; st.span -= ll; st.ref = rc; }
-            if (cnt) cnt->restart_depth++;
+            if (ctr) ctr->restart_depth++;
         }
         st.t = v.pool + ((uint64_t)(st.ref & ~kLeafBit) << v.hdr.pool_shift) + st.p;
         st.rem = st.span - st.p;                                 // > 0, and the block lies inside the text: pos + l < N holds in it
-        st.mode = LenState::COMPARE;
-        if (cnt) cnt->descents++;
+        st.mode = RunState::COMPARE;
+        if (ctr) ctr->descents++;
     }
-    if (st.mode == LenState::COMPARE) {
+    if (st.mode == RunState::COMPARE) {
         const uint32_t e = st.i + st.l;                          // < m
         uint32_t lim = m - e;
         if (lim > 8u) lim = 8u;
@@ -318,7 +378,7 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
                 st.n_Ns = k - 1u - h;                                // 'N's after the last other character
             }
         }
-        if (cnt) cnt->chars += k + (mismatch ? 1u : 0u);
+        if (ctr) ctr->chars += k + (mismatch ? 1u : 0u);
         st.l += k;
         st.t += k;
         st.rem -= k;
@@ -326,7 +386,7 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
             done = true;
         } else if (st.rem == 0) {                                // block exhausted while still matching
             if (st.pos + st.l < N) {
-                st.mode = LenState::DESCEND;
+                st.mode = RunState::DESCEND;
                 st.ref = v.hdr.root_ref;
                 st.span = N;
                 st.p = st.pos + st.l;
@@ -337,8 +397,7 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
     }
     if (done) {
         const uint32_t i = st.i;
-        if (ptr_out) ptr_out[i] = st.pos;
-        if (len) len[(int64_t)i * len_stride] = (LenT)st.l;
+        if (rrec_last) rrec_last[-(int64_t)st.k] = ((uint64_t)i << 32) | st.l;
         const bool emit = SEEDS ? (st.l >= st.prev_len && st.n_Ns < st.l && st.l >= min_len)    // seed_finder.hpp:148 (pl starts at 0)
                                 : (i == 0 || st.l >= st.prev_len);                               // src/mems.cpp:257-258
         if (emit) {
@@ -346,23 +405,39 @@ MONI_HD void lengths_step(const ImageView& v, const uint8_t* seq, uint32_t m, co
             if (SEEDS && ref_out) ref_out[st.n_mems] = st.pos;
             ++st.n_mems;
         }
-        st.prev_len = st.l;
-        st.prev_ptr = st.pos;
-        st.l = st.l ? st.l - 1 : 0;
-        st.i = i + 1;
-        st.mode = LenState::ADVANCE;
+        st.ip = i;
+        st.Lp = st.l;
+        ++st.k;
+        st.mode = RunState::NEXT;
     }
 }
 
 // The whole length loop of one read (a single lane of the state machine).  Returns the number of MEM records.
-template <typename LenT, bool SEEDS = false>
-MONI_HD uint32_t lengths_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint64_t* ptr, int64_t ptr_stride,
-                              uint64_t* ptr_out, LenT* len, uint64_t* mem_out, Counters* cnt, uint64_t* ref_out = nullptr,
-                              uint32_t min_len = 0, int64_t len_stride = 1) {
-    LenState st;
-    while (st.i < (uint32_t)m)
-        lengths_step<LenT, SEEDS>(v, seq, (uint32_t)m, ptr, ptr_stride, ptr_out, len, mem_out, st, cnt, ref_out, min_len, len_stride);
+template <bool SEEDS = false>
+MONI_HD uint32_t runs_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint32_t* flags, const uint64_t* rptr, uint32_t cnt,
+                           uint64_t* rrec, uint64_t* mem_out, Counters* ctr, uint64_t* ref_out = nullptr, uint32_t min_len = 0) {
+    RunState st;
+    while (st.mode != RunState::FINISHED)
+        runs_step<SEEDS>(v, seq, (uint32_t)m, flags, rptr + (cnt - 1), cnt, rrec ? rrec + (cnt - 1) : nullptr, mem_out, st, ctr, ref_out, min_len);
     return st.n_mems;
+}
+
+// pointers[] / lengths[] of one read from its restarts (what the reference's vectors hold): between restarts the pointer
+// grows by one and the length shrinks by one (floor 0), in u64 arithmetic.  Host-side helper of the run interfaces.
+inline void expand_runs(uint64_t m, const uint32_t* flags, const uint64_t* rptr, const uint64_t* rrec, uint32_t cnt, uint64_t* ptr_out,
+                        uint64_t* len_out) {
+    uint64_t p0 = 0, l0 = 0, i0 = 0;
+    uint32_t k = 0;
+    for (uint64_t i = 0; i < m; ++i) {
+        if ((flags[i >> 5] >> (i & 31)) & 1u) {
+            p0 = rptr[cnt - 1 - k];
+            l0 = rrec[cnt - 1 - k] & 0xFFFFFFFFull;
+            i0 = i;
+            ++k;
+        }
+        ptr_out[i] = p0 + (i - i0);
+        len_out[i] = l0 > i - i0 ? l0 - (i - i0) : 0;
+    }
 }
 
 // ---- occurrence enumeration (`moni align`, include/aligner/seed_finder.hpp:169-251, 346-368) ---------------------

@@ -76,32 +76,42 @@ int main(int argc, char** argv) {
 
         const uint64_t total = off[nr];
         std::vector<uint64_t> ptr(total + 1), len64(total + 1), mo(nr + 1), mems;
-        std::vector<uint32_t> len(total + 1);
         Counters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         for (uint64_t r = 0; r < nr; ++r) {
             const uint64_t o = off[r], m = off[r + 1] - o;
             ScanState s;
             scan_init(v, s);
+            // pass 1 the way the kernel runs it: pointers are kept only at the restarts (flags + rptr), ms_core.cuh run_note
+            std::vector<uint32_t> flags(m / 32 + 2, 0);
+            std::vector<uint64_t> rptr(m + 1), rrec(m + 1), direct(m + 1);
+            RunSink rs;
             for (uint64_t j = m; j-- > 0;) {
+                const uint64_t old = s.sample;
                 scan_step(v, img.sym.tcode, seqs[o + j], s, &cnt);
-                ptr[o + j] = s.sample;
+                direct[j] = s.sample;
+                run_note(rs, (uint32_t)j, (uint32_t)m, old, s.sample, rptr.data(), flags.data());
             }
             cnt.bases += m;
             std::vector<uint64_t> rec(m + 1);
-            const uint32_t k = lengths_read(v, seqs.data() + o, m, ptr.data() + o, 1, (uint64_t*)nullptr, len.data() + o, rec.data(), &cnt);
+            uint32_t k = 0;
+            if (m) {
+                k = runs_read<false>(v, seqs.data() + o, m, flags.data(), rptr.data(), rs.k, rrec.data(), rec.data(), &cnt);
+                expand_runs(m, flags.data(), rptr.data(), rrec.data(), rs.k, ptr.data() + o, len64.data() + o);
+                for (uint64_t j = 0; j < m; ++j)
+                    if (ptr[o + j] != direct[j]) throw std::runtime_error("expanded pointers differ from the scan's");
+            }
             mo[r] = mems.size();
             mems.insert(mems.end(), rec.begin(), rec.begin() + k);
             if (want_seeds) {
                 std::vector<uint64_t> ref(m + 1);
-                const uint32_t ks = lengths_read<uint32_t, true>(v, seqs.data() + o, m, ptr.data() + o, 1, (uint64_t*)nullptr, (uint32_t*)nullptr,
-                                                                 rec.data(), nullptr, ref.data(), seed_min_len);
+                const uint32_t ks = m ? runs_read<true>(v, seqs.data() + o, m, flags.data(), rptr.data(), rs.k, nullptr, rec.data(), nullptr, ref.data(),
+                                                        seed_min_len) : 0;
                 so.push_back(s_ref.size());
                 for (uint32_t t = 0; t < ks; ++t) { s_ref.push_back(ref[t]); s_len.push_back(rec[t] & 0xFFFFFFFFu); s_qpos.push_back(rec[t] >> 32); }
             }
         }
         if (want_seeds) so.push_back(s_ref.size());
         mo[nr] = mems.size();
-        for (uint64_t i = 0; i < total; ++i) len64[i] = len[i];
         std::vector<uint64_t> mp(mems.size() + 1), ml(mems.size() + 1);
         for (size_t i = 0; i < mems.size(); ++i) { mp[i] = mems[i] >> 32; ml[i] = mems[i] & 0xFFFFFFFFu; }
         f = fopen(argv[3], "wb");
