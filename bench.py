@@ -341,12 +341,12 @@ def ours_arm(args) -> None:
     # ---- end-to-end legs through the C ABI with pinned host buffers
     def e2e_leg(call, out):
         for _ in range(args.warmup):
-            call(h_seqs, h_offs, out=out)
+            call(h_seqs, h_offs, out)
         barrier()
         dev_sum, stage = 0.0, np.zeros(6)
         t_wall = time.perf_counter()
         for _ in range(args.steps):
-            call(h_seqs, h_offs, out=out)
+            call(h_seqs, h_offs, out)
             tt = ix.timing()
             dev_sum += tt["total_ms"]
             stage += np.array([tt[k] for k in ("h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms")])
@@ -378,6 +378,20 @@ def ours_arm(args) -> None:
     lo, hi, l16 = pool_a.view(np.uint32)[:total], pool_b.view(np.uint8)[:total], pool_b.view(np.uint16)[total:2 * total]
     legs["ms_packed"] = e2e_leg(ix.matching_statistics_packed, (lo, hi, l16))
     same["ms_packed"] = bool(np.array_equal(m.unpack_pointers(lo, hi), r_ptr) and np.array_equal(l16, r_len))
+    # ms as restart runs (moni_gpu_ms_runs): only the offsets where the reference's loop does work leave the device
+    q32, n32 = pool_a.view(np.uint32)[:total], pool_a.view(np.uint32)[total:2 * total]
+    legs["ms_runs"] = e2e_leg(ix.matching_statistics_runs, (h_mo, q32, n32, pool_b))
+    n_runs = int(h_mo[n_reads])
+    xp, xl = m.expand_runs(h_offs, h_mo, q32[:n_runs], n32[:n_runs], pool_b[:n_runs])
+    same["ms_runs"] = bool(np.array_equal(xp, r_ptr) and np.array_equal(xl, r_len))
+    del xp, xl
+    rec32, lo32, hi8 = pool_a.view(np.uint32)[:total], pool_a.view(np.uint32)[total:2 * total], pool_b.view(np.uint8)[:total]
+    h_mo[:] = 0
+    legs["ms_runs_packed"] = e2e_leg(lambda sq, of, out: ix.matching_statistics_runs(sq, of, out=out, packed=True), (h_mo, rec32, lo32, hi8))
+    uq, ul, up = m.unpack_runs(rec32[:n_runs], lo32[:n_runs], hi8[:n_runs])
+    xp, xl = m.expand_runs(h_offs, h_mo, uq, ul, up)
+    same["ms_runs_packed"] = bool(int(h_mo[n_reads]) == n_runs and np.array_equal(xp, r_ptr) and np.array_equal(xl, r_len))
+    del xp, xl, uq, ul, up
     clocks = sampler.summary() if sampler else None
     all_reads = sum_over_ranks(float(n_reads), dev)
     if rank != 0:
@@ -392,9 +406,11 @@ def ours_arm(args) -> None:
     stage_names = ["h2d", "pass1", "pass2", "compact", "d2h", "total"]
     d2h = {"mems_u64": 8 * (n_reads + 1) + 16 * n_mems, "mems_u32": 8 * (n_reads + 1) + 8 * n_mems,
            "mems_packed32": 8 * (n_reads + 1) + 4 * n_mems, "mems_packed16": 8 * (n_reads + 1) + 2 * n_mems,
-           "ms_u64": 16 * total, "ms_packed": 7 * total}
+           "ms_u64": 16 * total, "ms_packed": 7 * total, "ms_runs": 8 * (n_reads + 1) + 16 * n_runs,
+           "ms_runs_packed": 8 * (n_reads + 1) + 9 * n_runs}
     api = {"mems_u64": "moni_gpu_mems", "mems_u32": "moni_gpu_mems32", "mems_packed32": "moni_gpu_mems_packed",
-           "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed"}
+           "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed",
+           "ms_runs": "moni_gpu_ms_runs", "ms_runs_packed": "moni_gpu_ms_runs_packed"}
     h2d = int(total + 8 * (n_reads + 1))
 
     def leg_json(leg):
@@ -462,8 +478,9 @@ def ours_arm(args) -> None:
         "e2e": leg_json("mems_u64"),
         **{"e2e_" + k: leg_json(k) for k in legs if k.startswith("mems_") and k != "mems_u64"},
         "ms": {"value": value_ms, "unit": "reads/s", "bases_per_s": value_ms * read_len, "ms_per_step": dev_ms_ms / args.steps,
-               "stage_ms_per_step": {"pass1": kms_ms[0] / args.steps, "pass2": kms_ms[1] / args.steps, "untranspose": kms_ms[2] / args.steps},
-               "e2e": leg_json("ms_u64"), "e2e_packed": leg_json("ms_packed")},
+               "stage_ms_per_step": {"pass1": kms_ms[0] / args.steps, "pass2": kms_ms[1] / args.steps, "expand": kms_ms[2] / args.steps},
+               "e2e": leg_json("ms_u64"), "e2e_packed": leg_json("ms_packed"), "e2e_runs": leg_json("ms_runs"),
+               "e2e_runs_packed": leg_json("ms_runs_packed"), "runs_per_step": n_runs},
         "mem_records_per_step": n_mems,
         "gpu_launches": int(launches), "gpu_launches_ms_leg": int(launches_ms), "options": args.opt, "cpu_placement": numa_note,
         "host_buffers": f"pinned, NUMA node of the GPU ({m.load_library().moni_gpu_numa_node(local)})", "clocks": clocks,

@@ -111,6 +111,23 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
 int moni_gpu_ms_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads,
                        uint32_t* ptr_lo, uint8_t* ptr_hi, uint16_t* lengths);
 
+/* moni_gpu_ms as restart runs: what ms_c::matching_statistics computes (src/matching_statistics.cpp:242-278) without the
+ * redundancy of its two vectors.  The reference's length loop (:246-255) only does work at query offsets i with
+ * `i == 0 || pointers[i] != pointers[i-1] + 1` (restarts); at every other offset pointers[i] = pointers[i-1] + 1 and
+ * lengths[i] = lengths[i-1] - 1 (floor 0).  For read r the runs k in [run_offsets[r], run_offsets[r+1]) are its restarts in
+ * increasing query offset: run_qpos[k] = i, run_ptr[k] = pointers[i], run_len[k] = lengths[i]; the first run of a non-empty
+ * read is at i = 0.  moni_gpu_ms_runs_expand rebuilds the two vectors on the host (format conversion, no device work), so
+ * expand(runs) == moni_gpu_ms bit for bit, wrapped pointers included.  About 1 + #mismatches runs per read instead of two
+ * u64 per base leave the device.  Capacity rule as for moni_gpu_mems (offsets[n_reads] always suffices). */
+int moni_gpu_ms_runs(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* run_offsets,
+                     uint32_t* run_qpos, uint32_t* run_len, uint64_t* run_ptr, uint64_t run_capacity);
+/* Same runs in 9 bytes each: run_rec = (query offset << 16) | length (reads shorter than 65536 bases, else MONI_GPU_EINVAL) and the
+ * pointer's low 40 bits as ptr_lo + ptr_hi (decoded like moni_gpu_ms_packed's; needs n <= 2^40 - 2^31). */
+int moni_gpu_ms_runs_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* run_offsets,
+                            uint32_t* run_rec, uint32_t* ptr_lo, uint8_t* ptr_hi, uint64_t run_capacity);
+int moni_gpu_ms_runs_expand(const uint64_t* offsets, uint64_t n_reads, const uint64_t* run_offsets, const uint32_t* run_qpos,
+                            const uint32_t* run_len, const uint64_t* run_ptr, uint64_t* pointers, uint64_t* lengths);
+
 /* Event counters accumulated over all calls since the last reset, when counting is enabled
  * (moni_gpu_set_option("count", "1"); off by default, it costs a few percent):
  * c[0]=bases, c[1]=threshold jumps (ms_pointers.hpp:482-505 taken), c[2]=LCE restarts,

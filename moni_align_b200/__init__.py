@@ -43,7 +43,7 @@ EXPORTS = [
     "moni_gpu_counters", "moni_gpu_timing", "moni_gpu_set_option", "moni_gpu_host_alloc", "moni_gpu_host_free",
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
-    "moni_gpu_probe_random_lines", "moni_gpu_probe_release",
+    "moni_gpu_probe_random_lines", "moni_gpu_probe_release", "moni_gpu_ms_runs", "moni_gpu_ms_runs_packed", "moni_gpu_ms_runs_expand",
 ]
 
 
@@ -80,6 +80,9 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_ms_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, vp, vp, vp]
     L.moni_gpu_host_free.argtypes = [vp]
     L.moni_gpu_host_free.restype = None
+    L.moni_gpu_ms_runs.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, _u64p, ctypes.c_uint64]
+    L.moni_gpu_ms_runs_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, vp, ctypes.c_uint64]
+    L.moni_gpu_ms_runs_expand.argtypes = [_u64p, ctypes.c_uint64, _u64p, vp, vp, _u64p, _u64p, _u64p]
     L.moni_gpu_batch_create.argtypes = [vp, ci, vp, _u64p, ctypes.c_uint64, ctypes.POINTER(vp)]
     L.moni_gpu_batch_run.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_float)]
     L.moni_gpu_batch_fetch_ms.argtypes = [vp, _u64p, _u64p]
@@ -226,6 +229,28 @@ class MoniIndex:
             lo, hi, ln = out
         _check(self._L.moni_gpu_ms_packed(self._h, _ptr(seqs), _u64(offsets), nr, _ptr(lo), _ptr(hi), _ptr(ln)))
         return lo[:total], hi[:total], ln[:total]
+
+    def matching_statistics_runs(self, seqs: np.ndarray, offsets: np.ndarray, out=None, packed: bool = False):
+        """ms_c::matching_statistics as restart runs (moni_gpu_ms_runs): (run_offsets uint64[n+1], run_qpos uint32[k], run_len uint32[k],
+        run_ptr uint64[k]); packed=True (moni_gpu_ms_runs_packed): (run_offsets, run_rec uint32[k], ptr_lo uint32[k], ptr_hi uint8[k]).
+        expand_runs() rebuilds the reference's two vectors."""
+        seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        total = int(offsets[-1])
+        nr = offsets.shape[0] - 1
+        if out is None:
+            ro = np.empty(nr + 1, dtype=np.uint64)
+            a = np.empty(max(total, 1), dtype=np.uint32)
+            b = np.empty(max(total, 1), dtype=np.uint32)
+            c = np.empty(max(total, 1), dtype=np.uint8 if packed else np.uint64)
+        else:
+            ro, a, b, c = out
+        if packed:
+            _check(self._L.moni_gpu_ms_runs_packed(self._h, _ptr(seqs), _u64(offsets), nr, _u64(ro), _ptr(a), _ptr(b), _ptr(c), a.shape[0]))
+        else:
+            _check(self._L.moni_gpu_ms_runs(self._h, _ptr(seqs), _u64(offsets), nr, _u64(ro), _ptr(a), _ptr(b), _u64(c), a.shape[0]))
+        k = int(ro[nr])
+        return ro, a[:k], b[:k], c[:k]
 
     def maxrimal_exact_matches(self, seqs: np.ndarray, offsets: np.ndarray, out=None, dtype=np.uint64):
         """(mem_offsets uint64[n+1], mem_pos, mem_len) -- mems_c::maxrimal_exact_matches for every read;
@@ -407,6 +432,28 @@ def format_seeds(names: Iterable[bytes], seed_offsets, seed_ref, seed_len, seed_
         a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
         out.append(b">" + nm + b"\n" + b"".join(b"(%d,%d,%d) " % (int(seed_ref[t]), int(seed_len[t]), int(seed_qpos[t])) for t in range(a, b)) + b"\n")
     return b"".join(out)
+
+
+def expand_runs(offsets: np.ndarray, run_offsets: np.ndarray, run_qpos: np.ndarray, run_len: np.ndarray, run_ptr: np.ndarray, out=None):
+    """(pointers, lengths) uint64[offsets[-1]] from restart runs (moni_gpu_ms_runs_expand): the reference's two vectors."""
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    run_offsets = np.ascontiguousarray(run_offsets, dtype=np.uint64)
+    run_qpos = np.ascontiguousarray(run_qpos, dtype=np.uint32)
+    run_len = np.ascontiguousarray(run_len, dtype=np.uint32)
+    run_ptr = np.ascontiguousarray(run_ptr, dtype=np.uint64)
+    total = int(offsets[-1])
+    if out is None:
+        ptr, ln = np.empty(max(total, 1), dtype=np.uint64), np.empty(max(total, 1), dtype=np.uint64)
+    else:
+        ptr, ln = out
+    _check(load_library().moni_gpu_ms_runs_expand(_u64(offsets), offsets.shape[0] - 1, _u64(run_offsets), _ptr(run_qpos), _ptr(run_len),
+                                                  _u64(run_ptr), _u64(ptr), _u64(ln)))
+    return ptr[:total], ln[:total]
+
+
+def unpack_runs(run_rec: np.ndarray, ptr_lo: np.ndarray, ptr_hi: np.ndarray):
+    """(run_qpos, run_len, run_ptr) from the packed columns of moni_gpu_ms_runs_packed."""
+    return (run_rec >> np.uint32(16)).astype(np.uint32), (run_rec & np.uint32(0xFFFF)).astype(np.uint32), unpack_pointers(ptr_lo, ptr_hi)
 
 
 def unpack_pointers(ptr_lo: np.ndarray, ptr_hi: np.ndarray) -> np.ndarray:

@@ -58,23 +58,21 @@ __device__ __forceinline__ void flush_counters(const Counters& c, Counters* g) {
     atomicAdd(&g->descents, c.descents);
 }
 
-// How the reads of a chunk map to threads and where a warp keeps its pointers.
-//   slot  = global thread index; read = perm ? perm[slot] : slot   (perm sorts ragged chunks by length,
-//           longest first, so the 32 reads of a warp retire together and padding stays small)
-//   pointers of warp w: ptr_t[wbase(w) + step * 32 + lane], step = number of symbols consumed before
-//           (query offset i = m - 1 - step); wbase(w) = w * 32 * uniform_len, or wbase[w] for ragged chunks.
+// How the reads of a chunk map to threads and where a read keeps what the two passes exchange.
+//   slot  = global thread index; read = perm ? perm[slot] : slot   (perm sorts ragged chunks by length, longest first, so
+//           the 32 reads of a warp retire together)
+//   read r at chunk-relative offset o: flag words at flags[flag_base(o, r)], restart pointers (pass 1) and restart records
+//           (pass 2) at rptr / rrec[run_base(o, r)], filled from index 0 in the order of the backward scan.
 struct ChunkMap {
     const uint64_t* offs;      // n_reads + 1 absolute offsets into the caller's seqs
     const uint32_t* perm;      // or null
-    const uint64_t* wbase;     // or null (uniform_len != 0)
     uint64_t base;             // offs[0]: seqs on the device start here
     uint32_t n_reads;
-    uint32_t uniform_len;
 };
 
-__device__ __forceinline__ uint64_t warp_base(const ChunkMap& cm, uint32_t w) {
-    return cm.wbase ? __ldg(cm.wbase + w) : (uint64_t)w * 32u * cm.uniform_len;
-}
+// First restart entry of read r: a multiple of 4 entries (one 32-byte sector of pointers), at least m entries before the
+// next read's ((o + m + 4 (r + 1)) & ~3) - ((o + 4 r) & ~3) >= m + 1.  At most bases + 4 n_reads + 4 entries per chunk.
+__host__ __device__ __forceinline__ uint64_t run_base(uint64_t o, uint64_t r) { return (o + 4 * r) & ~3ull; }
 
 __device__ __forceinline__ uint32_t warp_max(uint32_t x) {
 #pragma unroll
@@ -90,43 +88,47 @@ __global__ void k_read_len(const uint64_t* __restrict__ offs, uint32_t n, uint32
     vals[r] = r;
 }
 
-// ext[w] = 32 * (longest read of warp w); ext[n_warps] = 0.  An exclusive scan turns it into wbase.
-__global__ void k_warp_extent(const uint64_t* __restrict__ offs, const uint32_t* __restrict__ perm, uint32_t n, uint32_t n_warps,
-                              uint64_t* __restrict__ ext) {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, w = slot >> 5;
-    if (w > n_warps) return;
-    uint32_t m = 0;
-    if (slot < n) {
-        const uint32_t r = perm ? perm[slot] : slot;
-        m = (uint32_t)(offs[r + 1] - offs[r]);
-    }
-    m = warp_max(m);
-    if ((threadIdx.x & 31) == 0) ext[w] = w < n_warps ? (uint64_t)m * 32u : 0;
-}
+// ---- pass 1: MS pointers, kept at the restarts ------------------------------------------------------
+// One read per thread.  Output per read (ms_core.cuh "restart runs"): the restart flags, the pointers at the restarts in scan
+// order, and their number.  A lane's pointers are staged four at a time in shared memory and leave as one aligned 32-byte
+// sector, so DRAM sees whole-sector writes although every lane appends to its own list at its own pace.
+constexpr int kStage = 4;
 
-// ---- pass 1: MS pointers -------------------------------------------------------------------------
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
-                                                        uint64_t* __restrict__ ptr_t, Counters* g) {
+                                                        uint64_t* __restrict__ rptr, uint32_t* __restrict__ flags,
+                                                        uint32_t* __restrict__ rcnt, Counters* g) {
     __shared__ uint8_t tcode[256];
     __shared__ __align__(16) uint8_t tiles[kBlock / 32][32 * kTileStride];
+    __shared__ uint64_t stage[kStage][kBlock];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) tcode[i] = v.sym->tcode[i];
     __syncthreads();
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
     if ((w << 5) >= cm.n_reads) return;                       // warp-uniform
     uint8_t* tile = tiles[threadIdx.x >> 5];
-    uint32_t o = 0, m = 0;                                    // chunk-relative offset (< 2^32) and length
+    uint32_t o = 0, m = 0, r = 0;                             // chunk-relative offset (< 2^32), length, read
     if (slot < cm.n_reads) {
-        const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
+        r = cm.perm ? __ldg(cm.perm + slot) : slot;
         const uint64_t a = __ldg(cm.offs + r);
         o = (uint32_t)(a - cm.base);
         m = (uint32_t)(__ldg(cm.offs + r + 1) - a);
     }
     const uint32_t mw = warp_max(m);
-    uint64_t* out = ptr_t + warp_base(cm, w) + lane;
+    uint64_t* const out = rptr + run_base(o, r);
+    uint32_t* const fl = flags + flag_base(o, r);
     ScanState s;
     scan_init(v, s);
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t acc = 0, k = 0;
+    auto push = [&](uint64_t x) {
+        stage[k & (kStage - 1)][threadIdx.x] = x;
+        ++k;
+        if ((k & (kStage - 1)) == 0) {
+            ulonglong2* dst = reinterpret_cast<ulonglong2*>(out + (k - kStage));
+            dst[0] = make_ulonglong2(stage[0][threadIdx.x], stage[1][threadIdx.x]);
+            dst[1] = make_ulonglong2(stage[2][threadIdx.x], stage[3][threadIdx.x]);
+        }
+    };
     for (uint32_t t0 = 0; t0 < mw; t0 += kTile) {
         __syncwarp();
         // refill: lane L fetches the byte of step t0 + L for each of the warp's reads in turn (one
@@ -142,94 +144,118 @@ __global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers(Image
         for (uint32_t t = 0; t < lim; ++t) {
             const uint32_t step = t0 + t;
             if (step < m) {
+                const uint64_t old = s.sample;                // pointers[j + 1]
                 scan_step(v, tcode, tile[lane * kTileStride + t], s, COUNT ? &c : nullptr);
-                out[(uint64_t)step * 32u] = s.sample;
+                // ms_core.cuh run_note, with the pointer list staged
+                const uint32_t i = m - step;                  // j + 1
+                if (i < m) {
+                    if (old != s.sample + 1) { push(old); acc |= 1u << (i & 31u); }
+                    if ((i & 31u) == 0) { fl[i >> 5] = acc; acc = 0; }
+                }
+                if (i == 1) { push(s.sample); fl[0] = acc | 1u; }
             }
         }
     }
+    for (uint32_t q = k & ~(uint32_t)(kStage - 1); q < k; ++q) out[q] = stage[q & (kStage - 1)][threadIdx.x];
+    if (slot < cm.n_reads) rcnt[r] = k;
     if (COUNT) { c.bases = m; flush_counters(c, g); }
 }
 
-// ---- pass 2: MS lengths / MEM records / seeds --------------------------------------------------------
-// MODE 0 (ms): the length of query offset i goes to len_t[] next to its pointer (same warp-transposed place, u32), so the
-// 32 lanes of a warp write into the same lines; k_ms_untranspose then produces the caller's layout with coalesced
-// accesses on both sides.  MODE 1 (mems): the read's MEM records, packed (i << 32) | len, go to rec[] at the read's own
-// offset (at most one per base) and counts[read] receives their number.  MODE 2 (seeds): same with
-// seed_finder::find_mems' rule (minimum length, N filter) and rec_ref[] = pointers[i].
+// ---- pass 2: MS lengths at the restarts / MEM records / seeds ----------------------------------------
+// MODE 0 (ms, runs): rrec[] receives (i << 32) | len of every restart, next to its pointer.  MODE 1 (mems): the read's MEM
+// records, packed (i << 32) | len, go to rec[] at the read's own offset (at most one per base) and counts[read] receives their
+// number.  MODE 2 (seeds): same with seed_finder::find_mems' rule (minimum length, N filter) and rec_ref[] = pointers[i].
 template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
-                                                       const uint64_t* __restrict__ ptr_t, uint32_t* __restrict__ len_t,
+                                                       const uint64_t* __restrict__ rptr, const uint32_t* __restrict__ flags,
+                                                       const uint32_t* __restrict__ rcnt, uint64_t* __restrict__ rrec,
                                                        uint64_t* __restrict__ rec, uint32_t* __restrict__ counts, Counters* g,
                                                        uint64_t* __restrict__ rec_ref, uint32_t min_len) {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= cm.n_reads) return;
     const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
     const uint64_t a = __ldg(cm.offs + r);
     const uint64_t o = a - cm.base, m = __ldg(cm.offs + r + 1) - a;
     if (m == 0) { if (MODE) counts[r] = 0; return; }
-    const uint64_t at = warp_base(cm, w) + lane + (m - 1) * 32u;              // query offset 0 = last step
+    const uint64_t rb = run_base(o, r);
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
-    const uint32_t k = lengths_read<uint32_t, MODE == 2>(v, seqs + o, m, ptr_t + at, -32, nullptr, MODE ? nullptr : len_t + at,
-                                                         MODE ? rec + o : nullptr, COUNT ? &c : nullptr,
-                                                         MODE == 2 ? rec_ref + o : nullptr, min_len, -32);
+    const uint32_t k = runs_read<MODE == 2>(v, seqs + o, m, flags + flag_base(o, r), rptr + rb, __ldg(rcnt + r), MODE ? nullptr : rrec + rb,
+                                            MODE ? rec + o : nullptr, COUNT ? &c : nullptr, MODE == 2 ? rec_ref + o : nullptr, min_len);
     if (MODE) counts[r] = k;
     if (COUNT) flush_counters(c, g);
 }
 
-// ms: warp-transposed (pointer, length) -> the caller's layout (u64 each, laid out like seqs).  One warp per 32 reads,
-// 32 steps at a time through shared memory: 256-byte loads along the lanes, 256-byte stores along each read.
-constexpr int kUtBlock = 64;
+// ms: restart runs -> the caller's layout (pointers[] / lengths[] laid out like seqs).  One warp per read, 32 query offsets per
+// trip: every lane finds the restart at or before its offset in the flag word (or the carry from earlier words), reads that
+// restart's pointer and length, and adds / subtracts the distance -- what the reference's loop does one offset at a time
+// (src/matching_statistics.cpp:246-255).  Stores are 256 bytes along the read.
 // PACKED: 7 bytes per base instead of 16 -- the low 40 bits of the pointer as u32 + u8 (a pointer is a text position < n,
 // or 2^64 - k with k < 2^31 after the reference's `sample--` wrapped: both survive `& (2^40 - 1)` when n <= 2^40 - 2^31)
 // and the length as u16 (reads shorter than 65536 bases).
 template <bool PACKED>
-__global__ void __launch_bounds__(kUtBlock) k_ms_untranspose(ChunkMap cm, const uint64_t* __restrict__ ptr_t,
-                                                             const uint32_t* __restrict__ len_t, uint64_t* __restrict__ ptr_out,
-                                                             uint64_t* __restrict__ len_out, uint32_t* __restrict__ lo_out,
-                                                             uint8_t* __restrict__ hi_out, uint16_t* __restrict__ len16_out) {
-    __shared__ uint64_t tp[kUtBlock / 32][32 * 33];
-    __shared__ uint32_t tl[kUtBlock / 32][32 * 33];
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31, w = slot >> 5;
-    if ((w << 5) >= cm.n_reads) return;                       // warp-uniform
-    uint64_t* P = tp[threadIdx.x >> 5];
-    uint32_t* Q = tl[threadIdx.x >> 5];
-    uint64_t o = 0;
-    uint32_t m = 0;
-    if (slot < cm.n_reads) {
-        const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
-        const uint64_t a = __ldg(cm.offs + r);
-        o = a - cm.base;
-        m = (uint32_t)(__ldg(cm.offs + r + 1) - a);
-    }
-    const uint32_t mw = warp_max(m);
-    const uint64_t base = warp_base(cm, w) + lane;
-    for (uint32_t t0 = 0; t0 < mw; t0 += 32) {
-        const uint32_t lim = min(32u, mw - t0);
-#pragma unroll 8
-        for (uint32_t t = 0; t < lim; ++t) {                  // entries of lanes whose read is shorter are never stored below
-            P[t * 33 + lane] = __ldg(ptr_t + base + (uint64_t)(t0 + t) * 32u);
-            Q[t * 33 + lane] = __ldg(len_t + base + (uint64_t)(t0 + t) * 32u);
-        }
-        __syncwarp();
-#pragma unroll 4
-        for (int rr = 0; rr < 32; ++rr) {
-            const uint64_t o_r = __shfl_sync(0xFFFFFFFFu, o, rr);
-            const uint32_t m_r = __shfl_sync(0xFFFFFFFFu, m, rr);
-            const uint32_t step = t0 + lane;
-            if (step < m_r) {
-                const uint64_t at = o_r + (m_r - 1 - step);
-                const uint64_t pv = P[lane * 33 + rr];
-                if (PACKED) {
-                    lo_out[at] = (uint32_t)pv;
-                    hi_out[at] = (uint8_t)(pv >> 32);
-                    len16_out[at] = (uint16_t)Q[lane * 33 + rr];
-                } else {
-                    ptr_out[at] = pv;
-                    len_out[at] = Q[lane * 33 + rr];
-                }
+__global__ void __launch_bounds__(kBlock) k_ms_expand(ChunkMap cm, const uint64_t* __restrict__ rptr, const uint64_t* __restrict__ rrec,
+                                                      const uint32_t* __restrict__ flags, const uint32_t* __restrict__ rcnt,
+                                                      uint64_t* __restrict__ ptr_out, uint64_t* __restrict__ len_out,
+                                                      uint32_t* __restrict__ lo_out, uint8_t* __restrict__ hi_out,
+                                                      uint16_t* __restrict__ len16_out) {
+    const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (r >= cm.n_reads) return;
+    const uint64_t a = __ldg(cm.offs + r);
+    const uint64_t o = a - cm.base, m = __ldg(cm.offs + r + 1) - a;
+    if (m == 0) return;
+    const uint32_t cnt = __ldg(rcnt + r);
+    const uint64_t* const rp = rptr + run_base(o, r) + (cnt - 1);     // restart k (in increasing query offset) is rp[-k]
+    const uint64_t* const rr = rrec + run_base(o, r) + (cnt - 1);
+    const uint32_t* const fl = flags + flag_base(o, r);
+    uint32_t seen = 0;                                                // restarts in earlier words
+    uint64_t carry = 0;                                               // query offset of the last of them
+    for (uint64_t i0 = 0; i0 < m; i0 += 32) {
+        const uint32_t word = __ldg(fl + (i0 >> 5));
+        const uint32_t upto = word & (0xFFFFFFFFu >> (31u - lane));    // restarts at offsets i0 .. i0 + lane
+        const uint64_t at = upto ? i0 + (31u - (uint32_t)__clz((int)upto)) : carry;
+        const uint32_t kk = seen + (uint32_t)__popc(upto) - 1u;         // offset 0 is a restart, so kk >= 0 from the first word on
+        const uint64_t i = i0 + lane;
+        if (i < m) {
+            const uint64_t d = i - at;
+            const uint64_t pv = __ldg(rp - (int64_t)kk) + d;
+            const uint64_t l0 = __ldg(rr - (int64_t)kk) & 0xFFFFFFFFull;
+            const uint64_t lv = l0 > d ? l0 - d : 0;
+            if (PACKED) {
+                lo_out[o + i] = (uint32_t)pv;
+                hi_out[o + i] = (uint8_t)(pv >> 32);
+                len16_out[o + i] = (uint16_t)lv;
+            } else {
+                ptr_out[o + i] = pv;
+                len_out[o + i] = lv;
             }
         }
-        __syncwarp();
+        if (word) { carry = i0 + (31u - (uint32_t)__clz((int)word)); seen += (uint32_t)__popc(word); }
+    }
+}
+
+// runs: the restarts of every read, compacted in increasing query offset.  WIDE: (query offset u32, length u32, pointer u64);
+// else one word (query offset << 16) | length for reads shorter than 65536 bases and the pointer's low 40 bits as u32 + u8.
+template <bool WIDE>
+__global__ void __launch_bounds__(kBlock) k_runs_gather(const uint64_t* __restrict__ rptr, const uint64_t* __restrict__ rrec,
+                                                        const uint64_t* __restrict__ offs, uint64_t base, uint32_t n_reads,
+                                                        const uint64_t* __restrict__ moff, uint32_t* __restrict__ c0,
+                                                        uint32_t* __restrict__ c1, uint64_t* __restrict__ c2_wide, uint8_t* __restrict__ c2_hi) {
+    const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (r >= n_reads) return;
+    const uint64_t o = offs[r] - base, a = moff[r], cnt = moff[r + 1] - a;
+    if (cnt == 0) return;
+    const uint64_t last = run_base(o, r) + (cnt - 1);
+    for (uint64_t k = lane; k < cnt; k += 32) {
+        const uint64_t x = rrec[last - k], pv = rptr[last - k];
+        if (WIDE) {
+            c0[a + k] = (uint32_t)(x >> 32);
+            c1[a + k] = (uint32_t)x;
+            c2_wide[a + k] = pv;
+        } else {
+            c0[a + k] = ((uint32_t)(x >> 32) << 16) | ((uint32_t)x & 0xFFFFu);
+            c1[a + k] = (uint32_t)pv;
+            c2_hi[a + k] = (uint8_t)(pv >> 32);
+        }
     }
 }
 
@@ -362,6 +388,10 @@ struct CudaError : std::runtime_error {
             throw CudaError(std::string(#call) + ": " + cudaGetErrorString(e_) + " (" __FILE__ ":" + std::to_string(__LINE__) + ")"); \
     } while (0)
 
+struct DeviceOom : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
@@ -371,7 +401,16 @@ struct DevBuf {
         p = nullptr;
         cap = 0;
         const size_t want = bytes + bytes / 8 + 256;
-        CK(cudaMalloc(&p, want));
+        const cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaErrorMemoryAllocation) {
+            cudaGetLastError();
+            p = nullptr;
+            size_t free_b = 0, total_b = 0;
+            cudaMemGetInfo(&free_b, &total_b);
+            throw DeviceOom("out of device memory: a scratch buffer of " + std::to_string(want) + " bytes is needed, " + std::to_string(free_b) +
+                            " bytes are free (smaller batches or fewer lanes need less)");
+        }
+        CK(e);
         cap = want;
     }
     void release() {
@@ -389,40 +428,65 @@ struct ChunkPlan {
     uint64_t base = 0, bases = 0;       // offsets[first], total bases
     uint32_t uniform_len = 0;           // common read length, or 0 for a ragged chunk
     uint64_t max_len = 0;
-    uint64_t n_warps() const { return (n + 31) / 32; }
     bool ragged() const { return uniform_len == 0 && max_len != 0; }
-    // entries of the warp-transposed pointer buffer: exact when uniform, else the bound that holds
-    // once reads are sorted by length (sum over warps of 32 * longest <= bases + 32 * max_len)
-    uint64_t ptr_entries() const { return ragged() ? bases + 32 * max_len + 32 : n_warps() * 32 * (uint64_t)uniform_len + 32; }
+    uint64_t run_entries() const { return bases + 4 * n + 8; }        // restart pointers / records: run_base()
+    uint64_t flag_words() const { return bases / 32 + n + 2; }        // flag_base()
 };
 
+// What a call wants from a chunk: decides which scratch buffers exist and how many bytes of HBM a base costs.
+enum Mode { kModeMs = 0, kModeMems = 1, kModeSeeds = 2, kModeRuns = 3 };
+
 struct Scratch {   // device buffers of one chunk
-    DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, wbase, ptr_t, out_ptr, out_len, rec, counts, moff, mem_pos, mem_len, cub;
-    DevBuf rec_ref, mem_ref;     // seeds only
-    DevBuf len_t;                // ms only: lengths, warp-transposed like ptr_t
-    DevBuf out_hi;               // ms, packed outputs: bits 32..39 of the pointers (out_ptr then holds the u32 halves, out_len u16 lengths)
+    DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, cub;
+    DevBuf flags, rptr, rcnt;    // pass 1 -> pass 2: restart flags, pointers at the restarts, restarts per read
+    DevBuf rrec;                 // ms / runs: (query offset, length) of every restart
+    DevBuf out_ptr, out_len;     // ms: results in the caller's layout (u64 each; packed: u32 pointer halves, u16 lengths)
+    DevBuf out_hi;               // ms, packed outputs: bits 32..39 of the pointers
+    DevBuf rec, counts, moff, mem_pos, mem_len;      // mems / seeds / runs: records per read, their compaction
+    DevBuf rec_ref, mem_ref;     // seeds: text positions; runs: pointers (mem_ref)
     void release() {
-        for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &wbase, &ptr_t, &out_ptr, &out_len, &rec, &counts, &moff,
-                          &mem_pos, &mem_len, &cub, &rec_ref, &mem_ref, &len_t, &out_hi})
+        for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &cub, &flags, &rptr, &rcnt, &rrec, &out_ptr, &out_len, &out_hi, &rec,
+                          &counts, &moff, &mem_pos, &mem_len, &rec_ref, &mem_ref})
             b->release();
     }
-    void reserve(const ChunkPlan& p, bool ms, bool mems, bool seeds = false) {
-        if (seeds) { rec_ref.reserve(p.bases * 8 + 16); mem_ref.reserve(p.bases * 8 + 16); }
+    size_t held() const {
+        size_t t = 0;
+        for (const DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &cub, &flags, &rptr, &rcnt, &rrec, &out_ptr, &out_len, &out_hi, &rec,
+                                &counts, &moff, &mem_pos, &mem_len, &rec_ref, &mem_ref})
+            t += b->cap;
+        return t;
+    }
+    // HBM bytes per base of a chunk in this mode (plus a few dozen bytes per read): what bounds the chunk size on a device
+    // whose memory is mostly taken (large indexes, several replicas or processes per GPU)
+    static double bytes_per_base(int mode) {
+        const double common = 1.0 + 8.0 + 1.0 / 8.0;                  // seqs, rptr, flags
+        switch (mode) {
+            case kModeMs: return (common + 8.0 + 16.0 + 1.0) * 1.125;     // rrec, out_ptr + out_len, out_hi
+            case kModeMems: return (common + 8.0 + 16.0) * 1.125;         // rec, mem_pos + mem_len
+            case kModeSeeds: return (common + 8.0 + 16.0 + 16.0) * 1.125; // + rec_ref, mem_ref
+            default: return (common + 8.0 + 16.0 + 1.0) * 1.125;          // runs: rrec, compacted columns
+        }
+    }
+    void reserve(const ChunkPlan& p, int mode) {
         seqs.reserve(p.bases + 16);
         offs.reserve((p.n + 1) * 8);
-        ptr_t.reserve(p.ptr_entries() * 8);
-        if (p.ragged()) {
-            keys_in.reserve(p.n * 4); keys_out.reserve(p.n * 4); vals_in.reserve(p.n * 4); perm.reserve(p.n * 4);
-            wbase.reserve((p.n_warps() + 1) * 8);
-        }
-        if (ms) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); len_t.reserve(p.ptr_entries() * 4); out_hi.reserve(p.bases + 16); }
-        if (mems) {
+        flags.reserve(p.flag_words() * 4);
+        rptr.reserve(p.run_entries() * 8);
+        rcnt.reserve((p.n + 1) * 4);
+        if (p.ragged()) { keys_in.reserve(p.n * 4); keys_out.reserve(p.n * 4); vals_in.reserve(p.n * 4); perm.reserve(p.n * 4); }
+        if (mode == kModeMs || mode == kModeRuns) rrec.reserve(p.run_entries() * 8);
+        if (mode == kModeMs) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); out_hi.reserve(p.bases + 16); }
+        if (mode == kModeMems || mode == kModeSeeds) {
             rec.reserve(p.bases * 8 + 16);
             counts.reserve((p.n + 1) * 4);
+        }
+        if (mode != kModeMs) {
             moff.reserve((p.n + 1) * 16);
             mem_pos.reserve(p.bases * 8 + 16);
             mem_len.reserve(p.bases * 8 + 16);
         }
+        if (mode == kModeSeeds) { rec_ref.reserve(p.bases * 8 + 16); mem_ref.reserve(p.bases * 8 + 16); }
+        if (mode == kModeRuns) { mem_ref.reserve(p.bases * 8 + 16); out_hi.reserve(p.bases + 16); }
     }
 };
 
@@ -510,17 +574,15 @@ ChunkMap chunk_map(const Scratch& S, const ChunkPlan& p) {
     ChunkMap cm;
     cm.offs = S.offs.as<uint64_t>();
     cm.perm = p.ragged() ? S.perm.as<uint32_t>() : nullptr;
-    cm.wbase = p.ragged() ? S.wbase.as<uint64_t>() : nullptr;
     cm.base = p.base;
     cm.n_reads = (uint32_t)p.n;
-    cm.uniform_len = p.uniform_len;
     return cm;
 }
 
-// Ragged chunks: sort the reads by length (longest first) and lay out the per-warp pointer areas.
+// Ragged chunks: sort the reads by length (longest first) so that the 32 reads of a warp finish together.
 void launch_prepare(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     if (!p.ragged()) return;
-    const uint32_t n = (uint32_t)p.n, nw = (uint32_t)p.n_warps();
+    const uint32_t n = (uint32_t)p.n;
     k_read_len<<<(n + 255) / 256, 256, 0, st>>>(S.offs.as<uint64_t>(), n, S.keys_in.as<uint32_t>(), S.vals_in.as<uint32_t>());
     g_launches++;
     int bits = 1;
@@ -532,73 +594,73 @@ void launch_prepare(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     CK(cub::DeviceRadixSort::SortPairsDescending(S.cub.p, tmp, S.keys_in.as<uint32_t>(), S.keys_out.as<uint32_t>(), S.vals_in.as<uint32_t>(),
                                                  S.perm.as<uint32_t>(), (int)n, 0, bits, st));
     g_launches += 3;
-    k_warp_extent<<<(nw * 32 + 32 + 255) / 256, 256, 0, st>>>(S.offs.as<uint64_t>(), S.perm.as<uint32_t>(), n, nw, S.wbase.as<uint64_t>());
-    g_launches++;
-    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, S.wbase.as<uint64_t>(), S.wbase.as<uint64_t>(), (int)(nw + 1), st));
-    S.cub.reserve(tmp);
-    CK(cub::DeviceScan::ExclusiveSum(S.cub.p, tmp, S.wbase.as<uint64_t>(), S.wbase.as<uint64_t>(), (int)(nw + 1), st));
-    g_launches += 2;
     CK(cudaGetLastError());
 }
 
 void launch_pass1(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     if (!p.n) return;
-    const dim3 grid((unsigned)((p.n_warps() * 32 + kBlock - 1) / kBlock));
+    const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
     const ChunkMap cm = chunk_map(S, p);
     if (g_count.load())
-        k_ms_pointers<true><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.ptr_t.as<uint64_t>(), R.counters.as<Counters>());
+        k_ms_pointers<true><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(),
+                                                      S.rcnt.as<uint32_t>(), R.counters.as<Counters>());
     else
-        k_ms_pointers<false><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.ptr_t.as<uint64_t>(), nullptr);
+        k_ms_pointers<false><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(),
+                                                       S.rcnt.as<uint32_t>(), nullptr);
     g_launches++;
     CK(cudaGetLastError());
 }
 
-// mode: 0 = ms, 1 = mems, 2 = seeds
 void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, int mode, cudaStream_t st, uint32_t min_len = 0) {
     if (!p.n) return;
     const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
     const ChunkMap cm = chunk_map(S, p);
     Counters* g = g_count.load() ? R.counters.as<Counters>() : nullptr;
     const uint8_t* sq = S.seqs.as<uint8_t>();
-    const uint64_t* pt = S.ptr_t.as<uint64_t>();
+    const uint64_t* rp = S.rptr.as<uint64_t>();
+    const uint32_t* fl = S.flags.as<uint32_t>();
+    const uint32_t* rc = S.rcnt.as<uint32_t>();
     uint64_t* rec = S.rec.as<uint64_t>();
     uint32_t* cnt = S.counts.as<uint32_t>();
-    if (mode == 2) {
-        if (g) k_ms_lengths<2, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, g, S.rec_ref.as<uint64_t>(), min_len);
-        else k_ms_lengths<2, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, nullptr, S.rec_ref.as<uint64_t>(), min_len);
-    } else if (mode == 1) {
-        if (g) k_ms_lengths<1, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, g, nullptr, 0);
-        else k_ms_lengths<1, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, nullptr, rec, cnt, nullptr, nullptr, 0);
+    if (mode == kModeSeeds) {
+        if (g) k_ms_lengths<2, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, g, S.rec_ref.as<uint64_t>(), min_len);
+        else k_ms_lengths<2, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, nullptr, S.rec_ref.as<uint64_t>(), min_len);
+    } else if (mode == kModeMems) {
+        if (g) k_ms_lengths<1, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, g, nullptr, 0);
+        else k_ms_lengths<1, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, nullptr, nullptr, 0);
     } else {
-        if (g) k_ms_lengths<0, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.len_t.as<uint32_t>(), nullptr, nullptr, g, nullptr, 0);
-        else k_ms_lengths<0, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, pt, S.len_t.as<uint32_t>(), nullptr, nullptr, nullptr, nullptr, 0);
+        if (g) k_ms_lengths<0, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, S.rrec.as<uint64_t>(), nullptr, nullptr, g, nullptr, 0);
+        else k_ms_lengths<0, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, S.rrec.as<uint64_t>(), nullptr, nullptr, nullptr, nullptr, 0);
     }
     g_launches++;
     CK(cudaGetLastError());
 }
 
-// ms: pointers and lengths from the warp-transposed buffers to the caller's layout
-void launch_untranspose(Scratch& S, const ChunkPlan& p, cudaStream_t st, bool packed = false) {
+// ms: pointers and lengths from the restart runs to the caller's layout
+void launch_expand(Scratch& S, const ChunkPlan& p, cudaStream_t st, bool packed = false) {
     if (!p.n) return;
-    const dim3 grid((unsigned)((p.n_warps() * 32 + kUtBlock - 1) / kUtBlock));
+    const dim3 grid((unsigned)((p.n * 32 + kBlock - 1) / kBlock));
     if (packed)
-        k_ms_untranspose<true><<<grid, kUtBlock, 0, st>>>(chunk_map(S, p), S.ptr_t.as<uint64_t>(), S.len_t.as<uint32_t>(), nullptr, nullptr,
-                                                          S.out_ptr.as<uint32_t>(), S.out_hi.as<uint8_t>(), S.out_len.as<uint16_t>());
+        k_ms_expand<true><<<grid, kBlock, 0, st>>>(chunk_map(S, p), S.rptr.as<uint64_t>(), S.rrec.as<uint64_t>(), S.flags.as<uint32_t>(),
+                                                   S.rcnt.as<uint32_t>(), nullptr, nullptr, S.out_ptr.as<uint32_t>(), S.out_hi.as<uint8_t>(),
+                                                   S.out_len.as<uint16_t>());
     else
-        k_ms_untranspose<false><<<grid, kUtBlock, 0, st>>>(chunk_map(S, p), S.ptr_t.as<uint64_t>(), S.len_t.as<uint32_t>(), S.out_ptr.as<uint64_t>(),
-                                                           S.out_len.as<uint64_t>(), nullptr, nullptr, nullptr);
+        k_ms_expand<false><<<grid, kBlock, 0, st>>>(chunk_map(S, p), S.rptr.as<uint64_t>(), S.rrec.as<uint64_t>(), S.flags.as<uint32_t>(),
+                                                    S.rcnt.as<uint32_t>(), S.out_ptr.as<uint64_t>(), S.out_len.as<uint64_t>(), nullptr, nullptr, nullptr);
     g_launches++;
     CK(cudaGetLastError());
 }
 
 // counts -> exclusive offsets (n + 1 entries) -> gather.  mem_pos/mem_len hold `bases` entries.
-// rec_bytes: 8 = two u64 arrays, 4 = two u32 arrays, 2 = one u32 array of packed (offset:16, length:16) records,
-// 12 = seeds (u32 query offset, u32 length, u64 text position)
+// rec_bytes: 8 = two u64 arrays, 4 = two u32 arrays, 2 = one u32 array of packed (offset:16, length:16) records, 1 = one u16 array of
+// packed (offset:8, length:8) records, 12 = seeds (u32 query offset, u32 length, u64 text position),
+// 16 = runs (u32 query offset, u32 length, u64 pointer), 9 = packed runs (u32 (offset:16, length:16), u32 + u8 pointer)
 void launch_compact(Scratch& S, const ChunkPlan& p, int rec_bytes, cudaStream_t st) {
     if (!p.n) return;
     const uint32_t n = (uint32_t)p.n;
+    const bool runs = rec_bytes == 16 || rec_bytes == 9;
     uint64_t* wide = S.moff.as<uint64_t>() + (n + 1);          // second half of moff: widened counts
-    k_widen_counts<<<(n + 1 + 255) / 256, 256, 0, st>>>(S.counts.as<uint32_t>(), wide, n);
+    k_widen_counts<<<(n + 1 + 255) / 256, 256, 0, st>>>(runs ? S.rcnt.as<uint32_t>() : S.counts.as<uint32_t>(), wide, n);
     g_launches++;
     size_t tmp = 0;
     CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, wide, S.moff.as<uint64_t>(), (int)(n + 1), st));
@@ -607,7 +669,13 @@ void launch_compact(Scratch& S, const ChunkPlan& p, int rec_bytes, cudaStream_t 
     g_launches += 2;
     const uint64_t threads = (uint64_t)n * 32;
     const unsigned blocks = (unsigned)((threads + kBlock - 1) / kBlock);
-    if (rec_bytes == 12)
+    if (rec_bytes == 16)
+        k_runs_gather<true><<<blocks, kBlock, 0, st>>>(S.rptr.as<uint64_t>(), S.rrec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                       S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>(), S.mem_ref.as<uint64_t>(), nullptr);
+    else if (rec_bytes == 9)
+        k_runs_gather<false><<<blocks, kBlock, 0, st>>>(S.rptr.as<uint64_t>(), S.rrec.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
+                                                        S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>(), nullptr, S.out_hi.as<uint8_t>());
+    else if (rec_bytes == 12)
         k_seed_gather<<<blocks, kBlock, 0, st>>>(S.rec.as<uint64_t>(), S.rec_ref.as<uint64_t>(), S.offs.as<uint64_t>(), p.base, n, S.moff.as<uint64_t>(),
                                                  S.mem_pos.as<uint32_t>(), S.mem_len.as<uint32_t>(), S.mem_ref.as<uint64_t>());
     else if (rec_bytes == 2)
@@ -707,18 +775,30 @@ struct RecOut {
 
 // Processes reads [r0, r1) of a host batch on one replica.  Chunks alternate between the replica's
 // lanes (stream + scratch each), so the copies of one chunk overlap the kernels of the other.
-// mode 0 = ms, 1 = mems, 2 = seeds.  mems / seeds: records go to out.col[] (contiguous from index 0, capacity out.cap)
+// mode: kModeMs, kModeMems, kModeSeeds, kModeRuns.  All but ms: records go to out.col[] (contiguous from index 0, capacity out.cap)
 // and per-read record offsets (relative to this shard) to out.off[0 .. r1-r0]; *needed receives the shard's record count.
 void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, const uint64_t* offsets, uint64_t r0, uint64_t r1,
                uint64_t* pointers, uint64_t* lengths, const RecOut& out, uint64_t* needed, Rendezvous* rv = nullptr, int shard = 0) {
     // rv != null: out.off / out.col are the CALLER's whole-batch arrays; this shard's records are kept on
     // the device until the shards before it have published their totals, then copied to their final place.
-    const bool mems = mode != 0;
+    const bool mems = mode != kModeMs;
     uint64_t* const rec_off = out.off;
     const uint64_t rec_cap = out.cap;
     std::lock_guard<std::mutex> lock(R.mu);
     CK(cudaSetDevice(R.dev));
     for (double& x : R.t) x = 0;
+    // A chunk may not need more scratch than its lane's share of the HBM that is free (or already held by the lanes): the index
+    // image, other replicas on the same device and other processes have taken theirs.  A single read larger than that share
+    // still forms a chunk of its own and then fails with MONI_GPU_ENOMEM and the size needed.
+    uint64_t hard_cap = kChunkHardCap;
+    {
+        size_t free_b = 0, total_b = 0, held = 0;
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        for (Lane& L : R.lanes) held += L.scratch.held();
+        const double share = 0.85 * (double)(free_b + held) / (double)R.lanes.size();
+        const uint64_t fit = (uint64_t)(share / Scratch::bytes_per_base(mode));
+        hard_cap = std::max<uint64_t>(1u << 16, std::min<uint64_t>(hard_cap, fit));
+    }
     // chunks are planned (and their offsets validated) just before they are enqueued, so the host's pass over the
     // offsets overlaps the GPU's work on earlier chunks
     std::vector<ChunkPlan> plans;
@@ -738,7 +818,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
         const ChunkPlan& p = plans[c];
         Lane& L = R.lanes[c % kLanes_];
         Scratch& S = L.scratch;
-        S.reserve(p, !mems, mems, mode == 2);
+        S.reserve(p, mode);
         ev_at.push_back(L.used);
         L.take();
         cudaEvent_t* e = L.events.data() + ev_at[c];
@@ -751,6 +831,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
         CK(cudaEventRecord(e[2], L.stream));
         if (out.fmt == 2 && mems && p.max_len > 0xFFFFull) throw BadBatch("packed MEM records need reads shorter than 65536 bases");
         if (out.fmt == 1 && mems && p.max_len > 0xFFull) throw BadBatch("16-bit MEM records need reads shorter than 256 bases");
+        if (out.fmt == 9 && p.max_len > 0xFFFFull) throw BadBatch("packed restart runs need reads shorter than 65536 bases");
         launch_pass2(R, S, p, mode, L.stream, out.min_len);
         CK(cudaEventRecord(e[3], L.stream));
         if (mems) {
@@ -759,7 +840,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
         } else {
             const bool packed = out.fmt == 7;      // moni_gpu_ms_packed: col[] = u32 pointer halves, u8 pointer bits 32..39, u16 lengths
             if (packed && p.max_len > 0xFFFFull) throw BadBatch("packed matching statistics need reads shorter than 65536 bases");
-            launch_untranspose(S, p, L.stream, packed);
+            launch_expand(S, p, L.stream, packed);
             CK(cudaEventRecord(e[4], L.stream));
             if (p.bases && packed) {
                 DevBuf* const src[3] = {&S.out_ptr, &S.out_hi, &S.out_len};
@@ -786,7 +867,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
             g_launches++;
         }
         const bool last = p.first + p.n == r1;
-        DevBuf* const chunk_col[3] = {&S.mem_pos, &S.mem_len, &S.mem_ref};
+        DevBuf* const chunk_col[3] = {&S.mem_pos, &S.mem_len, out.fmt == 9 ? &S.out_hi : &S.mem_ref};
         if (rv) {
             CK(cudaMemcpyAsync(R.shard_off.as<uint64_t>() + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToDevice, L.stream));
             for (int q = 0; q < out.ncol && k; ++q)
@@ -805,7 +886,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
     try {
         for (size_t c = 0; c < fronted || next_read < r1; ++c) {
             while (next_read < r1 && fronted < c + kLanes_) {
-                plans.push_back(plan_chunk(offsets, next_read, r1, idx->opt.chunk_bases, idx->opt.chunk_min_reads));
+                plans.push_back(plan_chunk(offsets, next_read, r1, std::min(idx->opt.chunk_bases, hard_cap), idx->opt.chunk_min_reads, hard_cap));
                 next_read += plans.back().n;
                 enqueue_front(fronted++);
             }
@@ -878,6 +959,9 @@ int guarded(F&& f) {
     } catch (const CudaError& e) {
         g_err = e.what();
         return MONI_GPU_ECUDA;
+    } catch (const DeviceOom& e) {
+        g_err = e.what();
+        return MONI_GPU_ENOMEM;
     } catch (const BadBatch& e) {
         g_err = e.what();
         return MONI_GPU_EINVAL;
@@ -1139,7 +1223,7 @@ static int ms_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offset
         std::vector<int> rc(G, 0);
         auto work = [&](int g) {
             rc[g] = guarded([&]() -> int {
-                run_shard(idx, *idx->reps[g], 0, seqs, offsets, cut[g], cut[g + 1], pointers, lengths, out, nullptr);
+                run_shard(idx, *idx->reps[g], kModeMs, seqs, offsets, cut[g], cut[g + 1], pointers, lengths, out, nullptr);
                 return 0;
             });
             if (rc[g]) errs[g] = g_err;
@@ -1236,28 +1320,62 @@ static RecOut rec_out(uint64_t* off, void* a, int wa, void* b, int wb, void* c, 
 
 int moni_gpu_mems(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
                   uint64_t* mem_pos, uint64_t* mem_len, uint64_t mem_capacity) {
-    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_pos, 8, mem_len, 8, nullptr, 0, mem_capacity, 8));
+    return mems_impl(idx, kModeMems, seqs, offsets, n_reads, rec_out(mem_offsets, mem_pos, 8, mem_len, 8, nullptr, 0, mem_capacity, 8));
 }
 
 int moni_gpu_mems32(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
                     uint32_t* mem_pos, uint32_t* mem_len, uint64_t mem_capacity) {
-    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_pos, 4, mem_len, 4, nullptr, 0, mem_capacity, 4));
+    return mems_impl(idx, kModeMems, seqs, offsets, n_reads, rec_out(mem_offsets, mem_pos, 4, mem_len, 4, nullptr, 0, mem_capacity, 4));
 }
 
 int moni_gpu_mems_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
                          uint32_t* mem_rec, uint64_t mem_capacity) {
-    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_rec, 4, nullptr, 0, nullptr, 0, mem_capacity, 2));
+    return mems_impl(idx, kModeMems, seqs, offsets, n_reads, rec_out(mem_offsets, mem_rec, 4, nullptr, 0, nullptr, 0, mem_capacity, 2));
 }
 
 int moni_gpu_mems_packed16(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* mem_offsets,
                            uint16_t* mem_rec, uint64_t mem_capacity) {
-    return mems_impl(idx, 1, seqs, offsets, n_reads, rec_out(mem_offsets, mem_rec, 2, nullptr, 0, nullptr, 0, mem_capacity, 1));
+    return mems_impl(idx, kModeMems, seqs, offsets, n_reads, rec_out(mem_offsets, mem_rec, 2, nullptr, 0, nullptr, 0, mem_capacity, 1));
+}
+
+int moni_gpu_ms_runs(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* run_offsets, uint32_t* run_qpos,
+                     uint32_t* run_len, uint64_t* run_ptr, uint64_t run_capacity) {
+    return mems_impl(idx, kModeRuns, seqs, offsets, n_reads, rec_out(run_offsets, run_qpos, 4, run_len, 4, run_ptr, 8, run_capacity, 16));
+}
+
+int moni_gpu_ms_runs_packed(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* run_offsets,
+                            uint32_t* run_rec, uint32_t* ptr_lo, uint8_t* ptr_hi, uint64_t run_capacity) {
+    if (idx && idx->hdr.n > (1ull << 40) - (1ull << 31)) { g_err = "packed pointers need n <= 2^40 - 2^31"; return MONI_GPU_EINVAL; }
+    return mems_impl(idx, kModeRuns, seqs, offsets, n_reads, rec_out(run_offsets, run_rec, 4, ptr_lo, 4, ptr_hi, 1, run_capacity, 9));
+}
+
+// Host-side expansion of restart runs into the reference's two vectors (pure format conversion: between restarts the pointer grows by
+// one and the length shrinks by one, floor 0).  No device work.
+int moni_gpu_ms_runs_expand(const uint64_t* offsets, uint64_t n_reads, const uint64_t* run_offsets, const uint32_t* run_qpos,
+                            const uint32_t* run_len, const uint64_t* run_ptr, uint64_t* pointers, uint64_t* lengths) {
+    if (!offsets || !run_offsets || (n_reads && (!run_qpos || !run_len || !run_ptr || !pointers || !lengths))) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
+    for (uint64_t r = 0; r < n_reads; ++r) {
+        const uint64_t o = offsets[r], m = offsets[r + 1] - o;
+        uint64_t k = run_offsets[r];
+        const uint64_t ke = run_offsets[r + 1];
+        if (m && (k == ke || run_qpos[k] != 0)) { g_err = "read " + std::to_string(r) + ": runs must start at query offset 0"; return MONI_GPU_EINVAL; }
+        for (; k < ke; ++k) {
+            const uint64_t i0 = run_qpos[k], i1 = k + 1 < ke ? run_qpos[k + 1] : m;
+            if (i1 <= i0 || i1 > m) { g_err = "read " + std::to_string(r) + ": run offsets must increase inside the read"; return MONI_GPU_EINVAL; }
+            const uint64_t p0 = run_ptr[k], l0 = run_len[k];
+            for (uint64_t i = i0; i < i1; ++i) {
+                pointers[o + i] = p0 + (i - i0);
+                lengths[o + i] = l0 > i - i0 ? l0 - (i - i0) : 0;
+            }
+        }
+    }
+    return 0;
 }
 
 int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t min_len,
                    uint64_t* seed_offsets, uint64_t* seed_ref, uint32_t* seed_qpos, uint32_t* seed_len, uint64_t seed_capacity) {
     const uint32_t ml = min_len > 0x7FFFFFFFull ? 0x7FFFFFFFu : (uint32_t)min_len;     // reads are shorter than 2^31
-    return mems_impl(idx, 2, seqs, offsets, n_reads, rec_out(seed_offsets, seed_qpos, 4, seed_len, 4, seed_ref, 8, seed_capacity, 12, ml));
+    return mems_impl(idx, kModeSeeds, seqs, offsets, n_reads, rec_out(seed_offsets, seed_qpos, 4, seed_len, 4, seed_ref, 8, seed_capacity, 12, ml));
 }
 
 int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
@@ -1387,7 +1505,8 @@ int moni_gpu_batch_create(moni_gpu_index* idx, int gpu_slot, const char* seqs, c
         CK(cudaSetDevice(R.dev));
         b->plan = plan_chunk(offsets, 0, n_reads, ~0ull, 0, ~0ull);
         const ChunkPlan& p = b->plan;
-        b->s.reserve(p, true, true);
+        b->s.reserve(p, kModeMs);
+        b->s.reserve(p, kModeMems);
         if (p.bases) CK(cudaMemcpyAsync(b->s.seqs.p, seqs + p.base, p.bases, cudaMemcpyHostToDevice, R.stream()));
         CK(cudaMemcpyAsync(b->s.offs.p, offsets, (n_reads + 1) * 8, cudaMemcpyHostToDevice, R.stream()));
         CK(cudaStreamSynchronize(R.stream()));
@@ -1410,10 +1529,10 @@ int moni_gpu_batch_run(moni_gpu_batch* b, int what, float kernel_ms[3]) {
         launch_prepare(b->s, b->plan, L.stream);
         launch_pass1(R, b->s, b->plan, L.stream);
         CK(cudaEventRecord(e[1], L.stream));
-        launch_pass2(R, b->s, b->plan, what == 2 ? 1 : 0, L.stream);
+        launch_pass2(R, b->s, b->plan, what == 2 ? kModeMems : kModeMs, L.stream);
         CK(cudaEventRecord(e[2], L.stream));
         if (what == 2) launch_compact(b->s, b->plan, 8, L.stream);
-        else launch_untranspose(b->s, b->plan, L.stream);
+        else launch_expand(b->s, b->plan, L.stream);
         CK(cudaEventRecord(e[3], L.stream));
         CK(cudaStreamSynchronize(L.stream));
         b->last = what;

@@ -579,3 +579,77 @@ def test_mems_packed16_equals_mems(m, indexes):
     assert e.value.code == -1
     three.close()
     small.close()
+
+
+def _runs_of(ptr, ln, offs):
+    """Restart runs of reference-style vectors, in numpy: restart at i == 0 or ptr[i] != ptr[i-1] + 1 (u64 arithmetic)."""
+    total = int(offs[-1])
+    rst = np.ones(total, dtype=bool)
+    with np.errstate(over="ignore"):
+        rst[1:] = ptr[1:] != ptr[:-1] + np.uint64(1)
+    rst[offs[:-1][offs[:-1] < total].astype(np.int64)] = True
+    at = np.nonzero(rst)[0]
+    read_of = np.searchsorted(offs, at, side="right") - 1
+    qpos = (at - offs[read_of].astype(np.int64)).astype(np.uint32)
+    ro = np.zeros(offs.shape[0], dtype=np.uint64)
+    np.cumsum(np.bincount(read_of, minlength=offs.shape[0] - 1), out=ro[1:])
+    return ro, qpos, ln[at].astype(np.uint32), ptr[at]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_ms_runs_expand_to_ms(case, m, indexes):
+    """moni_gpu_ms_runs returns exactly the restarts of the reference's vectors, and moni_gpu_ms_runs_expand rebuilds
+    pointers[] / lengths[] bit for bit (withN: wrapped pointers 2^64 - k); packed runs decode to the same; three replicas
+    keep the input order."""
+    names, seqs = read_fastq(os.path.join(GOLDEN, case + ".fq"))
+    seqs = seqs + [b"", b"A", b"ACGT" * 70]
+    flat, offs = pack(seqs)
+    ix = indexes[case]
+    ptr, ln = ix.matching_statistics(flat, offs)
+    ro, qp, rl, rp = ix.matching_statistics_runs(flat, offs)
+    want = _runs_of(ptr, ln, offs)
+    for got, exp in zip((ro, qp, rl, rp), want):
+        assert np.array_equal(got, exp)
+    p2, l2 = m.expand_runs(offs, ro, qp, rl, rp)
+    assert np.array_equal(p2, ptr) and np.array_equal(l2, ln)
+    assert m.format_ms(names, offs, p2) == open(os.path.join(GOLDEN, case + ".pointers"), "rb").read()
+    assert m.format_ms(names, offs, l2) == open(os.path.join(GOLDEN, case + ".lengths"), "rb").read()
+    rop, rec, lo, hi = ix.matching_statistics_runs(flat, offs, packed=True)
+    q2, n2, r2 = m.unpack_runs(rec, lo, hi)
+    assert np.array_equal(rop, ro) and np.array_equal(q2, qp) and np.array_equal(n2, rl) and np.array_equal(r2, rp)
+    three = m.MoniIndex(os.path.join(GOLDEN, case + ".fa"), gpus=[0, 0, 0])
+    for got, exp in zip(three.matching_statistics_runs(flat, offs), (ro, qp, rl, rp)):
+        assert np.array_equal(got, exp)
+    three.close()
+    with pytest.raises(m.MoniGpuError) as e:
+        ix.matching_statistics_runs(*pack([b"AC" * 40000]), packed=True)
+    assert e.value.code == -1
+
+
+def test_ms_runs_on_random_chunked_batches(m, oracle_mod):
+    """Runs over many chunks and lanes (small chunk size) expand to the oracle's vectors; ragged lengths incl. empty reads."""
+    rng = np.random.default_rng(77)
+    pre = os.path.join(GOLDEN, "pan4.fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = []
+    for _ in range(3000):
+        L = int(rng.integers(0, 400))
+        s = int(rng.integers(0, max(1, text.shape[0] - L - 1)))
+        r = text[s:s + L].copy()
+        mut = rng.random(L) < 0.03
+        r[mut] = np.frombuffer(b"ACGTN", dtype=np.uint8)[rng.integers(0, 5, size=int(mut.sum()))]
+        reads.append(r.tobytes())
+    flat, offs = pack(reads)
+    m.set_option("chunk_bases", 20000)
+    m.set_option("chunk_min_reads", 64)
+    try:
+        ix = m.MoniIndex(pre)
+        ro, qp, rl, rp = ix.matching_statistics_runs(flat, offs)
+        ptr, ln = m.expand_runs(offs, ro, qp, rl, rp)
+        ix.close()
+    finally:
+        m.set_option("chunk_bases", 1 << 24)
+        m.set_option("chunk_min_reads", 96 * 1024)
+    wp, wl = orc.ms(flat, offs)
+    assert np.array_equal(ptr, wp) and np.array_equal(ln, wl)

@@ -324,3 +324,33 @@ def test_exporter_image_does_not_depend_on_its_thread_count(case, host_sim, tmp_
             assert r.returncode == 0, r.stderr
             seen.add(re.search(rb"move table hash ([0-9a-f]+) rows (\d+)", r.stderr).groups())
         assert len(seen) == 1, (max_scan, seen)
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_runs_expand_rebuilds_the_reference_vectors(case):
+    """moni_gpu_ms_runs_expand (host-side format conversion, no device) on the restarts of the reference's own .pointers /
+    .lengths files gives those files back, wrapped pointers included; malformed runs are rejected."""
+    import moni_align_b200 as m
+    import refparse
+    pre = os.path.join(GOLDEN, case)
+    _, cnt, ptr = refparse.parse_values(pre + ".pointers")
+    _, _, ln = refparse.parse_values(pre + ".lengths")
+    offs = np.zeros(cnt.shape[0] + 1, dtype=np.uint64)
+    np.cumsum(cnt, out=offs[1:])
+    total = int(offs[-1])
+    rst = np.ones(total, dtype=bool)
+    with np.errstate(over="ignore"):
+        rst[1:] = ptr[1:] != ptr[:-1] + np.uint64(1)
+    rst[offs[:-1].astype(np.int64)] = True
+    at = np.nonzero(rst)[0]
+    read_of = np.searchsorted(offs, at, side="right") - 1
+    ro = np.zeros(offs.shape[0], dtype=np.uint64)
+    np.cumsum(np.bincount(read_of, minlength=cnt.shape[0]), out=ro[1:])
+    qpos = (at - offs[read_of].astype(np.int64)).astype(np.uint32)
+    p2, l2 = m.expand_runs(offs, ro, qpos, ln[at].astype(np.uint32), ptr[at])
+    assert np.array_equal(p2, ptr) and np.array_equal(l2, ln)
+    assert at.shape[0] < total                      # runs really are fewer than bases on these fixtures
+    bad = qpos.copy()
+    bad[0] = 1
+    with pytest.raises(m.MoniGpuError):
+        m.expand_runs(offs, ro, bad, ln[at].astype(np.uint32), ptr[at])
