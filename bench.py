@@ -75,24 +75,47 @@ def measured_peak_gbs():
 
 
 class ClockSampler(threading.Thread):
-    """Samples nvidia-smi SM clocks and throttle reasons during the timed region."""
+    """Samples SM clocks and throttle reasons during the timed region: NVML in-process (a query costs microseconds and takes no
+    driver-wide lock the way a spawned nvidia-smi does), nvidia-smi only if NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu: int):
         super().__init__(daemon=True)
         self.gpu, self.stop_flag, self.rows = gpu, threading.Event(), []
+        self.nv = self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(gpu)
+        except Exception:
+            self.nv = None
+
+    def _nvml_row(self):
+        nv = self.nv
+        sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+        mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        bits = [getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8), getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20), getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)]
+        return [str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits]
 
     def run(self):
         while not self.stop_flag.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                if self.nv is not None:
+                    self.rows.append(self._nvml_row())
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                         capture_output=True, text=True, timeout=5).stdout.strip()
+                    if out:
+                        self.rows.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            self.stop_flag.wait(0.1)
+            self.stop_flag.wait(0.05 if self.nv is not None else 0.25)
 
     def summary(self) -> dict:
         self.stop_flag.set()
@@ -102,7 +125,7 @@ class ClockSampler(threading.Thread):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) > 2 + i and r[2 + i].lower().startswith("active")})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+                "reasons": reasons, "samples": len(self.rows), "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
 # ------------------------------------------------------------------------------------------ reference arm
@@ -343,16 +366,18 @@ def ours_arm(args) -> None:
         for _ in range(args.warmup):
             call(h_seqs, h_offs, out)
         barrier()
-        dev_sum, stage = 0.0, np.zeros(6)
+        dev_sum, stage, per_step = 0.0, np.zeros(6), []
         t_wall = time.perf_counter()
         for _ in range(args.steps):
+            t_s = time.perf_counter()
             call(h_seqs, h_offs, out)
+            per_step.append((time.perf_counter() - t_s) * 1e3)
             tt = ix.timing()
             dev_sum += tt["total_ms"]
             stage += np.array([tt[k] for k in ("h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms")])
         barrier()
         wall = (time.perf_counter() - t_wall) * 1e3
-        return {"dev": max_over_ranks(dev_sum, dev), "wall": max_over_ranks(wall, dev), "stage": stage}
+        return {"dev": max_over_ranks(dev_sum, dev), "wall": max_over_ranks(wall, dev), "stage": stage, "per_step": per_step}
 
     legs = {}
     # mems, u64 records: the reference's own record type (std::pair<size_t,size_t>, src/mems.cpp:277-279)
@@ -416,7 +441,7 @@ def ours_arm(args) -> None:
     def leg_json(leg):
         return {"value": rate(leg), "unit": "reads/s", "api": api[leg], "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h[leg]),
                 "ms_per_step_wall": legs[leg]["wall"] / args.steps, "ms_per_step_device": legs[leg]["dev"] / args.steps,
-                "same_bits_as_resident_run": same[leg],
+                "same_bits_as_resident_run": same[leg], "ms_per_step_wall_min_median_max": [min(legs[leg]["per_step"]), float(np.median(legs[leg]["per_step"])), max(legs[leg]["per_step"])],
                 "stage_busy_ms_per_step": dict(zip(stage_names, (legs[leg]["stage"] / args.steps).tolist()))}
 
     # roofline of the dominant kernel: B200 fetches one 128-byte DRAM line per random access, so

@@ -181,18 +181,19 @@ inline char* put_u64(char* p, uint64_t v) {
 }
 
 // A batch travelling through the three stages (parse -> GPU call -> format + write).  Sequence and result buffers are
-// pinned so the library's copies run at PCIe speed; results come back in the packed layouts (7 bytes per base for ms,
-// 4 bytes per MEM) unless a read of 65536 bases or more forces the wide calls.
+// pinned so the library's copies run at PCIe speed; results come back in the packed layouts (ms: 9 bytes per restart run,
+// expanded to the reference's two vectors by the formatter threads; mems: 4 bytes per MEM) unless a read of 65536 bases or
+// more forces the wide calls.
 struct Slot {
     std::string names;                       // name bytes back to back
     std::vector<uint32_t> name_end{0};       // n_reads + 1
     std::vector<uint64_t> offsets{0};        // n_reads + 1
     char* seqs = nullptr;                    // pinned
     uint64_t cap = 0;                        // bases the pinned buffers hold
-    uint32_t* lo = nullptr;                  // ms: pointer low words; mems: packed records        (pinned, cap)
-    uint8_t* hi = nullptr;                   // ms: pointer bits 32..39                             (pinned, cap)
-    uint16_t* len16 = nullptr;               // ms: lengths                                         (pinned, cap)
-    std::vector<uint64_t> moff;              // mems: n_reads + 1
+    uint32_t* lo = nullptr;                  // ms: run records (query offset << 16 | length); mems: packed records   (pinned, cap)
+    uint8_t* hi = nullptr;                   // ms: pointer bits 32..39 of every run                                   (pinned, cap)
+    uint32_t* plo = nullptr;                 // ms: pointer low words of every run                                     (pinned, cap)
+    std::vector<uint64_t> moff;              // n_reads + 1: record (mems) or run (ms) offsets
     std::vector<uint64_t> w1, w2;            // wide fallback (reads of >= 65536 bases)
     uint64_t max_len = 0;
     bool wide = false, last = false;
@@ -200,8 +201,8 @@ struct Slot {
     uint64_t total() const { return offsets.back(); }
     void clear() { names.clear(); name_end.assign(1, 0); offsets.assign(1, 0); max_len = 0; wide = false; last = false; }
     void release() {
-        moni_gpu_host_free(seqs); moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(len16);
-        seqs = nullptr; lo = nullptr; hi = nullptr; len16 = nullptr; cap = 0;
+        moni_gpu_host_free(seqs); moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(plo);
+        seqs = nullptr; lo = nullptr; hi = nullptr; plo = nullptr; cap = 0;
     }
     // grows the pinned buffers to hold `bases` (keeps the sequence bytes already there)
     void ensure(uint64_t bases, bool mems, bool fatal = true) {
@@ -213,14 +214,14 @@ struct Slot {
         if (!ns && !fatal) return;                 // pre-allocation beside the index load: the load reports what is wrong
         if (!ns) die("cannot allocate pinned host memory for the read batch");
         if (seqs) memcpy(ns, seqs, total());
-        moni_gpu_host_free(seqs); moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(len16);
+        moni_gpu_host_free(seqs); moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(plo);
         seqs = ns;
         lo = (uint32_t*)moni_gpu_host_alloc((ncap + 4) * 4);
         hi = mems ? nullptr : (uint8_t*)moni_gpu_host_alloc(ncap + 16);
-        len16 = mems ? nullptr : (uint16_t*)moni_gpu_host_alloc((ncap + 8) * 2);
-        if (!lo || (!mems && (!hi || !len16))) {
-            if (!fatal) { cap = 0; moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(len16); moni_gpu_host_free(seqs);
-                          lo = nullptr; hi = nullptr; len16 = nullptr; seqs = nullptr; return; }
+        plo = mems ? nullptr : (uint32_t*)moni_gpu_host_alloc((ncap + 4) * 4);
+        if (!lo || (!mems && (!hi || !plo))) {
+            if (!fatal) { cap = 0; moni_gpu_host_free(lo); moni_gpu_host_free(hi); moni_gpu_host_free(plo); moni_gpu_host_free(seqs);
+                          lo = nullptr; hi = nullptr; plo = nullptr; seqs = nullptr; return; }
             die("cannot allocate pinned host memory for the results");
         }
         cap = ncap;
@@ -258,10 +259,19 @@ void format_ms(const Slot& B, int which, size_t a, size_t b, std::string& out) {
         if (B.wide) {
             const uint64_t* v = (which ? B.w2.data() : B.w1.data()) + o;
             for (uint64_t i = 0; i < m; ++i) { p = put_u64(p, v[i]); *p++ = ' '; }
-        } else if (which) {
-            for (uint64_t i = 0; i < m; ++i) { p = put_u64(p, B.len16[o + i]); *p++ = ' '; }
         } else {
-            for (uint64_t i = 0; i < m; ++i) { p = put_u64(p, unpack_pointer(B.lo[o + i], B.hi[o + i])); *p++ = ' '; }
+            // restart runs -> the reference's vectors (include/moni_gpu.h, moni_gpu_ms_runs): inside a run the pointer grows by
+            // one and the length shrinks by one, floor 0 (src/matching_statistics.cpp:246-255)
+            for (uint64_t k = B.moff[r], ke = B.moff[r + 1]; k < ke; ++k) {
+                const uint64_t i0 = B.lo[k] >> 16, i1 = k + 1 < ke ? B.lo[k + 1] >> 16 : m;
+                if (which) {
+                    const uint64_t l0 = B.lo[k] & 0xFFFF;
+                    for (uint64_t i = i0; i < i1; ++i) { p = put_u64(p, l0 > i - i0 ? l0 - (i - i0) : 0); *p++ = ' '; }
+                } else {
+                    const uint64_t p0 = unpack_pointer(B.plo[k], B.hi[k]);
+                    for (uint64_t i = i0; i < i1; ++i) { p = put_u64(p, p0 + (i - i0)); *p++ = ' '; }
+                }
+            }
         }
         put_header(B, r, out);
         out.append(tmp.data(), p - tmp.data());
@@ -507,7 +517,8 @@ int main(int argc, char** argv) {
                     }
                 } else {
                     if (!B.wide) {
-                        rc = moni_gpu_ms_packed(idx, B.seqs, B.offsets.data(), nr, B.lo, B.hi, B.len16);
+                        B.moff.resize(nr + 1);
+                        rc = moni_gpu_ms_runs_packed(idx, B.seqs, B.offsets.data(), nr, B.moff.data(), B.lo, B.plo, B.hi, total);
                         if (rc == MONI_GPU_EINVAL) B.wide = true;          // text too long for 40-bit packed pointers
                     }
                     if (B.wide) {

@@ -41,7 +41,10 @@ using namespace moni;
 namespace {
 
 #ifndef MONI_P1_MINBLOCKS
-#define MONI_P1_MINBLOCKS 1          // resident CTAs per SM the pass-1 kernel is compiled for (register cap = 65536 / (128 * this))
+#define MONI_P1_MINBLOCKS 12         // resident CTAs per SM the pass-1 kernels are compiled for (register cap 65536 / (128 * 12) -> 40, no spills)
+#endif
+#ifndef MONI_P2_MINBLOCKS
+#define MONI_P2_MINBLOCKS 12         // same cap for pass 2 (its text-in-HBM variants fit 40 registers without spills)
 #endif
 constexpr int kBlock = 128;          // 4 warps; warps never synchronise with each other after the prologue
 constexpr int kTile = 32;            // steps staged per refill
@@ -161,26 +164,186 @@ __global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers(Image
     if (COUNT) { c.bases = m; flush_counters(c, g); }
 }
 
+// ---- dynamic variants: every lane pulls its next read from a counter ------------------------------------
+// A read is a chain of dependent steps (a 10 kbp read is 10^4 of them, each a DRAM round trip), so a kernel whose lanes each
+// own one read lasts as long as its longest read while the short ones leave their lanes idle.  Here the kernel is persistent
+// (one resident wave) and a lane that finishes a read takes the next one of the chunk (ragged chunks hand them out longest
+// first): the memory system sees the same number of chains in flight from the first read to the last.
+__device__ __forceinline__ uint32_t pull_slot(uint32_t* ctr, bool want, uint32_t lane) {
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, want);
+    if (!mask) return 0xFFFFFFFFu;
+    const uint32_t leader = (uint32_t)__ffs((int)mask) - 1u;
+    uint32_t first = 0;
+    if (lane == leader) first = atomicAdd(ctr, (uint32_t)__popc(mask));
+    first = __shfl_sync(0xFFFFFFFFu, first, leader);
+    return want ? first + (uint32_t)__popc(mask & ((1u << lane) - 1u)) : 0xFFFFFFFFu;
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Pass 1, dynamic.  The bases of a lane's read arrive in shared memory as aligned 16-byte blocks fetched with cp.async one
+// block ahead of the scan (two half-windows per lane), so the read bytes cost no registers and no exposed latency.
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers_dyn(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
+                                                            uint64_t* __restrict__ rptr, uint32_t* __restrict__ flags,
+                                                            uint32_t* __restrict__ rcnt, uint32_t* __restrict__ next, Counters* g) {
+    __shared__ uint8_t tcode[256];
+    __shared__ __align__(16) uint8_t win[2][kBlock][16];
+    __shared__ uint64_t stage[kStage][kBlock];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) tcode[i] = v.sym->tcode[i];
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t wsm = (uint32_t)__cvta_generic_to_shared(&win[0][threadIdx.x][0]);
+    constexpr uint32_t kHalf = kBlock * 16;
+    bool have = false, dry = false;
+    uint32_t o = 0, m = 0, r = 0, j = 0, acc = 0, k = 0;
+    uint64_t* out = rptr;
+    uint32_t* fl = flags;
+    ScanState s;
+    scan_init(v, s);
+    Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
+    auto push = [&](uint64_t x) {
+        stage[k & (kStage - 1)][threadIdx.x] = x;
+        ++k;
+        if ((k & (kStage - 1)) == 0) {
+            ulonglong2* dst = reinterpret_cast<ulonglong2*>(out + (k - kStage));
+            dst[0] = make_ulonglong2(stage[0][threadIdx.x], stage[1][threadIdx.x]);
+            dst[1] = make_ulonglong2(stage[2][threadIdx.x], stage[3][threadIdx.x]);
+        }
+    };
+    for (;;) {
+        const bool want = !have && !dry;
+        const uint32_t slot = pull_slot(next, want, lane);
+        if (want) {
+            if (slot < cm.n_reads) {
+                r = cm.perm ? __ldg(cm.perm + slot) : slot;
+                const uint64_t a = __ldg(cm.offs + r);
+                o = (uint32_t)(a - cm.base);
+                m = (uint32_t)(__ldg(cm.offs + r + 1) - a);
+                if (m == 0) {
+                    rcnt[r] = 0;
+                } else {
+                    out = rptr + run_base(o, r);
+                    fl = flags + flag_base(o, r);
+                    scan_init(v, s);
+                    acc = 0;
+                    k = 0;
+                    j = m - 1;
+                    have = true;
+                    const uint32_t blk = (o + j) & ~15u;                     // block of the read's last base, and the one below it
+                    cp_async16(wsm + ((blk >> 4) & 1u) * kHalf, seqs + blk);
+                    if (blk >= 16u && blk > o) cp_async16(wsm + (((blk >> 4) & 1u) ^ 1u) * kHalf, seqs + (blk - 16u));
+                    cp_async_commit();
+                    cp_async_wait_all();
+                    if (COUNT) c.bases += m;
+                }
+            } else {
+                dry = true;
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, have)) break;
+        if (have) {
+            const uint32_t at = o + j;
+            const uint8_t ch = win[(at >> 4) & 1u][threadIdx.x][at & 15u];
+            const uint64_t old = s.sample;                                    // pointers[j + 1]
+            scan_step(v, tcode, ch, s, COUNT ? &c : nullptr);
+            const uint32_t i = j + 1;                                         // ms_core.cuh run_note, with the pointer list staged
+            if (i < m) {
+                if (old != s.sample + 1) { push(old); acc |= 1u << (i & 31u); }
+                if ((i & 31u) == 0) { fl[i >> 5] = acc; acc = 0; }
+            }
+            if (j == 0) {
+                push(s.sample);
+                fl[0] = acc | 1u;
+                for (uint32_t q = k & ~(uint32_t)(kStage - 1); q < k; ++q) out[q] = stage[q & (kStage - 1)][threadIdx.x];
+                rcnt[r] = k;
+                have = false;
+            } else {
+                --j;
+                const uint32_t nat = o + j;
+                if ((nat & 15u) == 15u) {                                     // entering the block below: requested 16 steps ago
+                    cp_async_wait_all();
+                    const uint32_t blk = nat & ~15u;
+                    if (blk >= 16u && blk > o) {                              // the read reaches into the block below that one
+                        cp_async16(wsm + (((blk >> 4) & 1u) ^ 1u) * kHalf, seqs + (blk - 16u));
+                        cp_async_commit();
+                    }
+                }
+            }
+        }
+    }
+    if (COUNT) flush_counters(c, g);
+}
+
+// Pass 2, dynamic: a lane walks the restarts of its read (ms_core.cuh runs_step) and then takes the next read.
+template <int MODE, bool COUNT, bool TEXT>
+__global__ void __launch_bounds__(kBlock, TEXT ? MONI_P2_MINBLOCKS : 8) k_ms_lengths_dyn(ImageView v, RunBufs B, ChunkMap cm, const uint32_t* __restrict__ rcnt,
+                                                                              uint32_t* __restrict__ counts, uint32_t* __restrict__ next, Counters* g,
+                                                                              uint32_t min_len) {
+    const uint32_t lane = threadIdx.x & 31;
+    bool have = false, dry = false;
+    uint32_t r = 0;
+    RunRead R;
+    RunState st;
+    Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (;;) {
+        const bool want = !have && !dry;
+        const uint32_t slot = pull_slot(next, want, lane);
+        if (want) {
+            if (slot < cm.n_reads) {
+                r = cm.perm ? __ldg(cm.perm + slot) : slot;
+                const uint64_t a = __ldg(cm.offs + r);
+                R.o = (uint32_t)(a - cm.base);
+                R.m = (uint32_t)(__ldg(cm.offs + r + 1) - a);
+                if (R.m == 0) {
+                    if (MODE) counts[r] = 0;
+                } else {
+                    R.cnt = __ldg(rcnt + r);
+                    R.fb = (uint32_t)flag_base(R.o, r);
+                    R.last = (uint32_t)run_base(R.o, r) + R.cnt - 1u;
+                    st = RunState();
+                    have = true;
+                }
+            } else {
+                dry = true;
+            }
+        }
+        if (!__any_sync(0xFFFFFFFFu, have)) break;
+        if (have) {
+            runs_step<MODE == 2, TEXT>(v, B, R, st, COUNT ? &c : nullptr, min_len);
+            if (st.mode == RunState::FINISHED) {
+                if (MODE) counts[r] = st.n_mems;
+                have = false;
+            }
+        }
+    }
+    if (COUNT) flush_counters(c, g);
+}
+
 // ---- pass 2: MS lengths at the restarts / MEM records / seeds ----------------------------------------
 // MODE 0 (ms, runs): rrec[] receives (i << 32) | len of every restart, next to its pointer.  MODE 1 (mems): the read's MEM
 // records, packed (i << 32) | len, go to rec[] at the read's own offset (at most one per base) and counts[read] receives their
 // number.  MODE 2 (seeds): same with seed_finder::find_mems' rule (minimum length, N filter) and rec_ref[] = pointers[i].
-template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(kBlock) k_ms_lengths(ImageView v, const uint8_t* __restrict__ seqs, ChunkMap cm,
-                                                       const uint64_t* __restrict__ rptr, const uint32_t* __restrict__ flags,
-                                                       const uint32_t* __restrict__ rcnt, uint64_t* __restrict__ rrec,
-                                                       uint64_t* __restrict__ rec, uint32_t* __restrict__ counts, Counters* g,
-                                                       uint64_t* __restrict__ rec_ref, uint32_t min_len) {
+template <int MODE, bool COUNT, bool TEXT>
+__global__ void __launch_bounds__(kBlock, TEXT ? MONI_P2_MINBLOCKS : 8) k_ms_lengths(ImageView v, RunBufs B, ChunkMap cm, const uint32_t* __restrict__ rcnt,
+                                                                          uint32_t* __restrict__ counts, Counters* g, uint32_t min_len) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= cm.n_reads) return;
     const uint32_t r = cm.perm ? __ldg(cm.perm + slot) : slot;
     const uint64_t a = __ldg(cm.offs + r);
-    const uint64_t o = a - cm.base, m = __ldg(cm.offs + r + 1) - a;
-    if (m == 0) { if (MODE) counts[r] = 0; return; }
-    const uint64_t rb = run_base(o, r);
+    RunRead R;
+    R.o = (uint32_t)(a - cm.base);
+    R.m = (uint32_t)(__ldg(cm.offs + r + 1) - a);
+    if (R.m == 0) { if (MODE) counts[r] = 0; return; }
+    R.cnt = __ldg(rcnt + r);
+    R.fb = (uint32_t)flag_base(R.o, r);
+    R.last = (uint32_t)run_base(R.o, r) + R.cnt - 1u;
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
-    const uint32_t k = runs_read<MODE == 2>(v, seqs + o, m, flags + flag_base(o, r), rptr + rb, __ldg(rcnt + r), MODE ? nullptr : rrec + rb,
-                                            MODE ? rec + o : nullptr, COUNT ? &c : nullptr, MODE == 2 ? rec_ref + o : nullptr, min_len);
+    const uint32_t k = runs_read<MODE == 2, TEXT>(v, B, R, COUNT ? &c : nullptr, min_len);
     if (MODE) counts[r] = k;
     if (COUNT) flush_counters(c, g);
 }
@@ -373,6 +536,7 @@ struct Options {
     uint64_t chunk_min_reads = 96 * 1024;
     uint32_t l2_fetch = 0;          // 0 = leave the device default
     uint32_t lanes = 4;
+    int dynamic = 2;                // 0 = one read per lane, 1 = persistent kernels whose lanes pull reads, 2 = auto (pull when reads are ragged)
 };
 Options g_opt;
 inline double wall_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
@@ -437,7 +601,7 @@ struct ChunkPlan {
 enum Mode { kModeMs = 0, kModeMems = 1, kModeSeeds = 2, kModeRuns = 3 };
 
 struct Scratch {   // device buffers of one chunk
-    DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, cub;
+    DevBuf seqs, offs, keys_in, keys_out, vals_in, perm, cub, ctr;
     DevBuf flags, rptr, rcnt;    // pass 1 -> pass 2: restart flags, pointers at the restarts, restarts per read
     DevBuf rrec;                 // ms / runs: (query offset, length) of every restart
     DevBuf out_ptr, out_len;     // ms: results in the caller's layout (u64 each; packed: u32 pointer halves, u16 lengths)
@@ -445,13 +609,13 @@ struct Scratch {   // device buffers of one chunk
     DevBuf rec, counts, moff, mem_pos, mem_len;      // mems / seeds / runs: records per read, their compaction
     DevBuf rec_ref, mem_ref;     // seeds: text positions; runs: pointers (mem_ref)
     void release() {
-        for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &cub, &flags, &rptr, &rcnt, &rrec, &out_ptr, &out_len, &out_hi, &rec,
+        for (DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &cub, &ctr, &flags, &rptr, &rcnt, &rrec, &out_ptr, &out_len, &out_hi, &rec,
                           &counts, &moff, &mem_pos, &mem_len, &rec_ref, &mem_ref})
             b->release();
     }
     size_t held() const {
         size_t t = 0;
-        for (const DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &cub, &flags, &rptr, &rcnt, &rrec, &out_ptr, &out_len, &out_hi, &rec,
+        for (const DevBuf* b : {&seqs, &offs, &keys_in, &keys_out, &vals_in, &perm, &cub, &ctr, &flags, &rptr, &rcnt, &rrec, &out_ptr, &out_len, &out_hi, &rec,
                                 &counts, &moff, &mem_pos, &mem_len, &rec_ref, &mem_ref})
             t += b->cap;
         return t;
@@ -473,6 +637,7 @@ struct Scratch {   // device buffers of one chunk
         flags.reserve(p.flag_words() * 4);
         rptr.reserve(p.run_entries() * 8);
         rcnt.reserve((p.n + 1) * 4);
+        ctr.reserve(16);
         if (p.ragged()) { keys_in.reserve(p.n * 4); keys_out.reserve(p.n * 4); vals_in.reserve(p.n * 4); perm.reserve(p.n * 4); }
         if (mode == kModeMs || mode == kModeRuns) rrec.reserve(p.run_entries() * 8);
         if (mode == kModeMs) { out_ptr.reserve(p.bases * 8 + 16); out_len.reserve(p.bases * 8 + 16); out_hi.reserve(p.bases + 16); }
@@ -512,6 +677,8 @@ struct Lane {
 
 struct Replica {
     int dev = 0;
+    int sms = 0;
+    int dynamic = 2;
     std::vector<Lane> lanes;
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
     DevBuf phi, phi_inv, phi_dir, phi_inv_dir;            // `moni align` indexes only
@@ -597,41 +764,78 @@ void launch_prepare(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     CK(cudaGetLastError());
 }
 
+// Blocks of one resident wave of a persistent kernel (never more than the chunk has reads for).
+template <typename K>
+unsigned persistent_grid(const Replica& R, K kernel, uint64_t n_reads) {
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlock, 0));
+    const uint64_t wave = (uint64_t)std::max(per_sm, 1) * (uint64_t)std::max(R.sms, 1);
+    return (unsigned)std::min<uint64_t>(wave, (n_reads + kBlock - 1) / kBlock);
+}
+
+bool use_dynamic(const Replica& R, const ChunkPlan& p) { return R.dynamic == 1 || (R.dynamic == 2 && p.ragged()); }
+
 void launch_pass1(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     if (!p.n) return;
-    const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
     const ChunkMap cm = chunk_map(S, p);
-    if (g_count.load())
-        k_ms_pointers<true><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(),
-                                                      S.rcnt.as<uint32_t>(), R.counters.as<Counters>());
-    else
-        k_ms_pointers<false><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(),
-                                                       S.rcnt.as<uint32_t>(), nullptr);
+    const bool count = g_count.load();
+    Counters* g = count ? R.counters.as<Counters>() : nullptr;
+    if (use_dynamic(R, p)) {
+        CK(cudaMemsetAsync(S.ctr.p, 0, 16, st));
+        if (count)
+            k_ms_pointers_dyn<true><<<persistent_grid(R, k_ms_pointers_dyn<true>, p.n), kBlock, 0, st>>>(
+                R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(), S.rcnt.as<uint32_t>(), S.ctr.as<uint32_t>(), g);
+        else
+            k_ms_pointers_dyn<false><<<persistent_grid(R, k_ms_pointers_dyn<false>, p.n), kBlock, 0, st>>>(
+                R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(), S.rcnt.as<uint32_t>(), S.ctr.as<uint32_t>(), nullptr);
+    } else {
+        const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
+        if (count)
+            k_ms_pointers<true><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(),
+                                                          S.rcnt.as<uint32_t>(), g);
+        else
+            k_ms_pointers<false><<<grid, kBlock, 0, st>>>(R.view, S.seqs.as<uint8_t>(), cm, S.rptr.as<uint64_t>(), S.flags.as<uint32_t>(),
+                                                           S.rcnt.as<uint32_t>(), nullptr);
+    }
     g_launches++;
     CK(cudaGetLastError());
 }
 
-void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, int mode, cudaStream_t st, uint32_t min_len = 0) {
-    if (!p.n) return;
-    const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
+template <int MODE, bool TEXT>
+void launch_pass2_mode(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st, uint32_t min_len) {
     const ChunkMap cm = chunk_map(S, p);
     Counters* g = g_count.load() ? R.counters.as<Counters>() : nullptr;
-    const uint8_t* sq = S.seqs.as<uint8_t>();
-    const uint64_t* rp = S.rptr.as<uint64_t>();
-    const uint32_t* fl = S.flags.as<uint32_t>();
+    RunBufs B;
+    B.seqs = S.seqs.as<uint8_t>();
+    B.flags = S.flags.as<uint32_t>();
+    B.rptr = S.rptr.as<uint64_t>();
+    B.rrec = MODE == 0 ? S.rrec.as<uint64_t>() : nullptr;
+    B.rec = MODE ? S.rec.as<uint64_t>() : nullptr;
+    B.rec_ref = MODE == 2 ? S.rec_ref.as<uint64_t>() : nullptr;
     const uint32_t* rc = S.rcnt.as<uint32_t>();
-    uint64_t* rec = S.rec.as<uint64_t>();
-    uint32_t* cnt = S.counts.as<uint32_t>();
-    if (mode == kModeSeeds) {
-        if (g) k_ms_lengths<2, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, g, S.rec_ref.as<uint64_t>(), min_len);
-        else k_ms_lengths<2, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, nullptr, S.rec_ref.as<uint64_t>(), min_len);
-    } else if (mode == kModeMems) {
-        if (g) k_ms_lengths<1, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, g, nullptr, 0);
-        else k_ms_lengths<1, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, nullptr, rec, cnt, nullptr, nullptr, 0);
+    uint32_t* cnt = MODE ? S.counts.as<uint32_t>() : nullptr;
+    if (use_dynamic(R, p)) {
+        uint32_t* next = S.ctr.as<uint32_t>() + 1;        // zeroed with pass 1's counter
+        if (g) k_ms_lengths_dyn<MODE, true, TEXT><<<persistent_grid(R, k_ms_lengths_dyn<MODE, true, TEXT>, p.n), kBlock, 0, st>>>(R.view, B, cm, rc, cnt, next, g, min_len);
+        else k_ms_lengths_dyn<MODE, false, TEXT><<<persistent_grid(R, k_ms_lengths_dyn<MODE, false, TEXT>, p.n), kBlock, 0, st>>>(R.view, B, cm, rc, cnt, next, nullptr, min_len);
     } else {
-        if (g) k_ms_lengths<0, true><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, S.rrec.as<uint64_t>(), nullptr, nullptr, g, nullptr, 0);
-        else k_ms_lengths<0, false><<<grid, kBlock, 0, st>>>(R.view, sq, cm, rp, fl, rc, S.rrec.as<uint64_t>(), nullptr, nullptr, nullptr, nullptr, 0);
+        const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
+        if (g) k_ms_lengths<MODE, true, TEXT><<<grid, kBlock, 0, st>>>(R.view, B, cm, rc, cnt, g, min_len);
+        else k_ms_lengths<MODE, false, TEXT><<<grid, kBlock, 0, st>>>(R.view, B, cm, rc, cnt, nullptr, min_len);
     }
+}
+
+template <int MODE>
+void launch_pass2_mode(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st, uint32_t min_len) {
+    if (R.view.hdr.root_ref & kLeafBit) launch_pass2_mode<MODE, true>(R, S, p, st, min_len);       // the text itself is in HBM
+    else launch_pass2_mode<MODE, false>(R, S, p, st, min_len);
+}
+
+void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, int mode, cudaStream_t st, uint32_t min_len = 0) {
+    if (!p.n) return;
+    if (mode == kModeSeeds) launch_pass2_mode<2>(R, S, p, st, min_len);
+    else if (mode == kModeMems) launch_pass2_mode<1>(R, S, p, st, 0);
+    else launch_pass2_mode<0>(R, S, p, st, 0);
     g_launches++;
     CK(cudaGetLastError());
 }
@@ -716,7 +920,7 @@ ChunkPlan plan_chunk(const uint64_t* offsets, uint64_t a, uint64_t r1, uint64_t 
     p.first = a;
     p.base = offsets[a];
     uint64_t b = a, lo = ~0ull, hi = 0;
-    while (b < r1 && b - a < 0x7FFFFFE0ull) {
+    while (b < r1 && b - a < (1ull << 28)) {          // run_base / flag_base stay below 2^32
         const uint64_t s = offsets[b], e = offsets[b + 1];
         if (e < s) throw BadBatch("offsets must be non-decreasing");
         if (e - s >= 0x7FFFFFFFull) throw BadBatch("reads of 2^31 bases or more are not supported");
@@ -1004,6 +1208,7 @@ int moni_gpu_set_option(const char* key, const char* value) {
     else if (k == "chunk_bases" && v >= 1 && v <= (1ll << 31)) g_opt.chunk_bases = (uint64_t)v;
     else if (k == "chunk_min_reads" && v >= 0) g_opt.chunk_min_reads = (uint64_t)v;
     else if (k == "lanes" && v >= 1 && v <= kMaxLanes) g_opt.lanes = (uint32_t)v;
+    else if (k == "dynamic" && v >= 0 && v <= 2) g_opt.dynamic = (int)v;
     else if (k == "l2_fetch" && (v == 0 || v == 32 || v == 64 || v == 128)) g_opt.l2_fetch = (uint32_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }
     return 0;
@@ -1145,7 +1350,9 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
         for (int g = 0; g < n_gpus; ++g) {
             std::unique_ptr<Replica> R(new Replica);
             R->dev = devs[g];
+            R->dynamic = idx->opt.dynamic;
             CK(cudaSetDevice(R->dev));
+            CK(cudaDeviceGetAttribute(&R->sms, cudaDevAttrMultiProcessorCount, R->dev));
             if (idx->opt.l2_fetch) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, idx->opt.l2_fetch));
             R->lanes.resize(idx->opt.lanes);
             for (Lane& L : R->lanes) CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));

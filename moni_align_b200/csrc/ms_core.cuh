@@ -274,67 +274,102 @@ struct RunState {
     uint32_t k = 0;                 // restarts finished
     uint32_t w = 0, bits = 0;       // flag cursor: bits = flags of word w not yet visited
     uint32_t ip = 0, Lp = 0;        // previous restart and its length
-    uint32_t i = 0, l = 0, prev_len = 0, n_mems = 0;
+    uint32_t i = 0, l = 0, n_mems = 0;
     uint32_t n_Ns = 0;              // seeds only: length of the run of 'N' that ends the characters compared so far
     uint32_t ref = 0;               // DESCEND: current grammar reference
     uint64_t pos = 0;
-    uint64_t nxt = 0;               // pointer of the next restart, loaded one micro-step ahead (valid once primed)
-    bool primed = false;
+    uint64_t nxt = 0, nxt2 = 0;     // pointers of the next two restarts, loaded ahead
     uint64_t span = 0, p = 0;       // DESCEND: expansion length of ref, offset inside it
     const uint8_t* t = nullptr;     // COMPARE: next text byte
     uint64_t rem = 0;               // COMPARE: text bytes left in the literal block
 };
 
-// One micro-step of read `seq[0..m)`, m >= 1.  flags = the read's flag words, rlast = &rptr[cnt - 1] (the entry of restart i = 0;
-// the k-th restart in increasing query offset is rlast[-k]), cnt = number of restarts.  When a restart is finished, writes
-// rrec_last[-k] = (i << 32) | len (if not null) and the MEM record(s) (packed (i << 32) | len, if mem_out != null): the
-// reference's rule `i == 0 || len[i] >= len[i-1]` (src/mems.cpp:257-258) also fires at offsets between restarts whose
-// predecessor has length 0 (then len stays 0): those (i, 0) records are written on the way to the next restart.
+// The chunk buffers pass 2 works on (kernel-constant) and where one read lives in them (32-bit: a chunk holds fewer than 2^32
+// bases and 2^28 reads).  Keeping offsets instead of six pointers per lane is worth eight registers in the kernel.
+struct RunBufs {
+    const uint8_t* seqs = nullptr;      // read bytes of the chunk
+    const uint32_t* flags = nullptr;    // restart flags (flag_base)
+    const uint64_t* rptr = nullptr;     // pointers at the restarts (run_base)
+    uint64_t* rrec = nullptr;           // (i << 32) | len of every restart, same indexing as rptr; or null
+    uint64_t* rec = nullptr;            // MEM / seed records at the read's own offset; or null
+    uint64_t* rec_ref = nullptr;        // seeds: pointers[i] of every record; or null
+};
+struct RunRead {
+    uint32_t o = 0;         // chunk-relative offset of the read's first base (also where its records go)
+    uint32_t m = 0;         // length, >= 1
+    uint32_t fb = 0;        // first flag word
+    uint32_t last = 0;      // index in rptr / rrec of the restart at query offset 0 (= first entry + cnt - 1)
+    uint32_t cnt = 0;       // restarts
+};
+
+// One micro-step of a read.  The k-th restart in increasing query offset is rptr[last - k].  When a restart is finished, writes
+// rrec[last - k] = (i << 32) | len (if rrec) and the MEM record(s) (packed (i << 32) | len, if rec): the reference's rule
+// `i == 0 || len[i] >= len[i-1]` (src/mems.cpp:257-258) also fires at offsets between restarts whose predecessor has length 0
+// (then len stays 0): those (i, 0) records are written on the way to the next restart.
 // SEEDS: the record rule is seed_finder::find_mems' (include/aligner/seed_finder.hpp:148): l >= pl and n_Ns < l and
 // l >= min_len, where n_Ns counts the consecutive 'N' at the end of the characters matched so far (:139-143; it is only
-// touched when a character is compared and matches), which can only hold at a restart; ref_out[k] receives pointers[i].
-// Call while st.mode != FINISHED.  m < 2^31.
-template <bool SEEDS = false>
-MONI_HD void runs_step(const ImageView& v, const uint8_t* seq, uint32_t m, const uint32_t* flags, const uint64_t* rlast, uint32_t cnt,
-                       uint64_t* rrec_last, uint64_t* mem_out, RunState& st, Counters* ctr, uint64_t* ref_out = nullptr,
-                       uint32_t min_len = 0) {
+// touched when a character is compared and matches), which can only hold at a restart; rec_ref[k] receives pointers[i].
+// TEXT: the whole text is one literal block in HBM (ImageHeader::root_ref is a leaf): no descent, the compare address is
+// pool + pos + l, and the line the NEXT restart will read is requested (prefetch.global.L2) while this one is compared -- its
+// address is the next pointer plus the length this restart starts from, minus the distance to the next restart, which is
+// within a few bytes of where that compare will really start -- so a lane keeps two random text lines in flight.
+// Call while st.mode != FINISHED.
+template <bool SEEDS = false, bool TEXT = false>
+MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, RunState& st, Counters* ctr, uint32_t min_len = 0) {
     const uint64_t N = v.hdr.text_len;
+    const uint8_t* const text = v.pool + ((uint64_t)(v.hdr.root_ref & ~kLeafBit) << v.hdr.pool_shift);    // TEXT only
+    const uint32_t m = R.m;
     bool done = false;
     if (st.mode == RunState::NEXT) {
-        if (st.k == cnt) {                                        // offsets after the last restart: lengths run down to 0, then (i, 0) records
-            if (!SEEDS && mem_out)
-                for (uint64_t q = (uint64_t)st.ip + st.Lp + 1; q < m; ++q) mem_out[st.n_mems++] = q << 32;
+        if (st.k == R.cnt) {                                      // offsets after the last restart: lengths run down to 0, then (i, 0) records
+            if (!SEEDS && B.rec)
+                for (uint32_t q = st.ip + st.Lp + 1; q < m; ++q) B.rec[(uint64_t)R.o + st.n_mems++] = (uint64_t)q << 32;
             st.mode = RunState::FINISHED;
             return;
         }
-        if (!st.primed) { st.bits = ld(flags); st.nxt = ld(rlast); st.primed = true; }
-        while (st.bits == 0) st.bits = ld(flags + (++st.w));
+        if (st.k == 0) {
+            st.bits = ld(B.flags + R.fb);
+            st.nxt = ld(B.rptr + R.last);
+            if (R.cnt > 1) st.nxt2 = ld(B.rptr + (R.last - 1));
+        }
+        while (st.bits == 0) st.bits = ld(B.flags + R.fb + (++st.w));
         const uint32_t i = 32u * st.w + ctz32(st.bits);
         st.bits &= st.bits - 1u;
         st.pos = st.nxt;
-        if (st.k + 1 < cnt) st.nxt = ld(rlast - (int64_t)(st.k + 1));    // consumed one restart later: hides behind this restart's text access
+        st.nxt = st.nxt2;                                         // pointers are consumed two restarts after they were requested
+        if (st.k + 2 < R.cnt) st.nxt2 = ld(B.rptr + (R.last - (st.k + 2)));
         if (st.k) {
-            if (!SEEDS && mem_out)
-                for (uint64_t q = (uint64_t)st.ip + st.Lp + 1; q < i; ++q) mem_out[st.n_mems++] = q << 32;
+            if (!SEEDS && B.rec)
+                for (uint32_t q = st.ip + st.Lp + 1; q < i; ++q) B.rec[(uint64_t)R.o + st.n_mems++] = (uint64_t)q << 32;
             const uint32_t d = i - st.ip;                         // >= 1
-            st.prev_len = st.Lp > d - 1u ? st.Lp - (d - 1u) : 0u;   // len[i - 1]
             st.l = st.Lp > d ? st.Lp - d : 0u;                    // the l the reference carries into offset i
         } else {
-            st.prev_len = 0;
             st.l = 0;
         }
         st.i = i;
         if (ctr) ctr->restarts++;
+#if defined(__CUDA_ARCH__)
+        if (TEXT && st.k + 1 < R.cnt) {
+            const uint32_t d = st.bits ? ctz32(st.bits) + 32u * st.w - i : 1u;      // distance to the next restart when this word shows it
+            const uint64_t at = st.nxt + (st.l > d ? st.l - d : 0u);
+            if (at < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(text + at));
+        }
+#endif
         done = true;
         if (i + st.l < m && st.pos + st.l < N) {                  // u64 add wraps exactly as in the reference
-            st.mode = RunState::DESCEND;
-            st.ref = v.hdr.root_ref;
-            st.span = N;
-            st.p = st.pos + st.l;
             done = false;
+            if (TEXT) {
+                st.mode = RunState::COMPARE;
+                if (ctr) ctr->descents++;
+            } else {
+                st.mode = RunState::DESCEND;
+                st.ref = v.hdr.root_ref;
+                st.span = N;
+                st.p = st.pos + st.l;
+            }
         }
     }
-    if (st.mode == RunState::DESCEND) {
+    if (!TEXT && st.mode == RunState::DESCEND) {
         // tight loop on purpose: a level is ~10 instructions, far less than one trip through this function
         while (!(st.ref & kLeafBit)) {
 #if defined(__CUDA_ARCH__)
@@ -357,9 +392,10 @@ MONI_HD void runs_step(const ImageView& v, const uint8_t* seq, uint32_t m, const
         const uint32_t e = st.i + st.l;                          // < m
         uint32_t lim = m - e;
         if (lim > 8u) lim = 8u;
-        if ((uint64_t)lim > st.rem) lim = (uint32_t)st.rem;
-        const uint64_t rd = load8(seq + e);
-        const uint64_t x = load8(st.t) ^ rd;
+        const uint64_t rem = TEXT ? N - (st.pos + st.l) : st.rem;   // text bytes left (TEXT: pos + l < N holds here)
+        if ((uint64_t)lim > rem) lim = (uint32_t)rem;
+        const uint64_t rd = load8(B.seqs + ((uint64_t)R.o + e));
+        const uint64_t x = load8(TEXT ? text + (st.pos + st.l) : st.t) ^ rd;
         uint32_t k = x ? first_diff_byte(x) : 8u;
         const bool mismatch = k < lim;
         if (!mismatch) k = lim;
@@ -380,12 +416,11 @@ MONI_HD void runs_step(const ImageView& v, const uint8_t* seq, uint32_t m, const
         }
         if (ctr) ctr->chars += k + (mismatch ? 1u : 0u);
         st.l += k;
-        st.t += k;
-        st.rem -= k;
+        if (!TEXT) { st.t += k; st.rem -= k; }
         if (mismatch || e + k >= m) {
             done = true;
-        } else if (st.rem == 0) {                                // block exhausted while still matching
-            if (st.pos + st.l < N) {
+        } else if (TEXT ? rem == k : st.rem == 0) {              // block (TEXT: the text) exhausted while still matching
+            if (!TEXT && st.pos + st.l < N) {
                 st.mode = RunState::DESCEND;
                 st.ref = v.hdr.root_ref;
                 st.span = N;
@@ -397,12 +432,17 @@ MONI_HD void runs_step(const ImageView& v, const uint8_t* seq, uint32_t m, const
     }
     if (done) {
         const uint32_t i = st.i;
-        if (rrec_last) rrec_last[-(int64_t)st.k] = ((uint64_t)i << 32) | st.l;
-        const bool emit = SEEDS ? (st.l >= st.prev_len && st.n_Ns < st.l && st.l >= min_len)    // seed_finder.hpp:148 (pl starts at 0)
-                                : (i == 0 || st.l >= st.prev_len);                               // src/mems.cpp:257-258
+        if (B.rrec) B.rrec[R.last - st.k] = ((uint64_t)i << 32) | st.l;
+        uint32_t prev_len = 0;                                   // len[i - 1]
+        if (st.k) {
+            const uint32_t d1 = i - st.ip - 1u;
+            prev_len = st.Lp > d1 ? st.Lp - d1 : 0u;
+        }
+        const bool emit = SEEDS ? (st.l >= prev_len && st.n_Ns < st.l && st.l >= min_len)        // seed_finder.hpp:148 (pl starts at 0)
+                                : (i == 0 || st.l >= prev_len);                                   // src/mems.cpp:257-258
         if (emit) {
-            if (mem_out) mem_out[st.n_mems] = ((uint64_t)i << 32) | st.l;
-            if (SEEDS && ref_out) ref_out[st.n_mems] = st.pos;
+            if (B.rec) B.rec[(uint64_t)R.o + st.n_mems] = ((uint64_t)i << 32) | st.l;
+            if (SEEDS && B.rec_ref) B.rec_ref[(uint64_t)R.o + st.n_mems] = st.pos;
             ++st.n_mems;
         }
         st.ip = i;
@@ -413,12 +453,10 @@ MONI_HD void runs_step(const ImageView& v, const uint8_t* seq, uint32_t m, const
 }
 
 // The whole length loop of one read (a single lane of the state machine).  Returns the number of MEM records.
-template <bool SEEDS = false>
-MONI_HD uint32_t runs_read(const ImageView& v, const uint8_t* seq, uint64_t m, const uint32_t* flags, const uint64_t* rptr, uint32_t cnt,
-                           uint64_t* rrec, uint64_t* mem_out, Counters* ctr, uint64_t* ref_out = nullptr, uint32_t min_len = 0) {
+template <bool SEEDS = false, bool TEXT = false>
+MONI_HD uint32_t runs_read(const ImageView& v, const RunBufs& B, const RunRead& R, Counters* ctr, uint32_t min_len = 0) {
     RunState st;
-    while (st.mode != RunState::FINISHED)
-        runs_step<SEEDS>(v, seq, (uint32_t)m, flags, rptr + (cnt - 1), cnt, rrec ? rrec + (cnt - 1) : nullptr, mem_out, st, ctr, ref_out, min_len);
+    while (st.mode != RunState::FINISHED) runs_step<SEEDS, TEXT>(v, B, R, st, ctr, min_len);
     return st.n_mems;
 }
 

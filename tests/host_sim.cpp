@@ -75,6 +75,7 @@ int main(int argc, char** argv) {
         fclose(f);
 
         const uint64_t total = off[nr];
+        const bool text_mode = (img.hdr.root_ref & kLeafBit) != 0;
         std::vector<uint64_t> ptr(total + 1), len64(total + 1), mo(nr + 1), mems;
         Counters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         for (uint64_t r = 0; r < nr; ++r) {
@@ -92,10 +93,21 @@ int main(int argc, char** argv) {
                 run_note(rs, (uint32_t)j, (uint32_t)m, old, s.sample, rptr.data(), flags.data());
             }
             cnt.bases += m;
-            std::vector<uint64_t> rec(m + 1);
+            std::vector<uint64_t> rec(m + 1), ref(m + 1);
             uint32_t k = 0;
+            // the buffers as pass 2 sees them: a chunk that holds this read alone, at offset 0
+            RunBufs B;
+            B.seqs = seqs.data() + o;
+            B.flags = flags.data();
+            B.rptr = rptr.data();
+            B.rrec = rrec.data();
+            B.rec = rec.data();
+            B.rec_ref = ref.data();
+            RunRead R;
+            R.o = 0; R.m = (uint32_t)m; R.fb = 0; R.cnt = rs.k; R.last = rs.k ? rs.k - 1 : 0;
             if (m) {
-                k = runs_read<false>(v, seqs.data() + o, m, flags.data(), rptr.data(), rs.k, rrec.data(), rec.data(), &cnt);
+                // the kernels pick the text-in-HBM specialisation of pass 2 when the root of the grammar table is one literal block
+                k = text_mode ? runs_read<false, true>(v, B, R, &cnt) : runs_read<false, false>(v, B, R, &cnt);
                 expand_runs(m, flags.data(), rptr.data(), rrec.data(), rs.k, ptr.data() + o, len64.data() + o);
                 for (uint64_t j = 0; j < m; ++j)
                     if (ptr[o + j] != direct[j]) throw std::runtime_error("expanded pointers differ from the scan's");
@@ -103,9 +115,8 @@ int main(int argc, char** argv) {
             mo[r] = mems.size();
             mems.insert(mems.end(), rec.begin(), rec.begin() + k);
             if (want_seeds) {
-                std::vector<uint64_t> ref(m + 1);
-                const uint32_t ks = m ? runs_read<true>(v, seqs.data() + o, m, flags.data(), rptr.data(), rs.k, nullptr, rec.data(), nullptr, ref.data(),
-                                                        seed_min_len) : 0;
+                B.rrec = nullptr;
+                const uint32_t ks = !m ? 0 : text_mode ? runs_read<true, true>(v, B, R, nullptr, seed_min_len) : runs_read<true, false>(v, B, R, nullptr, seed_min_len);
                 so.push_back(s_ref.size());
                 for (uint32_t t = 0; t < ks; ++t) { s_ref.push_back(ref[t]); s_len.push_back(rec[t] & 0xFFFFFFFFu); s_qpos.push_back(rec[t] >> 32); }
             }

@@ -252,6 +252,19 @@ def main():
             same = same and bool(np.array_equal(m.unpack_pointers(lo[sl_], hi[sl_]), p_[sl_]) and np.array_equal(l16[sl_], l_[sl_]))
         out["ms_packed"] = {"reads": int(k_ms), "wall_ms": dt * 1e3, "reads_per_s": k_ms / dt, "bases_per_s": t_ms / dt, "d2h_bytes": 7 * t_ms,
                             "timing": ix.timing(), "same_as_ms": same}
+        out["ms"]["max_pointer"] = int(p_[p_ < np.uint64(1 << 62)].max())
+        out["ms"]["pointers_at_or_beyond_2^32"] = int((p_[p_ < np.uint64(1 << 62)] >= np.uint64(1 << 32)).sum())
+        ro = m.pinned_empty(k_ms + 1, np.uint64)
+        rq, rl, rp = m.pinned_empty(t_ms, np.uint32), m.pinned_empty(t_ms, np.uint32), m.pinned_empty(t_ms, np.uint64)
+        ix.matching_statistics_runs(h_seqs[:t_ms], h_offs[:k_ms + 1], out=(ro, rq, rl, rp))
+        t = time.perf_counter()
+        ix.matching_statistics_runs(h_seqs[:t_ms], h_offs[:k_ms + 1], out=(ro, rq, rl, rp))
+        dt = time.perf_counter() - t
+        nrun = int(ro[k_ms])
+        xp, xl = m.expand_runs(h_offs[:k_ms + 1], ro, rq[:nrun], rl[:nrun], rp[:nrun])
+        out["ms_runs"] = {"reads": int(k_ms), "wall_ms": dt * 1e3, "reads_per_s": k_ms / dt, "runs": nrun, "d2h_bytes": 16 * nrun + 8 * (k_ms + 1),
+                          "timing": ix.timing(), "expands_to_ms": bool(np.array_equal(xp, p_) and np.array_equal(xl, l_))}
+        del xp, xl
         # properties of the complete result: lengths are matching statistics of the pointers
         Lm = l_.reshape(-1, L)
         ok1 = ok2 = True
@@ -324,6 +337,30 @@ def main():
         with tempfile.TemporaryDirectory() as td:
             return cli_vs_reference(prefix, list(reads[sel]), td, "short", cores)
     parity()
+
+    @stage("edge")
+    def edge():
+        """The edge-case file of SURVEY.md 8(d) on this index: N, lowercase, symbols absent from the text, 1-base reads, reads longer
+        than any match, reads that run into the end of the text -- reference binaries vs the drop-in CLIs, byte for byte."""
+        rng = np.random.default_rng(4242)
+        N = text.shape[0]
+        lst = [np.frombuffer(b"A", dtype=np.uint8), np.frombuffer(b"N" * 60, dtype=np.uint8), np.frombuffer(b"acgtacgtacgtacgtnnnn", dtype=np.uint8),
+               text[N - 150:N].copy(), text[N - 40:N].copy(), text[0:200].copy(),
+               np.frombuffer(b"ACGTNacgtnRYKMxyz0123456789", dtype=np.uint8)[rng.integers(0, 27, size=300)],
+               synth.ACGT[rng.integers(0, 4, size=700, dtype=np.uint8)]]
+        for _ in range(200):
+            s0 = int(rng.integers(0, N - 400))
+            r = text[s0:s0 + int(rng.integers(20, 400))].copy()
+            k = int(rng.integers(0, 4))
+            for q in rng.integers(0, r.shape[0], size=k):
+                r[q] = ord("N") if rng.random() < 0.5 else ord("x")
+            lst.append(r)
+        # far ends of the text: pointers beyond 2^32 when the text is that long
+        for s0 in (N - 5000, N // 2, (1 << 32) + 12345 if N > (1 << 32) + 20000 else N // 3):
+            lst.append(text[s0:s0 + 250].copy())
+        with tempfile.TemporaryDirectory() as td:
+            return cli_vs_reference(prefix, lst, td, "edge", cores)
+    edge()
 
     m.release_pinned()
 

@@ -653,3 +653,40 @@ def test_ms_runs_on_random_chunked_batches(m, oracle_mod):
         m.set_option("chunk_min_reads", 96 * 1024)
     wp, wl = orc.ms(flat, offs)
     assert np.array_equal(ptr, wp) and np.array_equal(ln, wl)
+
+
+@pytest.mark.parametrize("case", ["pan4", "withN"])
+def test_dynamic_and_static_kernels_agree(case, m, oracle_mod):
+    """The persistent kernels whose lanes pull reads from a counter (option dynamic=1; the default for ragged chunks) and the
+    one-read-per-lane kernels (dynamic=0) give the same bits for ms, mems, seeds and runs, on ragged batches with empty reads,
+    one-base reads and reads much longer than the others, over several chunks."""
+    import synth
+    pre = os.path.join(GOLDEN, case + ".fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = [r for r in synth.short_reads(text, 2000, 100, 31, err=0.03)]
+    reads += synth.long_reads(text, 60, 32, mean=1500, sd=900, lo=1, hi=6000)
+    reads += [np.zeros(0, dtype=np.uint8), np.frombuffer(b"A", dtype=np.uint8), np.frombuffer(b"NNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNNN", dtype=np.uint8)]
+    rng = np.random.default_rng(9)
+    rng.shuffle(reads)
+    flat, offs = m.pack_reads(reads)
+    res = {}
+    for dyn in (0, 1):
+        m.set_option("dynamic", dyn)
+        m.set_option("chunk_bases", 60000)
+        m.set_option("chunk_min_reads", 200)
+        try:
+            ix = m.MoniIndex(pre)
+        finally:
+            m.set_option("dynamic", 2)
+            m.set_option("chunk_bases", 1 << 24)
+            m.set_option("chunk_min_reads", 96 * 1024)
+        res[dyn] = (ix.matching_statistics(flat, offs), ix.maxrimal_exact_matches(flat, offs), ix.find_mems(flat, offs, 12),
+                    ix.matching_statistics_runs(flat, offs))
+        ix.close()
+    for a, b in zip(res[0], res[1]):
+        assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    wp, wl = orc.ms(flat, offs)
+    assert np.array_equal(res[1][0][0], wp) and np.array_equal(res[1][0][1], wl)
+    wm = orc.mems(flat, offs)
+    assert all(np.array_equal(x, y) for x, y in zip(res[1][1], wm))
