@@ -88,13 +88,14 @@ class ClockSampler(threading.Thread):
             import pynvml
             pynvml.nvmlInit()
             self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(gpu)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
         except Exception:
             self.nv = None
 
     def _nvml_row(self):
         nv = self.nv
         sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
-        mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        mx = self.max_sm
         try:
             r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
         except Exception:
@@ -115,7 +116,7 @@ class ClockSampler(threading.Thread):
                         self.rows.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            self.stop_flag.wait(0.05 if self.nv is not None else 0.25)
+            self.stop_flag.wait(0.25)
 
     def summary(self) -> dict:
         self.stop_flag.set()
@@ -253,6 +254,15 @@ def cpu_baseline_and_parity(args, prefix, reads_flat, n_reads, read_len, gpu_mem
     return cpu, par
 
 
+API_NAMES = {"mems_u64": "moni_gpu_mems", "mems_u32": "moni_gpu_mems32", "mems_packed32": "moni_gpu_mems_packed",
+             "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed",
+             "ms_runs": "moni_gpu_ms_runs", "ms_runs_packed": "moni_gpu_ms_runs_packed"}
+
+
+def api_name(leg: str) -> str:
+    return API_NAMES[leg]
+
+
 def random_line_peak(m, local: int) -> dict:
     """The random-access roofline of this GPU, measured now (dependent random 32-byte accesses over a 3 GiB table)."""
     out = {"table_bytes": 3 << 30, "unit": "lines/s", "line_bytes": 128, "points": []}
@@ -287,8 +297,12 @@ def ours_arm(args) -> None:
     dev = torch.device("cuda", local)
     numa_note = "off" if args.no_numa_bind else bind_near_gpu(local)
     log(f"rank {rank}: CPU placement: {numa_note}")
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        # a CPU-side barrier for the one leg where rank 0 drives every GPU itself: ranks waiting in an NCCL barrier would keep a
+        # polling kernel on their GPUs
+        cpu_group = dist.new_group(backend="gloo")
     w = workloads.WORKLOADS[args.workload]
     if rank == 0:
         workloads.ensure_index(args.workload)
@@ -377,6 +391,7 @@ def ours_arm(args) -> None:
             stage += np.array([tt[k] for k in ("h2d_ms", "pass1_ms", "pass2_ms", "compact_ms", "d2h_ms", "total_ms")])
         barrier()
         wall = (time.perf_counter() - t_wall) * 1e3
+        log(f"rank {rank}: {getattr(call, '__name__', 'call')} per-step wall ms: " + " ".join(f"{x:.1f}" for x in per_step))
         return {"dev": max_over_ranks(dev_sum, dev), "wall": max_over_ranks(wall, dev), "stage": stage, "per_step": per_step}
 
     legs = {}
@@ -419,9 +434,76 @@ def ours_arm(args) -> None:
     del xp, xl, uq, ul, up
     clocks = sampler.summary() if sampler else None
     all_reads = sum_over_ranks(float(n_reads), dev)
+    n_mems_all = sum_over_ranks(float(n_mems), dev)
+
+    # ---- what the host side of the box can move: every rank copies the byte counts of the packed16 leg, both directions at once
+    head_leg = "mems_packed16" if "mems_packed16" in legs else "mems_packed32"
+    rec_b = 2 if head_leg == "mems_packed16" else 4
+    dma = None
+    if world > 1:
+        hb, db = int(total), int(8 * (n_reads + 1) + rec_b * n_mems)
+        hin, hout = pool_a.view(np.uint8)[:hb], pool_b.view(np.uint8)[:db]
+        t_in, t_out = torch.from_numpy(hin), torch.from_numpy(hout)
+        d_in = torch.empty(hb, dtype=torch.uint8, device=dev)
+        d_out = torch.empty(db, dtype=torch.uint8, device=dev)
+        s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+        def both():
+            with torch.cuda.stream(s1):
+                d_in.copy_(t_in, non_blocking=True)
+            with torch.cuda.stream(s2):
+                t_out.copy_(d_out, non_blocking=True)
+        for _ in range(2):
+            both()
+        barrier()
+        t_w = time.perf_counter()
+        for _ in range(args.steps):
+            both()
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t_w, dev)
+        dma = {"bytes_per_gpu_per_step": hb + db, "aggregate_gb_per_s": world * (hb + db) * args.steps / dt / 1e9,
+               "ms_per_step": 1e3 * dt / args.steps, "what": "cudaMemcpyAsync of the packed16 leg's bytes, pinned host memory, host->device and device->host at once on every rank, no kernels"}
+        del d_in, d_out
+
+    # ---- the in-library multi-GPU path (north star): ONE host batch of world x n_reads reads through one call on an index that
+    # holds a replica on every GPU; the library splits it by bases and lands results in input order.  Rank 0 drives it alone.
+    sharded = None
+    if world > 1 and not args.no_sharded:
+        if rank == 0:
+            try:
+                ixs = m.MoniIndex(prefix, gpus=list(range(world)))
+                big_seqs = m.pinned_empty(total * world, np.uint8, gpu=local)
+                for g in range(world):
+                    big_seqs[g * total:(g + 1) * total] = h_seqs
+                big_offs = m.pinned_empty(n_reads * world + 1, np.uint64, gpu=local)
+                big_offs[:] = np.arange(n_reads * world + 1, dtype=np.uint64) * np.uint64(read_len)
+                big_mo = m.pinned_empty(n_reads * world + 1, np.uint64, gpu=local)
+                big_rec = m.pinned_empty(n_mems * world + 16, np.uint16 if rec_b == 2 else np.uint32, gpu=local)
+                call = ixs.maxrimal_exact_matches_packed16 if rec_b == 2 else ixs.maxrimal_exact_matches_packed
+                for _ in range(args.warmup):
+                    call(big_seqs, big_offs, (big_mo, big_rec))
+                t_w = time.perf_counter()
+                for _ in range(args.steps):
+                    call(big_seqs, big_offs, (big_mo, big_rec))
+                dt = time.perf_counter() - t_w
+                shift = 8 if rec_b == 2 else 16
+                ok = int(big_mo[-1]) == n_mems * world
+                for g in range(world):       # every copy of the batch must come back as the resident run's records, in input order
+                    seg = big_rec[g * n_mems:(g + 1) * n_mems]
+                    ok = ok and bool(np.array_equal(big_mo[g * n_reads:(g + 1) * n_reads + 1] - np.uint64(g * n_mems), mo)
+                                     and np.array_equal(seg >> shift, mp) and np.array_equal(seg & ((1 << shift) - 1), ml))
+                sharded = {"value": n_reads * world * args.steps / dt, "unit": "reads/s", "api": api_name(head_leg), "gpus_in_one_call": world,
+                           "reads_per_call": int(n_reads * world), "ms_per_call_wall": 1e3 * dt / args.steps, "same_bits": bool(ok),
+                           "h2d_bytes_per_call": int(world * total), "d2h_bytes_per_call": int(8 * (n_reads * world + 1) + rec_b * n_mems * world)}
+                ixs.close()
+            except Exception as e:
+                import traceback
+                traceback.print_exc()
+                sharded = {"error": f"{type(e).__name__}: {e}"}
+        dist.barrier(group=cpu_group)
     if rank != 0:
         if world > 1:
-            dist.barrier()          # rank 0 may still be running its reference sample
+            dist.barrier(group=cpu_group)          # rank 0 finishes its line
             dist.destroy_process_group()
         return
 
@@ -433,10 +515,11 @@ def ours_arm(args) -> None:
            "mems_packed32": 8 * (n_reads + 1) + 4 * n_mems, "mems_packed16": 8 * (n_reads + 1) + 2 * n_mems,
            "ms_u64": 16 * total, "ms_packed": 7 * total, "ms_runs": 8 * (n_reads + 1) + 16 * n_runs,
            "ms_runs_packed": 8 * (n_reads + 1) + 9 * n_runs}
-    api = {"mems_u64": "moni_gpu_mems", "mems_u32": "moni_gpu_mems32", "mems_packed32": "moni_gpu_mems_packed",
-           "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed",
-           "ms_runs": "moni_gpu_ms_runs", "ms_runs_packed": "moni_gpu_ms_runs_packed"}
-    h2d = int(total + 8 * (n_reads + 1))
+    api = API_NAMES
+    h2d = int(total)            # reads of one length: the library computes their offsets on the device (k_uniform_offsets)
+    if dma:
+        dma["e2e_packed_aggregate_gb_per_s"] = world * (h2d + d2h[head_leg]) / (legs[head_leg]["wall"] / args.steps / 1e3) / 1e9
+        dma["e2e_packed_fraction_of_ceiling"] = dma["e2e_packed_aggregate_gb_per_s"] / dma["aggregate_gb_per_s"]
 
     def leg_json(leg):
         return {"value": rate(leg), "unit": "reads/s", "api": api[leg], "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(d2h[leg]),
@@ -510,10 +593,11 @@ def ours_arm(args) -> None:
         "gpu_launches": int(launches), "gpu_launches_ms_leg": int(launches_ms), "options": args.opt, "cpu_placement": numa_note,
         "host_buffers": f"pinned, NUMA node of the GPU ({m.load_library().moni_gpu_numa_node(local)})", "clocks": clocks,
         "cpu_baseline": cpu, "parity_sample": par, "index_load_s": t_load,
+        **({"host_dma_ceiling": dma} if dma else {}), **({"e2e_sharded": sharded} if sharded else {}),
     }
     emit(line)
     if world > 1:
-        dist.barrier()
+        dist.barrier(group=cpu_group)
         dist.destroy_process_group()
 
 
@@ -528,6 +612,7 @@ def main():
     ap.add_argument("--pairs", type=int, default=0, help="read pairs per GPU per step (default: the workload's bench_pairs)")
     ap.add_argument("--ref-reads", type=int, default=100_000, help="reads in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the in-library multi-GPU leg (N > 1)")
     ap.add_argument("--no-numa-bind", action="store_true", help="do not pin each rank to the CPUs local to its GPU")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (moni_gpu_set_option), repeatable")

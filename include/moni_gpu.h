@@ -104,6 +104,22 @@ int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offset
 int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
                        uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity, int* truncated);
 
+/* Replaces seed_finder::populate_seeds(std::vector<mem_t>&) (include/aligner/seed_finder.hpp:311-319 -> populate_seed :258-309) with seed
+ * filtering off, for a batch of seeds (the records moni_gpu_seeds returned; seed_qpos = mem_t.idx).  Every seed gets its find_MEM_occs
+ * list (occ_offsets / occs, exactly what moni_gpu_seed_occs returns).  A seed with seed_len >= 2 * min_len additionally yields the two
+ * seeds the reference appends to the read's vector (:277-306), stored as two consecutive entries h, h + 1 of the half_* arrays, in seed
+ * order: the left half, mem_t(upper_suffix, len >> 1, idx), whose list is upper_suffix, the suffixes above it and the suffixes below
+ * lower_suffix at the shorter length (upper / lower_suffix = the last position found above / below the seed, :272-275); and the right
+ * half, mem_t(pos + (len >> 1), len - (len >> 1), idx + (len >> 1)), with its own find_MEM_occs list.  half_parent[h] = index of the
+ * seed the half came from; half_ref / half_len / half_qpos = mem_t.pos / .len / .idx; lists in half_occ_offsets / half_occs.  The
+ * reference's per-read vector is the read's seeds followed by their halves in seed order.  *n_halves receives the number of half
+ * entries (capacity needed: 2 * n_seeds).  min_len >= 1.  Per-reference seed filtering (populate_dict, :331-) needs the lift-over
+ * index and is not done.  Needs the `moni align` index with the text resident, like moni_gpu_seed_occs; runs on the index's first GPU. */
+int moni_gpu_populate_seeds(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, const uint32_t* seed_qpos, uint64_t n_seeds,
+                            uint64_t min_len, uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity,
+                            uint64_t* n_halves, uint64_t* half_parent, uint64_t* half_ref, uint32_t* half_len, uint32_t* half_qpos,
+                            uint64_t* half_occ_offsets, uint64_t* half_occs, uint64_t half_occ_capacity, int* truncated);
+
 /* moni_gpu_ms with 7 bytes of results per base instead of 16 (the call is bound by the device->host copy): the pointer's low
  * 40 bits as ptr_lo (u32) + ptr_hi (u8), the length as u16.  pointer = lo | hi << 32, and if that is >= 2^40 - 2^31 subtract
  * 2^40 in 64-bit arithmetic: such a value is one of the reference's wrapped pointers 2^64 - k (its `sample--` after an absent

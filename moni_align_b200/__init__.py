@@ -44,6 +44,7 @@ EXPORTS = [
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
     "moni_gpu_probe_random_lines", "moni_gpu_probe_release", "moni_gpu_ms_runs", "moni_gpu_ms_runs_packed", "moni_gpu_ms_runs_expand",
+    "moni_gpu_populate_seeds",
 ]
 
 
@@ -69,6 +70,8 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_mems_packed16.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, ctypes.c_uint64]
     L.moni_gpu_seeds.argtypes = [vp, vp, _u64p, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, vp, vp, ctypes.c_uint64]
     L.moni_gpu_seed_occs.argtypes = [vp, _u64p, vp, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, ctypes.c_uint64, ctypes.POINTER(ci)]
+    L.moni_gpu_populate_seeds.argtypes = [vp, _u64p, vp, vp, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, _u64p, _u64p, ctypes.c_uint64,
+                                          _u64p, _u64p, _u64p, vp, vp, _u64p, _u64p, ctypes.c_uint64, ctypes.POINTER(ci)]
     L.moni_gpu_counters.argtypes = [vp, _u64p, ci]
     L.moni_gpu_timing.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     L.moni_gpu_set_option.argtypes = [cc, cc]
@@ -345,6 +348,59 @@ class MoniIndex:
                                             ctypes.byref(tr))
         _check(rc)
         return off, occs[:int(off[n])], bool(tr.value)
+
+    def populate_seeds(self, seed_offsets, seed_ref, seed_len, seed_qpos, min_len: int, max_per_direction: int = 1 << 20):
+        """seed_finder::populate_seeds (seed filtering off) for a batch: returns the reads' final seed vectors in the reference's order
+        -- (offsets uint64[n_reads+1], ref uint64, len uint32, qpos uint32, occ_offsets uint64, occs uint64, truncated): per read its
+        seeds with their occurrence lists, then the two halves of every seed of at least 2 * min_len bases (moni_gpu_populate_seeds)."""
+        seed_offsets = np.ascontiguousarray(seed_offsets, dtype=np.uint64)
+        seed_ref = np.ascontiguousarray(seed_ref, dtype=np.uint64)
+        seed_len = np.ascontiguousarray(seed_len, dtype=np.uint32)
+        seed_qpos = np.ascontiguousarray(seed_qpos, dtype=np.uint32)
+        n = seed_ref.shape[0]
+        tr, nh = ctypes.c_int(0), ctypes.c_uint64(0)
+        off = np.empty(n + 1, dtype=np.uint64)
+        hoff = np.empty(2 * n + 1, dtype=np.uint64)
+        hpar, href = np.empty(max(2 * n, 1), dtype=np.uint64), np.empty(max(2 * n, 1), dtype=np.uint64)
+        hlen, hq = np.empty(max(2 * n, 1), dtype=np.uint32), np.empty(max(2 * n, 1), dtype=np.uint32)
+        cap, hcap = max(4 * n, 1), max(8 * n, 1)
+        for _ in range(3):
+            occs, hoccs = np.empty(cap, dtype=np.uint64), np.empty(hcap, dtype=np.uint64)
+            rc = self._L.moni_gpu_populate_seeds(self._h, _u64(seed_ref), _ptr(seed_len), _ptr(seed_qpos), n, int(min_len), int(max_per_direction),
+                                                 _u64(off), _u64(occs), cap, ctypes.byref(nh), _u64(hpar), _u64(href), _ptr(hlen), _ptr(hq),
+                                                 _u64(hoff), _u64(hoccs), hcap, ctypes.byref(tr))
+            if rc == -4 and n:                   # a capacity was a guess: the sizes needed are in off[n] / hoff[n_halves]
+                cap = max(cap, int(off[n]))
+                hcap = max(hcap, int(hoff[int(nh.value)]) if int(nh.value) else hcap)
+                continue
+            break
+        _check(rc)
+        k = int(nh.value)
+        # the reference's per-read vectors: the read's seeds, then their halves in seed order
+        o_ref, o_len, o_q, lists = [], [], [], []
+        offs_out = [0]
+        read_of_half = np.searchsorted(seed_offsets, hpar[:k], side="right") - 1 if k else np.zeros(0, dtype=np.int64)
+        hstart = np.searchsorted(read_of_half, np.arange(seed_offsets.shape[0] - 1), side="left") if k else np.zeros(seed_offsets.shape[0] - 1, dtype=np.int64)
+        hend = np.searchsorted(read_of_half, np.arange(seed_offsets.shape[0] - 1), side="right") if k else np.zeros(seed_offsets.shape[0] - 1, dtype=np.int64)
+        for r in range(seed_offsets.shape[0] - 1):
+            a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
+            o_ref.append(seed_ref[a:b]); o_len.append(seed_len[a:b]); o_q.append(seed_qpos[a:b])
+            lists.append((off[a:b + 1], occs))
+            ha, hb = int(hstart[r]), int(hend[r])
+            o_ref.append(href[ha:hb]); o_len.append(hlen[ha:hb]); o_q.append(hq[ha:hb])
+            lists.append((hoff[ha:hb + 1], hoccs))
+            offs_out.append(offs_out[-1] + (b - a) + (hb - ha))
+        cnts, segs = [], []
+        for lo, src in lists:
+            if lo.shape[0] > 1:
+                cnts.append(np.diff(lo.astype(np.int64)))
+                segs.append(src[int(lo[0]):int(lo[-1])])
+        oo = np.zeros(offs_out[-1] + 1, dtype=np.uint64)
+        if cnts:
+            np.cumsum(np.concatenate(cnts), out=oo[1:])
+        cat = lambda xs, dt: np.concatenate(xs).astype(dt) if xs else np.zeros(0, dtype=dt)
+        return (np.array(offs_out, dtype=np.uint64), cat(o_ref, np.uint64), cat(o_len, np.uint32), cat(o_q, np.uint32), oo,
+                cat(segs, np.uint64), bool(tr.value))
 
     # -- instrumentation -----------------------------------------------------------------------
     def counters(self, reset: bool = True) -> dict:

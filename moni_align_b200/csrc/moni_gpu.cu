@@ -469,36 +469,72 @@ __global__ void __launch_bounds__(kBlock) k_mem_gather_packed(const uint64_t* __
 }
 
 // ---- occurrence enumeration: one seed per thread, Phi / Phi^-1 walks with a bounded LCE on the text in HBM -------------
-__global__ void __launch_bounds__(kBlock) k_occ_count(ImageView v, const uint64_t* __restrict__ ref, const uint32_t* __restrict__ len,
-                                                      uint64_t n_seeds, uint64_t cap, uint64_t* __restrict__ counts,
+// head / up / down: first list entry, start of the walk upwards, start of the walk downwards (ms_core.cuh occ_walk; one array
+// three times for plain seeds); above (may be null) receives the number of positions found above.
+__global__ void __launch_bounds__(kBlock) k_occ_count(ImageView v, const uint64_t* __restrict__ head, const uint64_t* __restrict__ up,
+                                                      const uint64_t* __restrict__ down, const uint32_t* __restrict__ len, uint64_t n_seeds,
+                                                      uint64_t cap, uint64_t* __restrict__ counts, uint32_t* __restrict__ above,
                                                       uint32_t* __restrict__ truncated) {
     const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     if (i > n_seeds) return;
     if (i == n_seeds) { counts[i] = 0; return; }
     bool tr = false;
-    counts[i] = occ_walk(v, ref[i], len[i], cap, nullptr, &tr);
+    uint32_t na = 0;
+    counts[i] = occ_walk(v, head[i], up[i], down[i], len[i], cap, nullptr, &tr, &na);
+    if (above) above[i] = na;
     if (tr) atomicOr(truncated, 1u);
 }
 
-__global__ void __launch_bounds__(kBlock) k_occ_fill(ImageView v, const uint64_t* __restrict__ ref, const uint32_t* __restrict__ len,
-                                                     uint64_t n_seeds, uint64_t cap, const uint64_t* __restrict__ off,
-                                                     uint64_t* __restrict__ occs) {
+__global__ void __launch_bounds__(kBlock) k_occ_fill(ImageView v, const uint64_t* __restrict__ head, const uint64_t* __restrict__ up,
+                                                     const uint64_t* __restrict__ down, const uint32_t* __restrict__ len, uint64_t n_seeds,
+                                                     uint64_t cap, const uint64_t* __restrict__ off, uint64_t* __restrict__ occs) {
     const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     if (i >= n_seeds) return;
-    occ_walk(v, ref[i], len[i], cap, occs + off[i], nullptr);
+    occ_walk(v, head[i], up[i], down[i], len[i], cap, occs + off[i], nullptr, nullptr);
 }
 
 // One walk instead of two when the per-direction cap bounds a seed's list: positions go to a fixed-stride staging area
 // (stride = 2 cap + 1; HBM has the room), and a streaming pass packs them once the offsets are known.
-__global__ void __launch_bounds__(kBlock) k_occ_walk_staged(ImageView v, const uint64_t* __restrict__ ref, const uint32_t* __restrict__ len,
-                                                            uint64_t n_seeds, uint64_t cap, uint64_t stride, uint64_t* __restrict__ counts,
-                                                            uint64_t* __restrict__ staging, uint32_t* __restrict__ truncated) {
+__global__ void __launch_bounds__(kBlock) k_occ_walk_staged(ImageView v, const uint64_t* __restrict__ head, const uint64_t* __restrict__ up,
+                                                            const uint64_t* __restrict__ down, const uint32_t* __restrict__ len, uint64_t n_seeds,
+                                                            uint64_t cap, uint64_t stride, uint64_t* __restrict__ counts,
+                                                            uint64_t* __restrict__ staging, uint32_t* __restrict__ above,
+                                                            uint32_t* __restrict__ truncated) {
     const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     if (i > n_seeds) return;
     if (i == n_seeds) { counts[i] = 0; return; }
     bool tr = false;
-    counts[i] = occ_walk(v, ref[i], len[i], cap, staging + i * stride, &tr);
+    uint32_t na = 0;
+    counts[i] = occ_walk(v, head[i], up[i], down[i], len[i], cap, staging + i * stride, &tr, &na);
+    if (above) above[i] = na;
     if (tr) atomicOr(truncated, 1u);
+}
+
+// populate_seed's two halves of every seed of at least 2 * min_len bases (include/aligner/seed_finder.hpp:277-306), from the seed's
+// own list: upper_suffix = the last position found above (the seed's position if none), lower_suffix = the last position of the
+// whole list.  slot[j] = index of the seed's left half among the halves (exclusive scan of 2 * qualifies), right half at slot + 1.
+__global__ void __launch_bounds__(kBlock) k_seed_qualifies(const uint32_t* __restrict__ len, uint64_t n_seeds, uint64_t min_len, uint64_t* __restrict__ slot) {
+    const uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (j > n_seeds) return;
+    slot[j] = (j < n_seeds && (uint64_t)len[j] >= (min_len << 1)) ? 2 : 0;
+}
+
+__global__ void __launch_bounds__(kBlock) k_make_halves(const uint64_t* __restrict__ ref, const uint32_t* __restrict__ len, const uint32_t* __restrict__ qpos,
+                                                        uint64_t n_seeds, uint64_t min_len, const uint64_t* __restrict__ slot,
+                                                        const uint64_t* __restrict__ off, const uint64_t* __restrict__ occs,
+                                                        const uint32_t* __restrict__ above, uint64_t* __restrict__ h_head, uint64_t* __restrict__ h_up,
+                                                        uint64_t* __restrict__ h_down, uint32_t* __restrict__ h_len, uint32_t* __restrict__ h_qpos,
+                                                        uint64_t* __restrict__ h_parent) {
+    const uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (j >= n_seeds) return;
+    const uint64_t l = len[j];
+    if (l < (min_len << 1)) return;
+    const uint64_t a = off[j], cnt = off[j + 1] - a;
+    const uint64_t upper = occs[a + above[j]], lower = occs[a + cnt - 1];     // occs[a] is the seed itself, then the positions above
+    const uint64_t ll = l >> 1, h = slot[j];
+    h_head[h] = upper; h_up[h] = upper; h_down[h] = lower; h_len[h] = (uint32_t)ll; h_qpos[h] = qpos[j]; h_parent[h] = j;
+    const uint64_t rp = ref[j] + ll;
+    h_head[h + 1] = rp; h_up[h + 1] = rp; h_down[h + 1] = rp; h_len[h + 1] = (uint32_t)(l - ll); h_qpos[h + 1] = qpos[j] + (uint32_t)ll; h_parent[h + 1] = j;
 }
 
 __global__ void __launch_bounds__(kBlock) k_occ_pack(const uint64_t* __restrict__ staging, uint64_t stride, const uint64_t* __restrict__ off,
@@ -509,6 +545,13 @@ __global__ void __launch_bounds__(kBlock) k_occ_pack(const uint64_t* __restrict_
     const uint64_t a = off[i], cnt = off[i + 1] - a;
     const uint64_t* src = staging + i * stride;
     for (uint64_t k = lane; k < cnt; k += 32) occs[a + k] = src[k];
+}
+
+// Offsets of a chunk whose reads all have the same length: computed on the device instead of crossing the host link (8 bytes per
+// read are 5 % of what a batch of 150-base reads sends).
+__global__ void k_uniform_offsets(uint64_t* __restrict__ offs, uint64_t base, uint32_t len, uint32_t n1) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n1) offs[i] = base + (uint64_t)i * len;
 }
 
 __global__ void k_widen_counts(const uint32_t* __restrict__ c, uint64_t* __restrict__ out, uint32_t n) {
@@ -683,6 +726,7 @@ struct Replica {
     DevBuf rows, row_pos, crun_row, slots, nodes, pool, sym, counters;
     DevBuf phi, phi_inv, phi_dir, phi_inv_dir;            // `moni align` indexes only
     DevBuf occ_ref, occ_len, occ_off, occ_out, occ_flag, occ_cub, occ_stage;   // moni_gpu_seed_occs scratch
+    DevBuf pop_qpos, pop_above, pop_slot, pop_head, pop_up, pop_down, pop_parent, pop_len, pop_hq, pop_hoff, pop_hout;   // moni_gpu_populate_seeds scratch
     DevBuf shard_off, shard_pos, shard_len, shard_ref;   // multi-GPU mems: a shard's records wait here for their global offset
     ImageView view;
     std::mutex mu;
@@ -694,6 +738,7 @@ struct Replica {
         sym.release(); counters.release();
         phi.release(); phi_inv.release(); phi_dir.release(); phi_inv_dir.release();
         occ_ref.release(); occ_len.release(); occ_off.release(); occ_out.release(); occ_flag.release(); occ_cub.release(); occ_stage.release();
+        for (DevBuf* b : {&pop_qpos, &pop_above, &pop_slot, &pop_head, &pop_up, &pop_down, &pop_parent, &pop_len, &pop_hq, &pop_hoff, &pop_hout}) b->release();
         shard_off.release(); shard_pos.release(); shard_len.release(); shard_ref.release();
         for (Lane& L : lanes) {
             L.scratch.release();
@@ -1028,7 +1073,12 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
         cudaEvent_t* e = L.events.data() + ev_at[c];
         CK(cudaEventRecord(e[0], L.stream));
         if (p.bases) CK(cudaMemcpyAsync(S.seqs.p, seqs + p.base, p.bases, cudaMemcpyHostToDevice, L.stream));
-        CK(cudaMemcpyAsync(S.offs.p, offsets + p.first, (p.n + 1) * 8, cudaMemcpyHostToDevice, L.stream));
+        if (p.uniform_len) {
+            k_uniform_offsets<<<(unsigned)((p.n + 1 + 255) / 256), 256, 0, L.stream>>>(S.offs.as<uint64_t>(), p.base, p.uniform_len, (uint32_t)(p.n + 1));
+            g_launches++;
+        } else {
+            CK(cudaMemcpyAsync(S.offs.p, offsets + p.first, (p.n + 1) * 8, cudaMemcpyHostToDevice, L.stream));
+        }
         CK(cudaEventRecord(e[1], L.stream));
         launch_prepare(S, p, L.stream);
         launch_pass1(R, S, p, L.stream);
@@ -1585,12 +1635,68 @@ int moni_gpu_seeds(moni_gpu_index* idx, const char* seqs, const uint64_t* offset
     return mems_impl(idx, kModeSeeds, seqs, offsets, n_reads, rec_out(seed_offsets, seed_qpos, 4, seed_len, 4, seed_ref, 8, seed_capacity, 12, ml));
 }
 
-int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
-                       uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity, int* truncated) {
-    if (!idx || !occ_offsets || (n_seeds && (!seed_ref || !seed_len)) || n_seeds >= 0x7FFFFFF0ull) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
-    if (truncated) *truncated = 0;
-    if (n_seeds == 0) { occ_offsets[0] = 0; return 0; }
-    if (!occs && occ_capacity) { g_err = "null output"; return MONI_GPU_EINVAL; }
+namespace {
+
+// One enumeration job on a replica's first stream: lists for n seeds given on the device.  phase 1 walks (counting, or staging when
+// the cap bounds the lists), scans the counts into offsets, sends the offsets home and returns the total; phase 2 produces the
+// packed lists in `lists` (reserved by the caller once the total is known to fit its capacity).
+struct OccJob {
+    const uint64_t *head = nullptr, *up = nullptr, *down = nullptr;
+    const uint32_t* len = nullptr;
+    uint64_t n = 0, cap = 0, stride = 0;
+    DevBuf *off = nullptr, *stage = nullptr, *cub = nullptr, *flag = nullptr, *above = nullptr, *lists = nullptr;
+};
+
+uint64_t occ_phase1(Replica& R, cudaStream_t st, OccJob& J, uint64_t* h_off, bool* truncated) {
+    J.off->reserve((J.n + 1) * 8);
+    J.flag->reserve(16);
+    if (J.above) J.above->reserve((J.n + 1) * 4);
+    CK(cudaMemsetAsync(J.flag->p, 0, 4, st));
+    const unsigned blocks = (unsigned)((J.n + 1 + kBlock - 1) / kBlock);
+    // staged single walk when 2 cap + 1 positions per seed fit a bounded share of the free HBM; else count, then fill
+    J.stride = 0;
+    if (J.cap <= 4096) {
+        const uint64_t want = (2 * J.cap + 1) * 8 * J.n;
+        size_t free_b = 0, total_b = 0;
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        if (want <= J.stage->cap || want <= std::min<uint64_t>((uint64_t)free_b / 4, 8ull << 30)) J.stride = 2 * J.cap + 1;
+    }
+    uint32_t* ab = J.above ? J.above->as<uint32_t>() : nullptr;
+    if (J.stride) {
+        J.stage->reserve(J.stride * 8 * J.n);
+        k_occ_walk_staged<<<blocks, kBlock, 0, st>>>(R.view, J.head, J.up, J.down, J.len, J.n, J.cap, J.stride, J.off->as<uint64_t>(),
+                                                     J.stage->as<uint64_t>(), ab, J.flag->as<uint32_t>());
+    } else {
+        k_occ_count<<<blocks, kBlock, 0, st>>>(R.view, J.head, J.up, J.down, J.len, J.n, J.cap, J.off->as<uint64_t>(), ab, J.flag->as<uint32_t>());
+    }
+    g_launches++;
+    size_t tmp = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, J.off->as<uint64_t>(), J.off->as<uint64_t>(), (int)(J.n + 1), st));
+    J.cub->reserve(tmp);
+    CK(cub::DeviceScan::ExclusiveSum(J.cub->p, tmp, J.off->as<uint64_t>(), J.off->as<uint64_t>(), (int)(J.n + 1), st));
+    g_launches += 2;
+    uint32_t flag = 0;
+    CK(cudaMemcpyAsync(h_off, J.off->p, (J.n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&flag, J.flag->p, 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (truncated && flag) *truncated = true;
+    return h_off[J.n];
+}
+
+void occ_phase2(Replica& R, cudaStream_t st, OccJob& J, uint64_t total) {
+    J.lists->reserve(total * 8 + 16);
+    if (J.stride)
+        k_occ_pack<<<(unsigned)((J.n * 32 + kBlock - 1) / kBlock), kBlock, 0, st>>>(J.stage->as<uint64_t>(), J.stride, J.off->as<uint64_t>(), J.n,
+                                                                                    J.lists->as<uint64_t>());
+    else
+        k_occ_fill<<<(unsigned)((J.n + kBlock - 1) / kBlock), kBlock, 0, st>>>(R.view, J.head, J.up, J.down, J.len, J.n, J.cap, J.off->as<uint64_t>(),
+                                                                               J.lists->as<uint64_t>());
+    g_launches++;
+    CK(cudaGetLastError());
+}
+
+int check_occ_args(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds, uint64_t max_per_direction) {
+    if (n_seeds >= 0x7FFFFFF0ull) { g_err = "too many seeds"; return MONI_GPU_EINVAL; }
     // the reference asserts len > 0 in find_MEM_above / find_MEM_below (include/aligner/seed_finder.hpp:171,203): a zero-length seed
     // would "match" every suffix and walk the whole suffix array; a cap beyond 2^32 positions per direction cannot be stored anyway
     if (max_per_direction > (1ull << 32)) { g_err = "max_per_direction must be at most 2^32"; return MONI_GPU_EINVAL; }
@@ -1598,6 +1704,19 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
         if (seed_len[i] == 0) { g_err = "seed " + std::to_string(i) + " has length 0 (the reference requires len > 0)"; return MONI_GPU_EINVAL; }
     if (idx->hdr.phi_n == 0) { g_err = "this index has no Phi structures: load <prefix>.thrbv.full.ms (the `moni align` index)"; return MONI_GPU_EINVAL; }
     if (!(idx->hdr.root_ref & kLeafBit)) { g_err = "occurrence enumeration needs the text in HBM (leaf_len = 0 / text_budget)"; return MONI_GPU_EINVAL; }
+    (void)seed_ref;
+    return 0;
+}
+
+}  // namespace
+
+int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, uint64_t n_seeds,
+                       uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity, int* truncated) {
+    if (!idx || !occ_offsets || (n_seeds && (!seed_ref || !seed_len))) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
+    if (truncated) *truncated = 0;
+    if (n_seeds == 0) { occ_offsets[0] = 0; return 0; }
+    if (!occs && occ_capacity) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    if (const int rc = check_occ_args(idx, seed_ref, seed_len, n_seeds, max_per_direction)) return rc;
     return guarded([&]() -> int {
         Replica& R = *idx->reps[0];
         std::lock_guard<std::mutex> lock(R.mu);
@@ -1610,55 +1729,24 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
         CK(cudaEventRecord(e[0], st));
         R.occ_ref.reserve(n_seeds * 8);
         R.occ_len.reserve(n_seeds * 4);
-        R.occ_off.reserve((n_seeds + 1) * 8);
-        R.occ_flag.reserve(16);
         CK(cudaMemcpyAsync(R.occ_ref.p, seed_ref, n_seeds * 8, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(R.occ_len.p, seed_len, n_seeds * 4, cudaMemcpyHostToDevice, st));
-        CK(cudaMemsetAsync(R.occ_flag.p, 0, 4, st));
         CK(cudaEventRecord(e[1], st));
-        const unsigned blocks = (unsigned)((n_seeds + 1 + kBlock - 1) / kBlock);
-        // staged single walk when 2 cap + 1 positions per seed fit a bounded share of the free HBM; else count, then fill
-        uint64_t stride = 0;
-        if (max_per_direction <= 4096) {
-            const uint64_t want = (2 * max_per_direction + 1) * 8 * n_seeds;
-            size_t free_b = 0, total_b = 0;
-            CK(cudaMemGetInfo(&free_b, &total_b));
-            if (want <= R.occ_stage.cap || want <= std::min<uint64_t>((uint64_t)free_b / 4, 8ull << 30)) stride = 2 * max_per_direction + 1;
-        }
-        if (stride) {
-            R.occ_stage.reserve(stride * 8 * n_seeds);
-            k_occ_walk_staged<<<blocks, kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds, max_per_direction,
-                                                         stride, R.occ_off.as<uint64_t>(), R.occ_stage.as<uint64_t>(), R.occ_flag.as<uint32_t>());
-        } else {
-            k_occ_count<<<blocks, kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds, max_per_direction,
-                                                   R.occ_off.as<uint64_t>(), R.occ_flag.as<uint32_t>());
-        }
-        g_launches++;
-        size_t tmp = 0;
-        CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, R.occ_off.as<uint64_t>(), R.occ_off.as<uint64_t>(), (int)(n_seeds + 1), st));
-        R.occ_cub.reserve(tmp);
-        CK(cub::DeviceScan::ExclusiveSum(R.occ_cub.p, tmp, R.occ_off.as<uint64_t>(), R.occ_off.as<uint64_t>(), (int)(n_seeds + 1), st));
-        g_launches += 2;
+        OccJob J;
+        J.head = J.up = J.down = R.occ_ref.as<uint64_t>();
+        J.len = R.occ_len.as<uint32_t>();
+        J.n = n_seeds;
+        J.cap = max_per_direction;
+        J.off = &R.occ_off; J.stage = &R.occ_stage; J.cub = &R.occ_cub; J.flag = &R.occ_flag; J.lists = &R.occ_out;
+        bool tr = false;
+        const uint64_t total = occ_phase1(R, st, J, occ_offsets, &tr);
         CK(cudaEventRecord(e[2], st));
-        uint32_t flag = 0;
-        CK(cudaMemcpyAsync(occ_offsets, R.occ_off.p, (n_seeds + 1) * 8, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(&flag, R.occ_flag.p, 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        if (truncated) *truncated = flag ? 1 : 0;
-        const uint64_t total = occ_offsets[n_seeds];
+        if (truncated) *truncated = tr ? 1 : 0;
         if (total > occ_capacity) {
             g_err = "occ_capacity too small: " + std::to_string(total) + " positions needed";
             return MONI_GPU_ENOMEM;
         }
-        R.occ_out.reserve(total * 8 + 16);
-        if (stride)
-            k_occ_pack<<<(unsigned)((n_seeds * 32 + kBlock - 1) / kBlock), kBlock, 0, st>>>(R.occ_stage.as<uint64_t>(), stride, R.occ_off.as<uint64_t>(),
-                                                                                         n_seeds, R.occ_out.as<uint64_t>());
-        else
-            k_occ_fill<<<(unsigned)((n_seeds + kBlock - 1) / kBlock), kBlock, 0, st>>>(R.view, R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), n_seeds,
-                                                                                   max_per_direction, R.occ_off.as<uint64_t>(), R.occ_out.as<uint64_t>());
-        g_launches++;
-        CK(cudaGetLastError());
+        occ_phase2(R, st, J, total);
         CK(cudaEventRecord(e[3], st));
         CK(cudaMemcpyAsync(occs, R.occ_out.p, total * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(e[4], st));
@@ -1666,6 +1754,106 @@ int moni_gpu_seed_occs(moni_gpu_index* idx, const uint64_t* seed_ref, const uint
         // moni_gpu_timing: t[0] seeds in, t[1] count walk + scan, t[2] fill walk (after the offsets went home), t[4] positions out
         R.t[0] = ev_ms(e[0], e[1]); R.t[1] = ev_ms(e[1], e[2]); R.t[2] = ev_ms(e[2], e[3]); R.t[3] = 0; R.t[4] = ev_ms(e[3], e[4]);
         R.t[5] = ev_ms(e[0], e[4]);
+        for (int k = 0; k < 6; ++k) idx->t[k] = R.t[k];
+        return 0;
+    });
+}
+
+int moni_gpu_populate_seeds(moni_gpu_index* idx, const uint64_t* seed_ref, const uint32_t* seed_len, const uint32_t* seed_qpos, uint64_t n_seeds,
+                            uint64_t min_len, uint64_t max_per_direction, uint64_t* occ_offsets, uint64_t* occs, uint64_t occ_capacity,
+                            uint64_t* n_halves, uint64_t* half_parent, uint64_t* half_ref, uint32_t* half_len, uint32_t* half_qpos,
+                            uint64_t* half_occ_offsets, uint64_t* half_occs, uint64_t half_occ_capacity, int* truncated) {
+    if (!idx || !occ_offsets || !n_halves || !half_occ_offsets || (n_seeds && (!seed_ref || !seed_len || !seed_qpos))) { g_err = "bad arguments"; return MONI_GPU_EINVAL; }
+    if (truncated) *truncated = 0;
+    *n_halves = 0;
+    half_occ_offsets[0] = 0;
+    if (n_seeds == 0) { occ_offsets[0] = 0; return 0; }
+    if ((!occs && occ_capacity) || (!half_occs && half_occ_capacity)) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    if (const int rc = check_occ_args(idx, seed_ref, seed_len, n_seeds, max_per_direction)) return rc;
+    // a half of length len >> 1 exists only for len >= 2 * min_len; with min_len == 0 a one-base seed would get a left half of length 0
+    uint64_t want_halves = 0;
+    for (uint64_t i = 0; i < n_seeds; ++i)
+        if ((uint64_t)seed_len[i] >= (min_len << 1)) {
+            if (seed_len[i] < 2) { g_err = "seed " + std::to_string(i) + " is too short to be split (min_len must be at least 1)"; return MONI_GPU_EINVAL; }
+            want_halves += 2;
+        }
+    if (want_halves && (!half_parent || !half_ref || !half_len || !half_qpos)) { g_err = "null output"; return MONI_GPU_EINVAL; }
+    return guarded([&]() -> int {
+        Replica& R = *idx->reps[0];
+        std::lock_guard<std::mutex> lock(R.mu);
+        CK(cudaSetDevice(R.dev));
+        cudaStream_t st = R.stream();
+        Lane& L0 = R.lanes[0];
+        L0.used = 0;
+        L0.take();
+        cudaEvent_t* e = L0.events.data();      // 0 start, 1 lists of the seeds on the device, 2 lists of the halves on the device, 3 home
+        CK(cudaEventRecord(e[0], st));
+        R.occ_ref.reserve(n_seeds * 8);
+        R.occ_len.reserve(n_seeds * 4);
+        R.pop_qpos.reserve(n_seeds * 4);
+        CK(cudaMemcpyAsync(R.occ_ref.p, seed_ref, n_seeds * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(R.occ_len.p, seed_len, n_seeds * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(R.pop_qpos.p, seed_qpos, n_seeds * 4, cudaMemcpyHostToDevice, st));
+        OccJob J;
+        J.head = J.up = J.down = R.occ_ref.as<uint64_t>();
+        J.len = R.occ_len.as<uint32_t>();
+        J.n = n_seeds;
+        J.cap = max_per_direction;
+        J.off = &R.occ_off; J.stage = &R.occ_stage; J.cub = &R.occ_cub; J.flag = &R.occ_flag; J.lists = &R.occ_out; J.above = &R.pop_above;
+        bool tr = false;
+        const uint64_t total = occ_phase1(R, st, J, occ_offsets, &tr);
+        if (total > occ_capacity) {
+            g_err = "occ_capacity too small: " + std::to_string(total) + " positions needed";
+            return MONI_GPU_ENOMEM;
+        }
+        occ_phase2(R, st, J, total);
+        CK(cudaMemcpyAsync(occs, R.occ_out.p, total * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(e[1], st));
+        *n_halves = want_halves;
+        if (want_halves) {
+            const uint64_t nh = want_halves;
+            R.pop_slot.reserve((n_seeds + 1) * 8);
+            for (DevBuf* b : {&R.pop_head, &R.pop_up, &R.pop_down, &R.pop_parent}) b->reserve(nh * 8);
+            R.pop_len.reserve(nh * 4);
+            R.pop_hq.reserve(nh * 4);
+            const unsigned blocks = (unsigned)((n_seeds + 1 + kBlock - 1) / kBlock);
+            k_seed_qualifies<<<blocks, kBlock, 0, st>>>(R.occ_len.as<uint32_t>(), n_seeds, min_len, R.pop_slot.as<uint64_t>());
+            size_t tmp = 0;
+            CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, R.pop_slot.as<uint64_t>(), R.pop_slot.as<uint64_t>(), (int)(n_seeds + 1), st));
+            R.occ_cub.reserve(tmp);
+            CK(cub::DeviceScan::ExclusiveSum(R.occ_cub.p, tmp, R.pop_slot.as<uint64_t>(), R.pop_slot.as<uint64_t>(), (int)(n_seeds + 1), st));
+            k_make_halves<<<blocks, kBlock, 0, st>>>(R.occ_ref.as<uint64_t>(), R.occ_len.as<uint32_t>(), R.pop_qpos.as<uint32_t>(), n_seeds, min_len,
+                                                     R.pop_slot.as<uint64_t>(), R.occ_off.as<uint64_t>(), R.occ_out.as<uint64_t>(),
+                                                     R.pop_above.as<uint32_t>(), R.pop_head.as<uint64_t>(), R.pop_up.as<uint64_t>(),
+                                                     R.pop_down.as<uint64_t>(), R.pop_len.as<uint32_t>(), R.pop_hq.as<uint32_t>(),
+                                                     R.pop_parent.as<uint64_t>());
+            g_launches += 4;
+            CK(cudaGetLastError());
+            OccJob H;
+            H.head = R.pop_head.as<uint64_t>(); H.up = R.pop_up.as<uint64_t>(); H.down = R.pop_down.as<uint64_t>();
+            H.len = R.pop_len.as<uint32_t>();
+            H.n = nh;
+            H.cap = max_per_direction;
+            H.off = &R.pop_hoff; H.stage = &R.occ_stage; H.cub = &R.occ_cub; H.flag = &R.occ_flag; H.lists = &R.pop_hout;
+            const uint64_t htotal = occ_phase1(R, st, H, half_occ_offsets, &tr);
+            if (htotal > half_occ_capacity) {
+                g_err = "half_occ_capacity too small: " + std::to_string(htotal) + " positions needed";
+                return MONI_GPU_ENOMEM;
+            }
+            occ_phase2(R, st, H, htotal);
+            CK(cudaEventRecord(e[2], st));
+            CK(cudaMemcpyAsync(half_parent, R.pop_parent.p, nh * 8, cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpyAsync(half_ref, R.pop_head.p, nh * 8, cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpyAsync(half_len, R.pop_len.p, nh * 4, cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpyAsync(half_qpos, R.pop_hq.p, nh * 4, cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpyAsync(half_occs, R.pop_hout.p, htotal * 8, cudaMemcpyDeviceToHost, st));
+        } else {
+            CK(cudaEventRecord(e[2], st));
+        }
+        CK(cudaEventRecord(e[3], st));
+        CK(cudaStreamSynchronize(st));
+        if (truncated) *truncated = tr ? 1 : 0;
+        R.t[0] = 0; R.t[1] = ev_ms(e[0], e[1]); R.t[2] = ev_ms(e[1], e[2]); R.t[3] = 0; R.t[4] = ev_ms(e[2], e[3]); R.t[5] = ev_ms(e[0], e[3]);
         for (int k = 0; k < 6; ++k) idx->t[k] = R.t[k];
         return 0;
     });

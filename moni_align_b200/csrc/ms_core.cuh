@@ -309,10 +309,10 @@ struct RunRead {
 // SEEDS: the record rule is seed_finder::find_mems' (include/aligner/seed_finder.hpp:148): l >= pl and n_Ns < l and
 // l >= min_len, where n_Ns counts the consecutive 'N' at the end of the characters matched so far (:139-143; it is only
 // touched when a character is compared and matches), which can only hold at a restart; rec_ref[k] receives pointers[i].
-// TEXT: the whole text is one literal block in HBM (ImageHeader::root_ref is a leaf): no descent, the compare address is
-// pool + pos + l, and the line the NEXT restart will read is requested (prefetch.global.L2) while this one is compared -- its
-// address is the next pointer plus the length this restart starts from, minus the distance to the next restart, which is
-// within a few bytes of where that compare will really start -- so a lane keeps two random text lines in flight.
+// TEXT: the whole text is one literal block in HBM (ImageHeader::root_ref is a leaf): no descent and no descent state, the
+// compare address is pool + pos + l.  (Requesting the text line of the NEXT restart with prefetch.global.L2 while this one is
+// compared was measured and dropped: DRAM reads doubled, 17.3 -> 38.6 GB per 2 M reads, and the kernel went from 5.0 to 8.7 ms,
+// profiles/r02_c_launches.csv -- the prefetched line is fetched again by the demand load.)
 // Call while st.mode != FINISHED.
 template <bool SEEDS = false, bool TEXT = false>
 MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, RunState& st, Counters* ctr, uint32_t min_len = 0) {
@@ -348,13 +348,6 @@ MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, R
         }
         st.i = i;
         if (ctr) ctr->restarts++;
-#if defined(__CUDA_ARCH__)
-        if (TEXT && st.k + 1 < R.cnt) {
-            const uint32_t d = st.bits ? ctz32(st.bits) + 32u * st.w - i : 1u;      // distance to the next restart when this word shows it
-            const uint64_t at = st.nxt + (st.l > d ? st.l - d : 0u);
-            if (at < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(text + at));
-        }
-#endif
         done = true;
         if (i + st.l < m && st.pos + st.l < N) {                  // u64 add wraps exactly as in the reference
             done = false;
@@ -534,32 +527,41 @@ MONI_HD bool lce_at_least(const ImageView& v, uint64_t a, uint64_t b, uint64_t l
 
 // seed_finder::find_MEM_occs without seed filtering (:239-251): the seed position, then find_MEM_above (:169-197: Phi steps
 // while the LCE with the previous suffix reaches len; get_prev_occ_with_lcp :359-370), then find_MEM_below (:201-229, Phi^-1,
-// get_next_occ_with_lcp :346-357).  Writes at most `cap` positions per direction to out (if not null; out[0] = pos) and
-// returns the number of positions (1 + above + below); *truncated is set when a direction stopped at the cap.
-MONI_HD uint64_t occ_walk(const ImageView& v, uint64_t pos, uint64_t len, uint64_t cap, uint64_t* out, bool* truncated) {
+// get_next_occ_with_lcp :346-357).  Generalised to what populate_seed (:258-309) asks of the left half of a split MEM: the
+// list starts with `head`, the walk upwards starts at `up` and the walk downwards at `down` (a plain seed has head = up = down
+// = its position).  Writes at most `cap` positions per direction to out (if not null; out[0] = head) and returns the number of
+// positions (1 + above + below); *truncated is set when a direction stopped at the cap; *n_above (if not null) receives the
+// number found above.
+MONI_HD uint64_t occ_walk(const ImageView& v, uint64_t head, uint64_t up, uint64_t down, uint64_t len, uint64_t cap, uint64_t* out,
+                          bool* truncated, uint32_t* n_above = nullptr) {
     const uint64_t N = v.hdr.text_len, n = v.hdr.n;
     uint64_t k = 0;
-    if (out) out[k] = pos;
+    if (out) out[k] = head;
     ++k;
-    if (pos >= n) return k;          // not a text position (a wrapped pointer): the reference's Phi is undefined there
+    if (n_above) *n_above = 0;
     for (int dir = 0; dir < 2; ++dir) {
         const PhiEntry* tab = dir == 0 ? v.phi : v.phi_inv;
         const uint32_t* bdir = dir == 0 ? v.phi_dir : v.phi_inv_dir;
         const uint64_t stop_at = dir == 0 ? v.hdr.first_run_sample : v.hdr.init_sample;   // get_first / get_last_run_sample
-        uint64_t curr = pos, taken = 0;
-        for (;;) {
-            if (curr == stop_at) break;                                   // the reference returns lcp 0 here
-            const uint64_t next = phi_step(tab, bdir, v.hdr.phi_shift, v.hdr.phi_n, n, curr);
-            if (!((N - curr) >= len && (N - next) >= len)) break;         // lcp stays 0 (u64 arithmetic as in the reference)
-            if (!lce_at_least(v, curr, next, len)) break;
-            if (taken == cap) { if (truncated) *truncated = true; break; }
-            if (out) out[k] = next;
-            ++k;
-            ++taken;
-            curr = next;
-        }
+        uint64_t curr = dir == 0 ? up : down, taken = 0;
+        if (curr < n)                    // else not a text position (a wrapped pointer): the reference's Phi is undefined there
+            for (;;) {
+                if (curr == stop_at) break;                                   // the reference returns lcp 0 here
+                const uint64_t next = phi_step(tab, bdir, v.hdr.phi_shift, v.hdr.phi_n, n, curr);
+                if (!((N - curr) >= len && (N - next) >= len)) break;         // lcp stays 0 (u64 arithmetic as in the reference)
+                if (!lce_at_least(v, curr, next, len)) break;
+                if (taken == cap) { if (truncated) *truncated = true; break; }
+                if (out) out[k] = next;
+                ++k;
+                ++taken;
+                curr = next;
+            }
+        if (dir == 0 && n_above) *n_above = (uint32_t)taken;
     }
     return k;
+}
+MONI_HD uint64_t occ_walk(const ImageView& v, uint64_t pos, uint64_t len, uint64_t cap, uint64_t* out, bool* truncated) {
+    return occ_walk(v, pos, pos, pos, len, cap, out, truncated, nullptr);
 }
 
 }  // namespace moni

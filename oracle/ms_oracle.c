@@ -319,15 +319,17 @@ static int lce_reaches(const oracle_index* ix, u64 a, u64 b, u64 len) {
     return 1;
 }
 
-/* find_MEM_occs: occs = [pos] + above + below.  Returns the count; writes at most cap entries. */
-u64 oracle_find_mem_occs(oracle_index* ix, u64 pos, u64 len, u64* occs, u64 cap) {
+/* find_MEM_occs: occs = [pos] + above + below.  Returns the count; writes at most cap entries.
+ * Generalised to what populate_seed asks of the left half of a split MEM (seed_finder.hpp:277-291): the list starts with `head`,
+ * find_MEM_above starts at `up`, find_MEM_below at `down`; *n_above (if not NULL) receives the number found above. */
+u64 oracle_find_mem_occs3(oracle_index* ix, u64 head, u64 up, u64 down, u64 len, u64* occs, u64 cap, u64* n_above) {
     const u64 n = ix->text_len;                                          /* seed_finder::n */
     const u64 first_run_sample = (ix->samples_start[0] + 1) % ix->n;
     const u64 last_run_sample = (ix->samples_last[ix->R - 1] + 1) % ix->n;
     u64 k = 0;
-    if (k < cap) occs[k] = pos;
+    if (k < cap) occs[k] = head;
     ++k;
-    for (u64 curr = pos;;) {                                             /* find_MEM_above */
+    for (u64 curr = up;;) {                                              /* find_MEM_above */
         if (curr == first_run_sample) break;
         const u64 prev = phi(ix, curr);
         u64 ok = 0;
@@ -337,7 +339,8 @@ u64 oracle_find_mem_occs(oracle_index* ix, u64 pos, u64 len, u64* occs, u64 cap)
         ++k;
         curr = prev;
     }
-    for (u64 curr = pos;;) {                                             /* find_MEM_below */
+    if (n_above) *n_above = k - 1;
+    for (u64 curr = down;;) {                                            /* find_MEM_below */
         if (curr == last_run_sample) break;
         const u64 next = phi_inv(ix, curr);
         u64 ok = 0;
@@ -348,4 +351,8 @@ u64 oracle_find_mem_occs(oracle_index* ix, u64 pos, u64 len, u64* occs, u64 cap)
         curr = next;
     }
     return k;
+}
+
+u64 oracle_find_mem_occs(oracle_index* ix, u64 pos, u64 len, u64* occs, u64 cap) {
+    return oracle_find_mem_occs3(ix, pos, pos, pos, len, occs, cap, NULL);
 }

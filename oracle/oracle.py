@@ -239,6 +239,8 @@ class OracleIndex:
         L.oracle_set_phi.argtypes = [ctypes.c_uint64, u64p, u64p, u64p, u64p]
         L.oracle_find_mem_occs.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, u64p, ctypes.c_uint64]
         L.oracle_find_mem_occs.restype = ctypes.c_uint64
+        L.oracle_find_mem_occs3.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64, u64p, ctypes.c_uint64, u64p]
+        L.oracle_find_mem_occs3.restype = ctypes.c_uint64
         import os as _os
         ext = next((e for e in (".thrbv.ms", ".thrbv.full.ms", ".thrbv.full.lcp.ms") if _os.path.exists(prefix + e)), ".thrbv.ms")
         self.bwt = read_thrbv_ms(prefix + ext, full=ext != ".thrbv.ms")
@@ -316,13 +318,7 @@ class OracleIndex:
 
     def mem_occs(self, seed_ref, seed_len):
         """(occ_offsets, occs): seed_finder::find_MEM_occs (unfiltered) for every seed; needs the `moni align` index."""
-        b = self.bwt
-        if "pred" not in b:
-            raise ValueError("the oracle index was not loaded from a .thrbv.full.ms file")
-        k = self._keep
-        for name in ("pred", "pred_to_run", "pred_start", "pred_start_to_run"):
-            k[name] = np.ascontiguousarray(b[name], dtype=np.uint64)
-        self.lib.oracle_set_phi(b["R"], *[_p(k[nm], ctypes.c_uint64) for nm in ("pred", "pred_to_run", "pred_start", "pred_start_to_run")])
+        self._set_phi()
         off, out = [0], []
         buf = np.zeros(1 << 16, dtype=np.uint64)
         for p, l in zip(seed_ref, seed_len):
@@ -333,6 +329,52 @@ class OracleIndex:
             out.append(buf[:c].copy())
             off.append(off[-1] + c)
         return np.array(off, dtype=np.uint64), (np.concatenate(out) if out else np.zeros(0, dtype=np.uint64))
+
+    def _set_phi(self):
+        b = self.bwt
+        if "pred" not in b:
+            raise ValueError("the oracle index was not loaded from a .thrbv.full.ms file")
+        k = self._keep
+        for name in ("pred", "pred_to_run", "pred_start", "pred_start_to_run"):
+            k[name] = np.ascontiguousarray(b[name], dtype=np.uint64)
+        self.lib.oracle_set_phi(b["R"], *[_p(k[nm], ctypes.c_uint64) for nm in ("pred", "pred_to_run", "pred_start", "pred_start_to_run")])
+
+    def _occs3(self, head, up, down, ln):
+        buf = np.zeros(1 << 16, dtype=np.uint64)
+        na = ctypes.c_uint64(0)
+        c = int(self.lib.oracle_find_mem_occs3(self.h, int(head), int(up), int(down), int(ln), _p(buf, ctypes.c_uint64), buf.shape[0], ctypes.byref(na)))
+        if c > buf.shape[0]:
+            buf = np.zeros(c, dtype=np.uint64)
+            c = int(self.lib.oracle_find_mem_occs3(self.h, int(head), int(up), int(down), int(ln), _p(buf, ctypes.c_uint64), buf.shape[0], ctypes.byref(na)))
+        return buf[:c].copy(), int(na.value)
+
+    def populate_seeds(self, seed_offsets, seed_ref, seed_len, seed_qpos, min_len: int):
+        """seed_finder::populate_seeds with seed filtering off (include/aligner/seed_finder.hpp:311-319 -> populate_seed :258-309), per read:
+        every MEM gets its find_MEM_occs list; a MEM with len >= 2 * min_len appends two more seeds to the read's vector -- the left
+        half (upper_suffix, len >> 1, idx) whose list is upper_suffix + find_MEM_above(upper_suffix) + find_MEM_below(lower_suffix) at
+        the shorter length (:277-291; upper / lower_suffix = occs.back() after the walk above / below, :272-275), and the right half
+        (pos + ll, len - ll, idx + ll) with its own find_MEM_occs (:293-301).  Returns (offsets, ref, len, qpos, occ_offsets, occs)
+        of the final vectors, in the reference's order (the read's MEMs, then the halves in MEM order)."""
+        self._set_phi()
+        off, ref, ln, qp, ooff, occs = [0], [], [], [], [0], []
+        for r in range(len(seed_offsets) - 1):
+            a, b = int(seed_offsets[r]), int(seed_offsets[r + 1])
+            tail = []
+            for t in range(a, b):
+                pos, l, i = int(seed_ref[t]), int(seed_len[t]), int(seed_qpos[t])
+                lst, na = self._occs3(pos, pos, pos, l)
+                ref.append(pos); ln.append(l); qp.append(i); occs.append(lst); ooff.append(ooff[-1] + len(lst))
+                if l >= (min_len << 1):
+                    upper, lower = int(lst[na]), int(lst[-1])
+                    ll = l >> 1
+                    tail.append((upper, ll, i, self._occs3(upper, upper, lower, ll)[0]))
+                    tail.append((pos + ll, l - ll, i + ll, self._occs3(pos + ll, pos + ll, pos + ll, l - ll)[0]))
+            for p_, l_, i_, lst in tail:
+                ref.append(p_); ln.append(l_); qp.append(i_); occs.append(lst); ooff.append(ooff[-1] + len(lst))
+            off.append(len(ref))
+        u = np.uint64
+        return (np.array(off, dtype=u), np.array(ref, dtype=u), np.array(ln, dtype=u), np.array(qp, dtype=u), np.array(ooff, dtype=u),
+                np.concatenate(occs) if occs else np.zeros(0, dtype=u))
 
     def counters(self, reset: bool = True) -> dict:
         out = np.zeros(5, dtype=np.uint64)

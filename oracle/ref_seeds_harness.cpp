@@ -11,7 +11,13 @@
 // seed_finder::find_MEM_occs (:239-251: the seed's own position, then Phi steps upwards and Phi^-1 steps downwards while
 // the bounded LCE reaches the seed length; no seed filtering):   (pos,len,idx:occ,occ,...)
 //
-// usage: ref_seeds <index-prefix> <reads.fq> <min_len> <out.seeds> [occs]
+// With "pop" instead, the read's MEMs go through seed_finder::populate_seeds (:311-319 -> populate_seed :258-309, seed filtering off):
+// every MEM gets its occurrence list and a MEM of at least 2 * min_len bases appends its two halves to the vector -- the left
+// half (upper_suffix, len / 2, idx) whose list is upper_suffix, the suffixes above it and the suffixes below lower_suffix at the
+// shorter length, and the right half (pos + len / 2, len - len / 2, idx + len / 2) with its own find_MEM_occs list.  The whole
+// vector is printed in its final order, same token format.
+//
+// usage: ref_seeds <index-prefix> <reads.fq> <min_len> <out.seeds> [occs|pop]
 //   needs <prefix>.thrbv.full.ms (reference rlebwt_ms_full_build -n), <prefix>.plain.slp and an (empty) <prefix>.ldx
 #include <cstdio>
 #include <cstdlib>
@@ -25,6 +31,7 @@
 int main(int argc, char** argv) {
     if (argc != 5 && argc != 6) { fprintf(stderr, "usage: ref_seeds prefix reads.fq min_len out [occs]\n"); return 2; }
     const bool with_occs = argc == 6;
+    const bool populate = argc == 6 && std::string(argv[5]) == "pop";
     const size_t min_len = (size_t)atoll(argv[3]);
 #ifdef REF_SEEDS_LCP   // the sampled-LCP index: <prefix>.thrbv.full.lcp.ms, occurrences through moni_lcp::Phi_lcp / Phi_inv_lcp
     seed_finder<plain_slp_t, moni_lcp<>> sf(argv[1], min_len, false, 5000);
@@ -39,10 +46,11 @@ int main(int argc, char** argv) {
     while (kseq_read(seq) >= 0) {
         std::vector<mem_t> mems;
         sf.find_mems(seq, mems);
+        if (populate) sf.populate_seeds(mems);
         fprintf(out, ">%s\n", seq->name.s);
         for (mem_t& m : mems) {
             if (!with_occs) { fprintf(out, "(%zu,%zu,%zu) ", m.pos, m.len, m.idx); continue; }
-            sf.find_MEM_occs(m);
+            if (!populate) sf.find_MEM_occs(m);
             fprintf(out, "(%zu,%zu,%zu:", m.pos, m.len, m.idx);
             for (size_t k = 0; k < m.occs.size(); ++k) fprintf(out, k ? ",%zu" : "%zu", m.occs[k]);
             fprintf(out, ") ");

@@ -67,6 +67,10 @@ def main():
             subprocess.run([os.path.join(BIN, "ref_seeds"), fa, os.path.join(td, case + ".fq"), "12", os.path.join(td, f"{case}.occs12"), "occs"],
                            check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
             shutil.copy(os.path.join(td, f"{case}.occs12"), HERE)
+            # seed_finder::populate_seeds (half-MEM splitting, seed filtering off) on the same MEMs
+            subprocess.run([os.path.join(BIN, "ref_seeds"), fa, os.path.join(td, case + ".fq"), "12", os.path.join(td, f"{case}.pop12"), "pop"],
+                           check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            shutil.copy(os.path.join(td, f"{case}.pop12"), HERE)
             shutil.copy(fa + ".thrbv.full.ms", HERE)
 
 

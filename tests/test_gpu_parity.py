@@ -690,3 +690,23 @@ def test_dynamic_and_static_kernels_agree(case, m, oracle_mod):
     assert np.array_equal(res[1][0][0], wp) and np.array_equal(res[1][0][1], wl)
     wm = orc.mems(flat, offs)
     assert all(np.array_equal(x, y) for x, y in zip(res[1][1], wm))
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_populate_seeds_equals_reference(case, m, oracle_mod, tmp_path):
+    """moni_gpu_seeds + moni_gpu_populate_seeds on the `moni align` index == the reference's find_mems + populate_seeds with seed
+    filtering off (tests/golden/<case>.pop12, min_len 12): every MEM's list, then the two halves of every MEM of >= 24 bases."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    ix = m.MoniIndex(full_only_prefix(case, tmp_path))
+    so, ref, qpos, ln = ix.find_mems(flat, offs, 12)
+    po, pref, pln, pq, oo, occs, trunc = ix.populate_seeds(so, ref, ln, qpos, 12)
+    assert not trunc
+    assert int(po[-1]) > ref.shape[0]
+    assert oracle_mod.format_occs(names, po, pref, pln, pq, oo, occs) == open(pre + ".pop12", "rb").read()
+    with pytest.raises(m.MoniGpuError) as e:          # a split needs min_len >= 1
+        ix.populate_seeds(so, ref, ln, qpos, 0)
+    assert e.value.code == -1
+    ix.close()

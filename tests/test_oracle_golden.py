@@ -135,3 +135,18 @@ def test_oracle_occurrences_equal_reference_find_MEM_occs(case, oracle_mod, tmp_
     oo, occs = ix.mem_occs(ref, ln)
     assert int(oo[-1]) > len(ref)            # some seeds do have further occurrences
     assert oracle_mod.format_occs(names, so, ref, ln, qpos, oo, occs) == open(pre + ".occs12", "rb").read()
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_oracle_populate_seeds_equals_reference(case, oracle_mod, tmp_path):
+    """The restatement of seed_finder::populate_seeds (half-MEM splitting, seed filtering off) == the reference's own, on its own
+    .thrbv.full.ms (tests/golden/<case>.pop12: ref_seeds ... pop, min_len 12): the read's MEMs with their lists, then the halves."""
+    from conftest import full_only_prefix
+    pre = os.path.join(GOLDEN, case)
+    ix = oracle_mod.OracleIndex(full_only_prefix(case, tmp_path))
+    names, seqs = read_fastq(pre + ".fq")
+    flat, offs = pack(seqs)
+    so, ref, qpos, ln = ix.seeds(flat, offs, 12)
+    po, pref, pln, pq, oo, occs = ix.populate_seeds(so, ref, ln, qpos, 12)
+    assert int(po[-1]) > len(ref)            # some MEMs are long enough to be split
+    assert oracle_mod.format_occs(names, po, pref, pln, pq, oo, occs) == open(pre + ".pop12", "rb").read()
