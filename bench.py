@@ -83,6 +83,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, gpu: int):
         super().__init__(daemon=True)
         self.gpu, self.stop_flag, self.rows = gpu, threading.Event(), []
+        self.paused = False
         self.nv = self.h = None
         try:
             import pynvml
@@ -104,18 +105,22 @@ class ClockSampler(threading.Thread):
                 getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20), getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)]
         return [str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits]
 
+    def sample_once(self):
+        try:
+            if self.nv is not None:
+                self.rows.append(self._nvml_row())
+            else:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+        except Exception:
+            pass
+
     def run(self):
         while not self.stop_flag.is_set():
-            try:
-                if self.nv is not None:
-                    self.rows.append(self._nvml_row())
-                else:
-                    out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                         capture_output=True, text=True, timeout=5).stdout.strip()
-                    if out:
-                        self.rows.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
+            if not self.paused:
+                self.sample_once()
             self.stop_flag.wait(0.25)
 
     def summary(self) -> dict:

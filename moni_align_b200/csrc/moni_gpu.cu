@@ -44,8 +44,8 @@ namespace {
 #define MONI_P1_MINBLOCKS 12         // resident CTAs per SM the pass-1 kernels are compiled for (register cap 65536 / (128 * 12) -> 40, no spills)
 #endif
 #ifndef MONI_P2_MINBLOCKS
-#define MONI_P2_MINBLOCKS 12         // same cap for pass 2 (its text-in-HBM variants fit 40 registers without spills)
-#endif
+#define MONI_P2_MINBLOCKS 8          // pass 2: 64 registers, 1024 threads per SM -- faster than 40 registers x 1536 threads (4.6 vs 6.2 ms
+#endif                               // per 2 M cfg3 reads, profiles/r02_h_ab_variants.json): more reads than that thrash L1
 constexpr int kBlock = 128;          // 4 warps; warps never synchronise with each other after the prologue
 constexpr int kTile = 32;            // steps staged per refill
 constexpr int kTileStride = 36;      // bytes per read in the tile: 9 words, odd -> conflict-free column reads
@@ -71,6 +71,7 @@ struct ChunkMap {
     const uint32_t* perm;      // or null
     uint64_t base;             // offs[0]: seqs on the device start here
     uint32_t n_reads;
+    uint64_t seq_bytes, flag_words, run_entries;      // extents of the chunk's buffers (MONI_BOUNDS_CHECK builds test against them)
 };
 
 // First restart entry of read r: a multiple of 4 entries (one 32-byte sector of pointers), at least m entries before the
@@ -126,12 +127,14 @@ __global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers(Image
     auto push = [&](uint64_t x) {
         stage[k & (kStage - 1)][threadIdx.x] = x;
         ++k;
+        MONI_ASSERT(k <= m && run_base(o, r) + k <= cm.run_entries);
         if ((k & (kStage - 1)) == 0) {
             ulonglong2* dst = reinterpret_cast<ulonglong2*>(out + (k - kStage));
             dst[0] = make_ulonglong2(stage[0][threadIdx.x], stage[1][threadIdx.x]);
             dst[1] = make_ulonglong2(stage[2][threadIdx.x], stage[3][threadIdx.x]);
         }
     };
+    MONI_ASSERT(flag_base(o, r) + (m + 31) / 32 <= cm.flag_words && (uint64_t)o + m + 16 <= cm.seq_bytes);
     for (uint32_t t0 = 0; t0 < mw; t0 += kTile) {
         __syncwarp();
         // refill: lane L fetches the byte of step t0 + L for each of the warp's reads in turn (one
@@ -229,12 +232,15 @@ __global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers_dyn(I
                 } else {
                     out = rptr + run_base(o, r);
                     fl = flags + flag_base(o, r);
+                    MONI_ASSERT(flag_base(o, r) + (m + 31) / 32 <= cm.flag_words && (uint64_t)o + m + 16 <= cm.seq_bytes);
+                    MONI_ASSERT(run_base(o, r) + m <= cm.run_entries);
                     scan_init(v, s);
                     acc = 0;
                     k = 0;
                     j = m - 1;
                     have = true;
                     const uint32_t blk = (o + j) & ~15u;                     // block of the read's last base, and the one below it
+                    MONI_ASSERT((uint64_t)blk + 16 <= cm.seq_bytes);
                     cp_async16(wsm + ((blk >> 4) & 1u) * kHalf, seqs + blk);
                     if (blk >= 16u && blk > o) cp_async16(wsm + (((blk >> 4) & 1u) ^ 1u) * kHalf, seqs + (blk - 16u));
                     cp_async_commit();
@@ -280,8 +286,8 @@ __global__ void __launch_bounds__(kBlock, MONI_P1_MINBLOCKS) k_ms_pointers_dyn(I
 }
 
 // Pass 2, dynamic: a lane walks the restarts of its read (ms_core.cuh runs_step) and then takes the next read.
-template <int MODE, bool COUNT, bool TEXT>
-__global__ void __launch_bounds__(kBlock, TEXT ? MONI_P2_MINBLOCKS : 8) k_ms_lengths_dyn(ImageView v, RunBufs B, ChunkMap cm, const uint32_t* __restrict__ rcnt,
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(kBlock, MONI_P2_MINBLOCKS) k_ms_lengths_dyn(ImageView v, RunBufs B, ChunkMap cm, const uint32_t* __restrict__ rcnt,
                                                                               uint32_t* __restrict__ counts, uint32_t* __restrict__ next, Counters* g,
                                                                               uint32_t min_len) {
     const uint32_t lane = threadIdx.x & 31;
@@ -314,7 +320,7 @@ __global__ void __launch_bounds__(kBlock, TEXT ? MONI_P2_MINBLOCKS : 8) k_ms_len
         }
         if (!__any_sync(0xFFFFFFFFu, have)) break;
         if (have) {
-            runs_step<MODE == 2, TEXT>(v, B, R, st, COUNT ? &c : nullptr, min_len);
+            runs_step<MODE == 2>(v, B, R, st, COUNT ? &c : nullptr, min_len);
             if (st.mode == RunState::FINISHED) {
                 if (MODE) counts[r] = st.n_mems;
                 have = false;
@@ -328,8 +334,8 @@ __global__ void __launch_bounds__(kBlock, TEXT ? MONI_P2_MINBLOCKS : 8) k_ms_len
 // MODE 0 (ms, runs): rrec[] receives (i << 32) | len of every restart, next to its pointer.  MODE 1 (mems): the read's MEM
 // records, packed (i << 32) | len, go to rec[] at the read's own offset (at most one per base) and counts[read] receives their
 // number.  MODE 2 (seeds): same with seed_finder::find_mems' rule (minimum length, N filter) and rec_ref[] = pointers[i].
-template <int MODE, bool COUNT, bool TEXT>
-__global__ void __launch_bounds__(kBlock, TEXT ? MONI_P2_MINBLOCKS : 8) k_ms_lengths(ImageView v, RunBufs B, ChunkMap cm, const uint32_t* __restrict__ rcnt,
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(kBlock, MONI_P2_MINBLOCKS) k_ms_lengths(ImageView v, RunBufs B, ChunkMap cm, const uint32_t* __restrict__ rcnt,
                                                                           uint32_t* __restrict__ counts, Counters* g, uint32_t min_len) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= cm.n_reads) return;
@@ -343,7 +349,7 @@ __global__ void __launch_bounds__(kBlock, TEXT ? MONI_P2_MINBLOCKS : 8) k_ms_len
     R.fb = (uint32_t)flag_base(R.o, r);
     R.last = (uint32_t)run_base(R.o, r) + R.cnt - 1u;
     Counters c = {0, 0, 0, 0, 0, 0, 0, 0};
-    const uint32_t k = runs_read<MODE == 2, TEXT>(v, B, R, COUNT ? &c : nullptr, min_len);
+    const uint32_t k = runs_read<MODE == 2>(v, B, R, COUNT ? &c : nullptr, min_len);
     if (MODE) counts[r] = k;
     if (COUNT) flush_counters(c, g);
 }
@@ -379,6 +385,7 @@ __global__ void __launch_bounds__(kBlock) k_ms_expand(ChunkMap cm, const uint64_
         const uint32_t kk = seen + (uint32_t)__popc(upto) - 1u;         // offset 0 is a restart, so kk >= 0 from the first word on
         const uint64_t i = i0 + lane;
         if (i < m) {
+            MONI_ASSERT(kk < cnt && at <= i);
             const uint64_t d = i - at;
             const uint64_t pv = __ldg(rp - (int64_t)kk) + d;
             const uint64_t l0 = __ldg(rr - (int64_t)kk) & 0xFFFFFFFFull;
@@ -788,6 +795,9 @@ ChunkMap chunk_map(const Scratch& S, const ChunkPlan& p) {
     cm.perm = p.ragged() ? S.perm.as<uint32_t>() : nullptr;
     cm.base = p.base;
     cm.n_reads = (uint32_t)p.n;
+    cm.seq_bytes = p.bases + 16;
+    cm.flag_words = p.flag_words();
+    cm.run_entries = p.run_entries();
     return cm;
 }
 
@@ -846,7 +856,7 @@ void launch_pass1(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     CK(cudaGetLastError());
 }
 
-template <int MODE, bool TEXT>
+template <int MODE>
 void launch_pass2_mode(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st, uint32_t min_len) {
     const ChunkMap cm = chunk_map(S, p);
     Counters* g = g_count.load() ? R.counters.as<Counters>() : nullptr;
@@ -857,23 +867,21 @@ void launch_pass2_mode(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t 
     B.rrec = MODE == 0 ? S.rrec.as<uint64_t>() : nullptr;
     B.rec = MODE ? S.rec.as<uint64_t>() : nullptr;
     B.rec_ref = MODE == 2 ? S.rec_ref.as<uint64_t>() : nullptr;
+    B.seq_bytes = p.bases + 16;
+    B.flag_words = p.flag_words();
+    B.run_entries = p.run_entries();
+    B.rec_entries = p.bases + 2;
     const uint32_t* rc = S.rcnt.as<uint32_t>();
     uint32_t* cnt = MODE ? S.counts.as<uint32_t>() : nullptr;
     if (use_dynamic(R, p)) {
         uint32_t* next = S.ctr.as<uint32_t>() + 1;        // zeroed with pass 1's counter
-        if (g) k_ms_lengths_dyn<MODE, true, TEXT><<<persistent_grid(R, k_ms_lengths_dyn<MODE, true, TEXT>, p.n), kBlock, 0, st>>>(R.view, B, cm, rc, cnt, next, g, min_len);
-        else k_ms_lengths_dyn<MODE, false, TEXT><<<persistent_grid(R, k_ms_lengths_dyn<MODE, false, TEXT>, p.n), kBlock, 0, st>>>(R.view, B, cm, rc, cnt, next, nullptr, min_len);
+        if (g) k_ms_lengths_dyn<MODE, true><<<persistent_grid(R, k_ms_lengths_dyn<MODE, true>, p.n), kBlock, 0, st>>>(R.view, B, cm, rc, cnt, next, g, min_len);
+        else k_ms_lengths_dyn<MODE, false><<<persistent_grid(R, k_ms_lengths_dyn<MODE, false>, p.n), kBlock, 0, st>>>(R.view, B, cm, rc, cnt, next, nullptr, min_len);
     } else {
         const dim3 grid((unsigned)((p.n + kBlock - 1) / kBlock));
-        if (g) k_ms_lengths<MODE, true, TEXT><<<grid, kBlock, 0, st>>>(R.view, B, cm, rc, cnt, g, min_len);
-        else k_ms_lengths<MODE, false, TEXT><<<grid, kBlock, 0, st>>>(R.view, B, cm, rc, cnt, nullptr, min_len);
+        if (g) k_ms_lengths<MODE, true><<<grid, kBlock, 0, st>>>(R.view, B, cm, rc, cnt, g, min_len);
+        else k_ms_lengths<MODE, false><<<grid, kBlock, 0, st>>>(R.view, B, cm, rc, cnt, nullptr, min_len);
     }
-}
-
-template <int MODE>
-void launch_pass2_mode(Replica& R, Scratch& S, const ChunkPlan& p, cudaStream_t st, uint32_t min_len) {
-    if (R.view.hdr.root_ref & kLeafBit) launch_pass2_mode<MODE, true>(R, S, p, st, min_len);       // the text itself is in HBM
-    else launch_pass2_mode<MODE, false>(R, S, p, st, min_len);
 }
 
 void launch_pass2(Replica& R, Scratch& S, const ChunkPlan& p, int mode, cudaStream_t st, uint32_t min_len = 0) {
@@ -957,7 +965,7 @@ struct BadBatch : std::runtime_error {
 // needs ~10^5 independent reads in flight whatever their length), or when it reaches hard_cap bases (device scratch
 // is ~24 bytes per base per lane; chunk-relative offsets are 32-bit).  Always at least one read.  Validates the
 // offsets it walks over (the only pass the host makes over them).
-constexpr uint64_t kChunkHardCap = 1ull << 29;
+constexpr uint64_t kChunkHardCap = 1ull << 30;
 
 ChunkPlan plan_chunk(const uint64_t* offsets, uint64_t a, uint64_t r1, uint64_t chunk_bases, uint64_t min_reads,
                      uint64_t hard_cap = kChunkHardCap) {
@@ -1048,6 +1056,10 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
         const uint64_t fit = (uint64_t)(share / Scratch::bytes_per_base(mode));
         hard_cap = std::max<uint64_t>(1u << 16, std::min<uint64_t>(hard_cap, fit));
     }
+    // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
+    // would cut a 1 G-base batch into two chunks and leave half the lanes (and the copy/compute overlap) unused, so the minimum
+    // shrinks until the shard makes at least two chunks per lane.
+    const uint64_t min_reads = std::min<uint64_t>(idx->opt.chunk_min_reads, std::max<uint64_t>(1024, (r1 - r0) / (2 * R.lanes.size())));
     // chunks are planned (and their offsets validated) just before they are enqueued, so the host's pass over the
     // offsets overlaps the GPU's work on earlier chunks
     std::vector<ChunkPlan> plans;
@@ -1140,7 +1152,7 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
     try {
         for (size_t c = 0; c < fronted || next_read < r1; ++c) {
             while (next_read < r1 && fronted < c + kLanes_) {
-                plans.push_back(plan_chunk(offsets, next_read, r1, std::min(idx->opt.chunk_bases, hard_cap), idx->opt.chunk_min_reads, hard_cap));
+                plans.push_back(plan_chunk(offsets, next_read, r1, std::min(idx->opt.chunk_bases, hard_cap), min_reads, hard_cap));
                 next_read += plans.back().n;
                 enqueue_front(fronted++);
             }
@@ -1770,13 +1782,12 @@ int moni_gpu_populate_seeds(moni_gpu_index* idx, const uint64_t* seed_ref, const
     if (n_seeds == 0) { occ_offsets[0] = 0; return 0; }
     if ((!occs && occ_capacity) || (!half_occs && half_occ_capacity)) { g_err = "null output"; return MONI_GPU_EINVAL; }
     if (const int rc = check_occ_args(idx, seed_ref, seed_len, n_seeds, max_per_direction)) return rc;
-    // a half of length len >> 1 exists only for len >= 2 * min_len; with min_len == 0 a one-base seed would get a left half of length 0
+    // a half of length len >> 1 exists only for len >= 2 * min_len; with min_len == 0 a one-base seed would get a left half of length 0,
+    // which the reference's walks assert against
+    if (min_len == 0) { g_err = "min_len must be at least 1"; return MONI_GPU_EINVAL; }
     uint64_t want_halves = 0;
     for (uint64_t i = 0; i < n_seeds; ++i)
-        if ((uint64_t)seed_len[i] >= (min_len << 1)) {
-            if (seed_len[i] < 2) { g_err = "seed " + std::to_string(i) + " is too short to be split (min_len must be at least 1)"; return MONI_GPU_EINVAL; }
-            want_halves += 2;
-        }
+        if ((uint64_t)seed_len[i] >= (min_len << 1)) want_halves += 2;
     if (want_halves && (!half_parent || !half_ref || !half_len || !half_qpos)) { g_err = "null output"; return MONI_GPU_EINVAL; }
     return guarded([&]() -> int {
         Replica& R = *idx->reps[0];

@@ -20,6 +20,22 @@
 #define MONI_HD inline
 #endif
 
+// -DMONI_BOUNDS_CHECK builds the kernels with an index check in front of every global access whose index is computed from
+// input data (rows, read bytes, text words, flag words, restart lists, records): a violation prints its source line and traps,
+// which the host sees as a CUDA error.  The pool's compute-sanitizer is closed, so this build (variants/libmoni_gpu_check.so,
+// tests/test_gpu_parity.py::test_bounds_checked_build_runs_the_suite) is the memcheck of this tree.
+#if defined(MONI_BOUNDS_CHECK) && defined(__CUDA_ARCH__)
+#define MONI_ASSERT(cond)                                                          \
+    do {                                                                           \
+        if (!(cond)) {                                                             \
+            printf("moni bounds check failed: %s (%s:%d)\n", #cond, __FILE__, __LINE__); \
+            __trap();                                                              \
+        }                                                                          \
+    } while (0)
+#else
+#define MONI_ASSERT(cond) ((void)0)
+#endif
+
 namespace moni {
 
 struct ImageView {
@@ -159,10 +175,12 @@ MONI_HD void scan_init(const ImageView& v, ScanState& s) {
 // Consumes one symbol; on return s.sample is the pointer to store.  `tcode` is the 256-byte symbol
 // class table (shared memory on the device).
 MONI_HD void scan_step(const ImageView& v, const uint8_t* tcode, uint8_t c, ScanState& s, Counters* cnt) {
+    MONI_ASSERT(s.cur <= v.hdr.n_rows);
     RowRegs row = load_row(v.rows, s.cur);
     while (s.off >= row.len()) {                     // forward scan after the previous LF (bounded by balancing)
         s.off -= row.len();
         s.cur += 1;
+        MONI_ASSERT(s.cur <= v.hdr.n_rows);
         row = load_row(v.rows, s.cur);
         if (cnt) cnt->scan_rows++;
     }
@@ -180,6 +198,7 @@ MONI_HD void scan_step(const ImageView& v, const uint8_t* tcode, uint8_t c, Scan
         const bool up = s.off < row.t_rel(slot);
         const uint32_t d = up ? row.dist_up(slot) : row.dist_dn(slot);
         if (d != kFar) {
+            MONI_ASSERT(up ? s.cur >= d : (uint64_t)s.cur + d <= v.hdr.n_rows);
             const RowRegs q = load_row(v.rows, up ? (uint64_t)s.cur - d : (uint64_t)s.cur + d);
             s.sample = up ? q.s_last() : q.s_start();
             s.off = q.dest_off() + (up ? q.len() - 1 : 0);
@@ -293,6 +312,7 @@ struct RunBufs {
     uint64_t* rrec = nullptr;           // (i << 32) | len of every restart, same indexing as rptr; or null
     uint64_t* rec = nullptr;            // MEM / seed records at the read's own offset; or null
     uint64_t* rec_ref = nullptr;        // seeds: pointers[i] of every record; or null
+    uint64_t seq_bytes = 0, flag_words = 0, run_entries = 0, rec_entries = 0;   // extents of the above (MONI_BOUNDS_CHECK builds test against them)
 };
 struct RunRead {
     uint32_t o = 0;         // chunk-relative offset of the read's first base (also where its records go)
@@ -309,21 +329,28 @@ struct RunRead {
 // SEEDS: the record rule is seed_finder::find_mems' (include/aligner/seed_finder.hpp:148): l >= pl and n_Ns < l and
 // l >= min_len, where n_Ns counts the consecutive 'N' at the end of the characters matched so far (:139-143; it is only
 // touched when a character is compared and matches), which can only hold at a restart; rec_ref[k] receives pointers[i].
-// TEXT: the whole text is one literal block in HBM (ImageHeader::root_ref is a leaf): no descent and no descent state, the
-// compare address is pool + pos + l.  (Requesting the text line of the NEXT restart with prefetch.global.L2 while this one is
-// compared was measured and dropped: DRAM reads doubled, 17.3 -> 38.6 GB per 2 M reads, and the kernel went from 5.0 to 8.7 ms,
-// profiles/r02_c_launches.csv -- the prefetched line is fetched again by the demand load.)
+// With the text in HBM the root is itself a literal block: DESCEND falls straight through.  Two variations were measured on cfg3 and
+// dropped (profiles/r02_c_launches.csv, r02_g_ab_variants.json, r02_h_ab_variants.json): requesting the text line of the NEXT
+// restart with prefetch.global.L2 while this one is compared (DRAM reads doubled, 17.3 -> 38.6 GB per 2 M reads: the demand load
+// fetches the line again; 5.0 -> 8.7 ms), and a text-only specialisation without the descent state (5.1 ms against 4.6 ms for this
+// code at the same 64-register cap; at 40 registers and 1536 threads per SM 6.2 ms: the read bytes and restart lists of that many
+// reads no longer fit L1).
 // Call while st.mode != FINISHED.
-template <bool SEEDS = false, bool TEXT = false>
+template <bool SEEDS = false>
 MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, RunState& st, Counters* ctr, uint32_t min_len = 0) {
     const uint64_t N = v.hdr.text_len;
-    const uint8_t* const text = v.pool + ((uint64_t)(v.hdr.root_ref & ~kLeafBit) << v.hdr.pool_shift);    // TEXT only
     const uint32_t m = R.m;
     bool done = false;
     if (st.mode == RunState::NEXT) {
+        MONI_ASSERT(R.cnt >= 1 && R.last >= R.cnt - 1 && R.last < B.run_entries && (uint64_t)R.fb + (m + 31) / 32 <= B.flag_words);
+        MONI_ASSERT(!B.rec || (uint64_t)R.o + m <= B.rec_entries);
         if (st.k == R.cnt) {                                      // offsets after the last restart: lengths run down to 0, then (i, 0) records
-            if (!SEEDS && B.rec)
+            if (!SEEDS && B.rec) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
                 for (uint32_t q = st.ip + st.Lp + 1; q < m; ++q) B.rec[(uint64_t)R.o + st.n_mems++] = (uint64_t)q << 32;
+            }
             st.mode = RunState::FINISHED;
             return;
         }
@@ -332,15 +359,20 @@ MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, R
             st.nxt = ld(B.rptr + R.last);
             if (R.cnt > 1) st.nxt2 = ld(B.rptr + (R.last - 1));
         }
-        while (st.bits == 0) st.bits = ld(B.flags + R.fb + (++st.w));
+        while (st.bits == 0) { MONI_ASSERT(st.w + 1 < (m + 31) / 32); st.bits = ld(B.flags + R.fb + (++st.w)); }
         const uint32_t i = 32u * st.w + ctz32(st.bits);
+        MONI_ASSERT(i < m);
         st.bits &= st.bits - 1u;
         st.pos = st.nxt;
         st.nxt = st.nxt2;                                         // pointers are consumed two restarts after they were requested
         if (st.k + 2 < R.cnt) st.nxt2 = ld(B.rptr + (R.last - (st.k + 2)));
         if (st.k) {
-            if (!SEEDS && B.rec)
+            if (!SEEDS && B.rec) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
                 for (uint32_t q = st.ip + st.Lp + 1; q < i; ++q) B.rec[(uint64_t)R.o + st.n_mems++] = (uint64_t)q << 32;
+            }
             const uint32_t d = i - st.ip;                         // >= 1
             st.l = st.Lp > d ? st.Lp - d : 0u;                    // the l the reference carries into offset i
         } else {
@@ -351,18 +383,13 @@ MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, R
         done = true;
         if (i + st.l < m && st.pos + st.l < N) {                  // u64 add wraps exactly as in the reference
             done = false;
-            if (TEXT) {
-                st.mode = RunState::COMPARE;
-                if (ctr) ctr->descents++;
-            } else {
-                st.mode = RunState::DESCEND;
-                st.ref = v.hdr.root_ref;
-                st.span = N;
-                st.p = st.pos + st.l;
-            }
+            st.mode = RunState::DESCEND;
+            st.ref = v.hdr.root_ref;
+            st.span = N;
+            st.p = st.pos + st.l;
         }
     }
-    if (!TEXT && st.mode == RunState::DESCEND) {
+    if (st.mode == RunState::DESCEND) {
         // tight loop on purpose: a level is ~10 instructions, far less than one trip through this function
         while (!(st.ref & kLeafBit)) {
 #if defined(__CUDA_ARCH__)
@@ -385,10 +412,11 @@ MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, R
         const uint32_t e = st.i + st.l;                          // < m
         uint32_t lim = m - e;
         if (lim > 8u) lim = 8u;
-        const uint64_t rem = TEXT ? N - (st.pos + st.l) : st.rem;   // text bytes left (TEXT: pos + l < N holds here)
-        if ((uint64_t)lim > rem) lim = (uint32_t)rem;
+        if ((uint64_t)lim > st.rem) lim = (uint32_t)st.rem;
+        MONI_ASSERT((uint64_t)R.o + e + 16 <= B.seq_bytes);
+        MONI_ASSERT((uint64_t)(st.t - v.pool) + 16 <= v.hdr.pool_bytes);
         const uint64_t rd = load8(B.seqs + ((uint64_t)R.o + e));
-        const uint64_t x = load8(TEXT ? text + (st.pos + st.l) : st.t) ^ rd;
+        const uint64_t x = load8(st.t) ^ rd;
         uint32_t k = x ? first_diff_byte(x) : 8u;
         const bool mismatch = k < lim;
         if (!mismatch) k = lim;
@@ -409,11 +437,12 @@ MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, R
         }
         if (ctr) ctr->chars += k + (mismatch ? 1u : 0u);
         st.l += k;
-        if (!TEXT) { st.t += k; st.rem -= k; }
+        st.t += k;
+        st.rem -= k;
         if (mismatch || e + k >= m) {
             done = true;
-        } else if (TEXT ? rem == k : st.rem == 0) {              // block (TEXT: the text) exhausted while still matching
-            if (!TEXT && st.pos + st.l < N) {
+        } else if (st.rem == 0) {                                // block exhausted while still matching
+            if (st.pos + st.l < N) {
                 st.mode = RunState::DESCEND;
                 st.ref = v.hdr.root_ref;
                 st.span = N;
@@ -434,6 +463,7 @@ MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, R
         const bool emit = SEEDS ? (st.l >= prev_len && st.n_Ns < st.l && st.l >= min_len)        // seed_finder.hpp:148 (pl starts at 0)
                                 : (i == 0 || st.l >= prev_len);                                   // src/mems.cpp:257-258
         if (emit) {
+            MONI_ASSERT(st.n_mems < m);
             if (B.rec) B.rec[(uint64_t)R.o + st.n_mems] = ((uint64_t)i << 32) | st.l;
             if (SEEDS && B.rec_ref) B.rec_ref[(uint64_t)R.o + st.n_mems] = st.pos;
             ++st.n_mems;
@@ -446,10 +476,10 @@ MONI_HD void runs_step(const ImageView& v, const RunBufs& B, const RunRead& R, R
 }
 
 // The whole length loop of one read (a single lane of the state machine).  Returns the number of MEM records.
-template <bool SEEDS = false, bool TEXT = false>
+template <bool SEEDS = false>
 MONI_HD uint32_t runs_read(const ImageView& v, const RunBufs& B, const RunRead& R, Counters* ctr, uint32_t min_len = 0) {
     RunState st;
-    while (st.mode != RunState::FINISHED) runs_step<SEEDS, TEXT>(v, B, R, st, ctr, min_len);
+    while (st.mode != RunState::FINISHED) runs_step<SEEDS>(v, B, R, st, ctr, min_len);
     return st.n_mems;
 }
 

@@ -75,7 +75,6 @@ int main(int argc, char** argv) {
         fclose(f);
 
         const uint64_t total = off[nr];
-        const bool text_mode = (img.hdr.root_ref & kLeafBit) != 0;
         std::vector<uint64_t> ptr(total + 1), len64(total + 1), mo(nr + 1), mems;
         Counters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         for (uint64_t r = 0; r < nr; ++r) {
@@ -106,8 +105,7 @@ int main(int argc, char** argv) {
             RunRead R;
             R.o = 0; R.m = (uint32_t)m; R.fb = 0; R.cnt = rs.k; R.last = rs.k ? rs.k - 1 : 0;
             if (m) {
-                // the kernels pick the text-in-HBM specialisation of pass 2 when the root of the grammar table is one literal block
-                k = text_mode ? runs_read<false, true>(v, B, R, &cnt) : runs_read<false, false>(v, B, R, &cnt);
+                k = runs_read<false>(v, B, R, &cnt);
                 expand_runs(m, flags.data(), rptr.data(), rrec.data(), rs.k, ptr.data() + o, len64.data() + o);
                 for (uint64_t j = 0; j < m; ++j)
                     if (ptr[o + j] != direct[j]) throw std::runtime_error("expanded pointers differ from the scan's");
@@ -116,7 +114,7 @@ int main(int argc, char** argv) {
             mems.insert(mems.end(), rec.begin(), rec.begin() + k);
             if (want_seeds) {
                 B.rrec = nullptr;
-                const uint32_t ks = !m ? 0 : text_mode ? runs_read<true, true>(v, B, R, nullptr, seed_min_len) : runs_read<true, false>(v, B, R, nullptr, seed_min_len);
+                const uint32_t ks = m ? runs_read<true>(v, B, R, nullptr, seed_min_len) : 0;
                 so.push_back(s_ref.size());
                 for (uint32_t t = 0; t < ks; ++t) { s_ref.push_back(ref[t]); s_len.push_back(rec[t] & 0xFFFFFFFFu); s_qpos.push_back(rec[t] >> 32); }
             }

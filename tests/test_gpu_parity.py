@@ -710,3 +710,61 @@ def test_populate_seeds_equals_reference(case, m, oracle_mod, tmp_path):
         ix.populate_seeds(so, ref, ln, qpos, 0)
     assert e.value.code == -1
     ix.close()
+
+
+def test_index_larger_than_l2_against_reference_binaries(m, tmp_path):
+    """BASELINE configs[2] (cfg3: n = 1.28 G, 4.8 GB image, far larger than the 126 MB L2) when its index travels with the snapshot
+    (data/cfg3, what bench.py times): 20 000 reads sampled from the text through the CUDA path and through the unmodified reference
+    `ms` / `mems` binaries -- pointers, lengths and MEM records equal number by number.  Skipped where the index is absent."""
+    import build_index
+    import refparse
+    import synth
+    import workloads
+    pre = workloads.index_prefix("cfg3")
+    if not os.path.exists(pre + ".thrbv.ms"):
+        pytest.skip("data/cfg3 index not present")
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "mems")):
+        pytest.skip("reference binaries not built")
+    workloads.ensure_index("cfg3", verbose=False)          # makes <prefix>.plain.slp from the seeded text if only the .thrbv.ms travelled
+    reads = workloads.reads_of("cfg3", pairs=10_000)
+    flat, offs = m.pack_reads(reads)
+    ix = m.MoniIndex(pre)
+    assert ix.n > (1 << 30)
+    ptr, ln = ix.matching_statistics(flat, offs)
+    mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+    ro, rq, rl, rp = ix.matching_statistics_runs(flat, offs)
+    xp, xl = m.expand_runs(offs, ro, rq, rl, rp)
+    assert np.array_equal(xp, ptr) and np.array_equal(xl, ln)
+    ix.close()
+    fq = os.path.join(str(tmp_path), "s.fq")
+    synth.write_fastq_matrix(fq, reads)
+    build_index.run_reference("ms", pre, fq, os.path.join(str(tmp_path), "ref"), threads=os.cpu_count() or 1)
+    build_index.run_reference("mems", pre, fq, os.path.join(str(tmp_path), "ref"), threads=os.cpu_count() or 1)
+    _, _, pv = refparse.parse_values(os.path.join(str(tmp_path), "ref.pointers"))
+    _, _, lv = refparse.parse_values(os.path.join(str(tmp_path), "ref.lengths"))
+    assert np.array_equal(pv, ptr) and np.array_equal(lv, ln)
+    _, cnt, qo, ql = refparse.parse_mems(os.path.join(str(tmp_path), "ref.mems"))
+    assert np.array_equal(cnt.astype(np.int64), np.diff(mo.astype(np.int64)))
+    assert np.array_equal(qo, mp) and np.array_equal(ql, ml)
+
+
+def test_bounds_checked_build_runs_the_suite():
+    """The kernels compiled with -DMONI_BOUNDS_CHECK (an index check in front of every data-dependent global access: move rows,
+    read bytes incl. the 15 bytes load8 may touch past a read, text words, flag words, restart lists, records; a violation traps)
+    run the parity tests that exercise ragged batches, chunking, sharding, both kernel families and the grammar path without a
+    trap and with the same bits.  This is the memcheck of this tree: the pool's compute-sanitizer is closed."""
+    import subprocess
+    import sys
+    lib = os.path.join(ROOT, "moni_align_b200", "variants", "libmoni_gpu_check.so")
+    if not os.path.exists(lib):
+        pytest.skip("bounds-checked library not built (make -C moni_align_b200/csrc)")
+    env = dict(os.environ, MONI_GPU_LIB=lib)
+    k = ("reference_files or random_reads or empty_ragged or chunking or sharded or runs or dynamic or packed or seeds_equal or "
+         "grammar_index or occurrences or populate")
+    p = subprocess.run([sys.executable, "-m", "pytest", os.path.join(ROOT, "tests", "test_gpu_parity.py"), "-m", "gpu", "-x", "-q", "-k", k,
+                        "--deselect", "tests/test_gpu_parity.py::test_bounds_checked_build_runs_the_suite"],
+                       env=env, capture_output=True, text=True, cwd=ROOT)
+    tail = (p.stdout + p.stderr)[-3000:]
+    assert p.returncode == 0, tail
+    assert "bounds check failed" not in tail
+    assert " passed" in p.stdout
