@@ -734,7 +734,6 @@ struct Replica {
     DevBuf phi, phi_inv, phi_dir, phi_inv_dir;            // `moni align` indexes only
     DevBuf occ_ref, occ_len, occ_off, occ_out, occ_flag, occ_cub, occ_stage;   // moni_gpu_seed_occs scratch
     DevBuf pop_qpos, pop_above, pop_slot, pop_head, pop_up, pop_down, pop_parent, pop_len, pop_hq, pop_hoff, pop_hout;   // moni_gpu_populate_seeds scratch
-    DevBuf shard_off, shard_pos, shard_len, shard_ref;   // multi-GPU mems: a shard's records wait here for their global offset
     ImageView view;
     std::mutex mu;
     double t[6] = {0, 0, 0, 0, 0, 0};
@@ -746,7 +745,6 @@ struct Replica {
         phi.release(); phi_inv.release(); phi_dir.release(); phi_inv_dir.release();
         occ_ref.release(); occ_len.release(); occ_off.release(); occ_out.release(); occ_flag.release(); occ_cub.release(); occ_stage.release();
         for (DevBuf* b : {&pop_qpos, &pop_above, &pop_slot, &pop_head, &pop_up, &pop_down, &pop_parent, &pop_len, &pop_hq, &pop_hoff, &pop_hout}) b->release();
-        shard_off.release(); shard_pos.release(); shard_len.release(); shard_ref.release();
         for (Lane& L : lanes) {
             L.scratch.release();
             for (auto& e : L.events) if (e) cudaEventDestroy(e);
@@ -997,25 +995,68 @@ __global__ void k_shift(uint64_t* __restrict__ a, uint64_t n, uint64_t by) {
     if (i < n) a[i] += by;
 }
 
-// Multi-GPU mems: shard g may send its records home once the record totals of shards 0..g-1 are known.
-struct Rendezvous {
+// One host batch, cut into chunks that the GPUs of an index take in turn (in input order, whoever has a free lane next).  For the
+// record-producing calls a chunk's records belong at the position given by the record counts of all chunks before it: every
+// chunk publishes its count as soon as its kernels are done and waits only for the counts of earlier chunks -- which started
+// earlier, on whatever GPU -- so results stream home in input order while later chunks are still being computed, with one GPU
+// or eight, and no host-side stitching.
+struct ChunkFeed {
     std::mutex mu;
     std::condition_variable cv;
-    std::vector<int64_t> total;      // -1 = not yet known, -2 = that shard failed
-    explicit Rendezvous(int parts) : total(parts, -1) {}
-    void publish(int g, int64_t t) {
-        { std::lock_guard<std::mutex> lock(mu); total[g] = t; }
+    const uint64_t* offsets = nullptr;
+    uint64_t next_read = 0, n_reads = 0;
+    uint64_t chunk_bases = 0, min_reads = 0, hard_cap = kChunkHardCap;
+    int workers = 1, arrived = 0;
+    std::vector<int64_t> count;          // records of chunk c; -1 = not yet known
+    std::vector<uint64_t> prefix{0};     // prefix[c] = records of chunks 0..c-1, valid for c <= known
+    size_t known = 0;
+    bool failed = false;
+
+    // every worker reports how many bases of scratch its GPU can take per lane; chunks are planned once all have (smallest wins)
+    void arrive(uint64_t fit) {
+        std::unique_lock<std::mutex> lock(mu);
+        hard_cap = std::max<uint64_t>(1u << 16, std::min(hard_cap, fit));
+        ++arrived;
+        cv.notify_all();
+        cv.wait(lock, [&] { return failed || arrived >= workers; });
+        if (failed) throw std::runtime_error("another GPU's part of the batch failed");
+    }
+    // next chunk in input order; false when the batch is exhausted
+    bool next(ChunkPlan& p, size_t& c) {
+        std::lock_guard<std::mutex> lock(mu);
+        if (failed) throw std::runtime_error("another GPU's part of the batch failed");
+        if (next_read >= n_reads) return false;
+        p = plan_chunk(offsets, next_read, n_reads, std::min(chunk_bases, hard_cap), min_reads, hard_cap);
+        next_read += p.n;
+        c = count.size();
+        count.push_back(-1);
+        prefix.push_back(0);
+        return true;
+    }
+    void publish(size_t c, uint64_t k) {
+        {
+            std::lock_guard<std::mutex> lock(mu);
+            count[c] = (int64_t)k;
+            while (known < count.size() && count[known] >= 0) {
+                prefix[known + 1] = prefix[known] + (uint64_t)count[known];
+                ++known;
+            }
+        }
         cv.notify_all();
     }
-    uint64_t base_of(int g) {
+    uint64_t wait_prefix(size_t c) {
         std::unique_lock<std::mutex> lock(mu);
-        uint64_t base = 0;
-        for (int h = 0; h < g; ++h) {
-            cv.wait(lock, [&] { return total[h] != -1; });
-            if (total[h] < 0) throw std::runtime_error("another GPU's shard failed");
-            base += (uint64_t)total[h];
-        }
-        return base;
+        cv.wait(lock, [&] { return failed || known >= c; });
+        if (failed) throw std::runtime_error("another GPU's part of the batch failed");
+        return prefix[c];
+    }
+    void fail() {
+        { std::lock_guard<std::mutex> lock(mu); failed = true; }
+        cv.notify_all();
+    }
+    uint64_t total() {
+        std::lock_guard<std::mutex> lock(mu);
+        return prefix[known];
     }
 };
 
@@ -1030,59 +1071,35 @@ struct RecOut {
     uint32_t min_len = 0;                        // seeds
 };
 
-// Processes reads [r0, r1) of a host batch on one replica.  Chunks alternate between the replica's
-// lanes (stream + scratch each), so the copies of one chunk overlap the kernels of the other.
-// mode: kModeMs, kModeMems, kModeSeeds, kModeRuns.  All but ms: records go to out.col[] (contiguous from index 0, capacity out.cap)
-// and per-read record offsets (relative to this shard) to out.off[0 .. r1-r0]; *needed receives the shard's record count.
-void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, const uint64_t* offsets, uint64_t r0, uint64_t r1,
-               uint64_t* pointers, uint64_t* lengths, const RecOut& out, uint64_t* needed, Rendezvous* rv = nullptr, int shard = 0) {
-    // rv != null: out.off / out.col are the CALLER's whole-batch arrays; this shard's records are kept on
-    // the device until the shards before it have published their totals, then copied to their final place.
+void collect_times(moni_gpu_index* idx) {
+    for (int k = 0; k < 6; ++k) {
+        idx->t[k] = 0;
+        for (auto& r : idx->reps) idx->t[k] = std::max(idx->t[k], r->t[k]);
+    }
+}
+
+// One GPU's share of a host batch: takes chunks from the feed while it has a free lane (stream + scratch each), so the copies of
+// one chunk overlap the kernels of the others.  mode: kModeMs, kModeMems, kModeSeeds, kModeRuns.  All but ms: records go to
+// out.col[] (contiguous in input order, capacity out.cap) and per-read record offsets to out.off[0 .. n_reads].
+void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, const uint64_t* offsets, uint64_t n_reads, ChunkFeed& feed,
+                uint64_t* pointers, uint64_t* lengths, const RecOut& out) {
     const bool mems = mode != kModeMs;
     uint64_t* const rec_off = out.off;
     const uint64_t rec_cap = out.cap;
-    std::lock_guard<std::mutex> lock(R.mu);
-    CK(cudaSetDevice(R.dev));
-    for (double& x : R.t) x = 0;
-    // A chunk may not need more scratch than its lane's share of the HBM that is free (or already held by the lanes): the index
-    // image, other replicas on the same device and other processes have taken theirs.  A single read larger than that share
-    // still forms a chunk of its own and then fails with MONI_GPU_ENOMEM and the size needed.
-    uint64_t hard_cap = kChunkHardCap;
-    {
-        size_t free_b = 0, total_b = 0, held = 0;
-        CK(cudaMemGetInfo(&free_b, &total_b));
-        for (Lane& L : R.lanes) held += L.scratch.held();
-        const double share = 0.85 * (double)(free_b + held) / (double)R.lanes.size();
-        const uint64_t fit = (uint64_t)(share / Scratch::bytes_per_base(mode));
-        hard_cap = std::max<uint64_t>(1u << 16, std::min<uint64_t>(hard_cap, fit));
-    }
-    // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
-    // would cut a 1 G-base batch into two chunks and leave half the lanes (and the copy/compute overlap) unused, so the minimum
-    // shrinks until the shard makes at least two chunks per lane.
-    const uint64_t min_reads = std::min<uint64_t>(idx->opt.chunk_min_reads, std::max<uint64_t>(1024, (r1 - r0) / (2 * R.lanes.size())));
-    // chunks are planned (and their offsets validated) just before they are enqueued, so the host's pass over the
-    // offsets overlaps the GPU's work on earlier chunks
-    std::vector<ChunkPlan> plans;
-    uint64_t next_read = r0;
+    struct InFlight { ChunkPlan p; size_t c, lane, ev_at; };
+    std::vector<InFlight> done;
+    std::vector<InFlight> q;                 // chunks enqueued and not yet finished, oldest first (at most one per lane)
     const size_t kLanes_ = R.lanes.size();
-    for (Lane& L : R.lanes) L.used = 0;
-    std::vector<size_t> ev_at;
-    uint64_t rec_total = 0;
-    if (mems && !rv) rec_off[0] = 0;
-    DevBuf* const shard_col[3] = {&R.shard_pos, &R.shard_len, &R.shard_ref};
-    if (rv) {
-        R.shard_off.reserve((r1 - r0 + 1) * 8);
-        for (int k = 0; k < out.ncol; ++k) shard_col[k]->reserve((offsets[r1] - offsets[r0]) * out.width[k] + 16);
-    }
+    size_t issued = 0;
 
-    auto enqueue_front = [&](size_t c) {
-        const ChunkPlan& p = plans[c];
-        Lane& L = R.lanes[c % kLanes_];
+    auto enqueue = [&](const ChunkPlan& p, size_t c) {
+        Lane& L = R.lanes[issued % kLanes_];
         Scratch& S = L.scratch;
         S.reserve(p, mode);
-        ev_at.push_back(L.used);
+        InFlight f{p, c, issued % kLanes_, L.used};
+        ++issued;
         L.take();
-        cudaEvent_t* e = L.events.data() + ev_at[c];
+        cudaEvent_t* e = L.events.data() + f.ev_at;
         CK(cudaEventRecord(e[0], L.stream));
         if (p.bases) CK(cudaMemcpyAsync(S.seqs.p, seqs + p.base, p.bases, cudaMemcpyHostToDevice, L.stream));
         if (p.uniform_len) {
@@ -1110,112 +1127,138 @@ void run_shard(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, cons
             CK(cudaEventRecord(e[4], L.stream));
             if (p.bases && packed) {
                 DevBuf* const src[3] = {&S.out_ptr, &S.out_hi, &S.out_len};
-                for (int q = 0; q < 3; ++q)
-                    CK(cudaMemcpyAsync((char*)out.col[q] + p.base * out.width[q], src[q]->p, p.bases * out.width[q], cudaMemcpyDeviceToHost, L.stream));
+                for (int k = 0; k < 3; ++k)
+                    CK(cudaMemcpyAsync((char*)out.col[k] + p.base * out.width[k], src[k]->p, p.bases * out.width[k], cudaMemcpyDeviceToHost, L.stream));
             } else if (p.bases) {
                 CK(cudaMemcpyAsync(pointers + p.base, S.out_ptr.p, p.bases * 8, cudaMemcpyDeviceToHost, L.stream));
                 CK(cudaMemcpyAsync(lengths + p.base, S.out_len.p, p.bases * 8, cudaMemcpyDeviceToHost, L.stream));
             }
             CK(cudaEventRecord(e[5], L.stream));
         }
+        q.push_back(f);
     };
-    // mems only: learn the chunk's record count, then send offsets (shifted to shard-relative) and records home
-    auto finish_mems = [&](size_t c) {
-        const ChunkPlan& p = plans[c];
-        Lane& L = R.lanes[c % kLanes_];
+    // oldest chunk in flight: ms -- wait until its results are home (the lane is free again); records -- learn its record count,
+    // publish it, wait for the counts of all earlier chunks, then send offsets (shifted to batch-relative) and records home
+    auto finish = [&](const InFlight& f) {
+        const ChunkPlan& p = f.p;
+        Lane& L = R.lanes[f.lane];
         Scratch& S = L.scratch;
-        cudaEvent_t* e = L.events.data() + ev_at[c];
+        cudaEvent_t* e = L.events.data() + f.ev_at;
+        if (!mems) {
+            CK(cudaEventSynchronize(e[5]));
+            return;
+        }
         uint64_t k = 0;
         CK(cudaMemcpyAsync(&k, S.moff.as<uint64_t>() + p.n, 8, cudaMemcpyDeviceToHost, L.stream));
         CK(cudaStreamSynchronize(L.stream));
-        if (rec_total) {
-            k_shift<<<(unsigned)((p.n + 1 + 255) / 256), 256, 0, L.stream>>>(S.moff.as<uint64_t>(), p.n + 1, rec_total);
+        feed.publish(f.c, k);
+        const uint64_t before = feed.wait_prefix(f.c);
+        if (before) {
+            k_shift<<<(unsigned)((p.n + 1 + 255) / 256), 256, 0, L.stream>>>(S.moff.as<uint64_t>(), p.n + 1, before);
             g_launches++;
         }
-        const bool last = p.first + p.n == r1;
+        const bool last = p.first + p.n == n_reads;
         DevBuf* const chunk_col[3] = {&S.mem_pos, &S.mem_len, out.fmt == 9 ? &S.out_hi : &S.mem_ref};
-        if (rv) {
-            CK(cudaMemcpyAsync(R.shard_off.as<uint64_t>() + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToDevice, L.stream));
-            for (int q = 0; q < out.ncol && k; ++q)
-                CK(cudaMemcpyAsync(shard_col[q]->as<char>() + rec_total * out.width[q], chunk_col[q]->p, k * out.width[q], cudaMemcpyDeviceToDevice, L.stream));
-        } else {
-            CK(cudaMemcpyAsync(rec_off + (p.first - r0), S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
-            for (int q = 0; q < out.ncol && k && rec_total + k <= rec_cap; ++q)
-                CK(cudaMemcpyAsync((char*)out.col[q] + rec_total * out.width[q], chunk_col[q]->p, k * out.width[q], cudaMemcpyDeviceToHost, L.stream));
-        }
+        CK(cudaMemcpyAsync(rec_off + p.first, S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
+        for (int col = 0; col < out.ncol && k && before + k <= rec_cap; ++col)
+            CK(cudaMemcpyAsync((char*)out.col[col] + before * out.width[col], chunk_col[col]->p, k * out.width[col], cudaMemcpyDeviceToHost, L.stream));
         CK(cudaEventRecord(e[5], L.stream));
-        rec_total += k;
     };
 
-    // keep lanes - 1 chunks enqueued ahead of the one whose results are being sent home
-    size_t fronted = 0;
     try {
-        for (size_t c = 0; c < fronted || next_read < r1; ++c) {
-            while (next_read < r1 && fronted < c + kLanes_) {
-                plans.push_back(plan_chunk(offsets, next_read, r1, std::min(idx->opt.chunk_bases, hard_cap), min_reads, hard_cap));
-                next_read += plans.back().n;
-                enqueue_front(fronted++);
-            }
-            if (mems) finish_mems(c);
+        CK(cudaSetDevice(R.dev));
+        for (double& x : R.t) x = 0;
+        for (Lane& L : R.lanes) L.used = 0;
+        // A chunk may not need more scratch than a lane's share of the HBM that is free (or already held by the lanes): the index
+        // image, other replicas on the same device and other processes have taken theirs.  A single read larger than that share
+        // still forms a chunk of its own and then fails with MONI_GPU_ENOMEM and the size needed.
+        {
+            size_t free_b = 0, total_b = 0, held = 0;
+            CK(cudaMemGetInfo(&free_b, &total_b));
+            for (Lane& L : R.lanes) held += L.scratch.held();
+            const double share = 0.85 * (double)(free_b + held) / (double)kLanes_;
+            feed.arrive((uint64_t)(share / Scratch::bytes_per_base(mode)));
         }
+        for (;;) {
+            ChunkPlan p;
+            size_t c = 0;
+            while (q.size() < kLanes_ && feed.next(p, c)) enqueue(p, c);
+            if (q.empty()) break;
+            finish(q.front());
+            done.push_back(q.front());
+            q.erase(q.begin());
+        }
+        for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
     } catch (...) {
-        // a bad offset found mid-batch (or a CUDA failure): nothing may still be writing the caller's buffers when we return
+        // a bad offset found mid-batch (or a CUDA failure): the other GPUs stop, and nothing may still be writing the caller's
+        // buffers when we return
+        feed.fail();
         for (Lane& L : R.lanes) cudaStreamSynchronize(L.stream);
         throw;
     }
-    const size_t nc = plans.size();
-    for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
-    if (nc && getenv("MONI_GPU_TRACE")) {      // per-chunk timeline (ms since the first event): where the pipeline idles
-        cudaEvent_t* e0 = R.lanes[0].events.data() + ev_at[0];
-        for (size_t c = 0; c < nc; ++c) {
-            cudaEvent_t* e = R.lanes[c % kLanes_].events.data() + ev_at[c];
-            fprintf(stderr, "[moni-gpu trace] gpu %d chunk %zu lane %zu reads %llu:", R.dev, c, c % kLanes_, (unsigned long long)plans[c].n);
+    if (!done.empty() && getenv("MONI_GPU_TRACE")) {      // per-chunk timeline (ms since the first event): where the pipeline idles
+        cudaEvent_t* e0 = R.lanes[done[0].lane].events.data() + done[0].ev_at;
+        for (const InFlight& f : done) {
+            cudaEvent_t* e = R.lanes[f.lane].events.data() + f.ev_at;
+            fprintf(stderr, "[moni-gpu trace] gpu %d chunk %zu lane %zu reads %llu:", R.dev, f.c, f.lane, (unsigned long long)f.p.n);
             for (int k = 0; k < kEv; ++k) fprintf(stderr, " %.3f", ev_ms(e0[0], e[k]));
             fprintf(stderr, "   (start h2d pass1 pass2 compact d2h)\n");
         }
     }
-    for (size_t c = 0; c < nc; ++c) {
-        cudaEvent_t* e = R.lanes[c % kLanes_].events.data() + ev_at[c];
+    for (const InFlight& f : done) {
+        cudaEvent_t* e = R.lanes[f.lane].events.data() + f.ev_at;
         for (int k = 0; k < 5; ++k) R.t[k] += ev_ms(e[k], e[k + 1]);
-        cudaEvent_t* e0 = R.lanes[0].events.data() + ev_at[0];
+        cudaEvent_t* e0 = R.lanes[done[0].lane].events.data() + done[0].ev_at;
         R.t[5] = std::max<double>(R.t[5], ev_ms(e0[0], e[5]));
     }
-    if (rv) {
-        rv->publish(shard, (int64_t)rec_total);
-        const uint64_t gbase = rv->base_of(shard);
-        Lane& L = R.lanes[0];
-        const size_t at = L.used;
-        L.take();
-        cudaEvent_t* e = L.events.data() + at;
-        const uint64_t nr = r1 - r0;
-        const bool last_shard = shard + 1 == (int)rv->total.size();
-        CK(cudaEventRecord(e[0], L.stream));
-        if (gbase && nr) {
-            k_shift<<<(unsigned)((nr + 1 + 255) / 256), 256, 0, L.stream>>>(R.shard_off.as<uint64_t>(), nr + 1, gbase);
-            g_launches++;
-        }
-        CK(cudaMemcpyAsync(rec_off + r0, R.shard_off.p, (nr + (last_shard ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
-        for (int q = 0; q < out.ncol && rec_total && gbase + rec_total <= rec_cap; ++q)
-            CK(cudaMemcpyAsync((char*)out.col[q] + gbase * out.width[q], shard_col[q]->p, rec_total * out.width[q], cudaMemcpyDeviceToHost, L.stream));
-        CK(cudaEventRecord(e[1], L.stream));
-        CK(cudaStreamSynchronize(L.stream));
-        const double ms = ev_ms(e[0], e[1]);
-        R.t[4] += ms;
-        R.t[5] += ms;
-    }
-    if (needed) *needed = rec_total;
 }
 
-void split_by_bases(const uint64_t* offsets, uint64_t n_reads, int parts, std::vector<uint64_t>& cut) {
-    cut.assign(parts + 1, n_reads);
-    cut[0] = 0;
-    const uint64_t total = offsets[n_reads] - offsets[0];
-    for (int g = 1; g < parts; ++g) {
-        const uint64_t want = offsets[0] + total / parts * g;
-        cut[g] = std::lower_bound(offsets, offsets + n_reads + 1, want) - offsets;
-        if (cut[g] < cut[g - 1]) cut[g] = cut[g - 1];
-        if (cut[g] > n_reads) cut[g] = n_reads;
+// Runs one batch over all replicas of the index; returns the number of records (0 for ms).
+uint64_t run_batch(moni_gpu_index* idx, int mode, const char* seqs, const uint64_t* offsets, uint64_t n_reads, uint64_t* pointers,
+                   uint64_t* lengths, const RecOut& out) {
+    const int G = (int)idx->reps.size();
+    // The workers of one call wait for each other (chunk counts), so a call owns ALL replicas while it runs: the locks are taken
+    // here, in replica order, not by the workers -- two concurrent calls on one index can then never hold one replica each.
+    std::vector<std::unique_lock<std::mutex>> locks;
+    for (auto& r : idx->reps) locks.emplace_back(r->mu);
+    ChunkFeed feed;
+    feed.offsets = offsets;
+    feed.n_reads = n_reads;
+    feed.chunk_bases = idx->opt.chunk_bases;
+    feed.workers = G;
+    // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
+    // would cut a 1 G-base batch into two chunks and leave lanes (and the copy/compute overlap) unused, so the minimum shrinks
+    // until the batch makes at least two chunks per lane.
+    feed.min_reads = std::min<uint64_t>(idx->opt.chunk_min_reads, std::max<uint64_t>(1024, n_reads / (2 * idx->opt.lanes * (uint64_t)G)));
+    if (G == 1) {
+        run_worker(idx, *idx->reps[0], mode, seqs, offsets, n_reads, feed, pointers, lengths, out);
+    } else {
+        std::vector<std::exception_ptr> errs(G);
+        std::vector<std::thread> th;
+        for (int g = 0; g < G; ++g)
+            th.emplace_back([&, g]() {
+                try {
+                    run_worker(idx, *idx->reps[g], mode, seqs, offsets, n_reads, feed, pointers, lengths, out);
+                } catch (...) {
+                    errs[g] = std::current_exception();
+                }
+            });
+        for (auto& t : th) t.join();
+        // the failure that started it, not the "another GPU failed" of those that were stopped by it
+        std::exception_ptr first, other;
+        for (int g = 0; g < G; ++g) {
+            if (!errs[g]) continue;
+            try { std::rethrow_exception(errs[g]); }
+            catch (const CudaError&) { if (!first) first = errs[g]; }
+            catch (const DeviceOom&) { if (!first) first = errs[g]; }
+            catch (const BadBatch&) { if (!first) first = errs[g]; }
+            catch (...) { if (!other) other = errs[g]; }
+        }
+        if (first) std::rethrow_exception(first);
+        if (other) std::rethrow_exception(other);
     }
+    collect_times(idx);
+    return feed.total();
 }
 
 template <typename F>
@@ -1240,12 +1283,6 @@ int guarded(F&& f) {
     }
 }
 
-void collect_times(moni_gpu_index* idx) {
-    for (int k = 0; k < 6; ++k) {
-        idx->t[k] = 0;
-        for (auto& r : idx->reps) idx->t[k] = std::max(idx->t[k], r->t[k]);
-    }
-}
 
 }  // namespace
 
@@ -1485,26 +1522,7 @@ static int ms_impl(moni_gpu_index* idx, const char* seqs, const uint64_t* offset
     if (out.fmt == 7 ? (!out.col[0] || !out.col[1] || !out.col[2]) : (!pointers || !lengths)) { g_err = "null output"; return MONI_GPU_EINVAL; }
     if (out.fmt == 7 && idx->hdr.n > (1ull << 40) - (1ull << 31)) { g_err = "packed pointers need n <= 2^40 - 2^31"; return MONI_GPU_EINVAL; }
     return guarded([&]() -> int {
-        const int G = (int)idx->reps.size();
-        std::vector<uint64_t> cut;
-        split_by_bases(offsets, n_reads, G, cut);
-        std::vector<std::string> errs(G);
-        std::vector<int> rc(G, 0);
-        auto work = [&](int g) {
-            rc[g] = guarded([&]() -> int {
-                run_shard(idx, *idx->reps[g], kModeMs, seqs, offsets, cut[g], cut[g + 1], pointers, lengths, out, nullptr);
-                return 0;
-            });
-            if (rc[g]) errs[g] = g_err;
-        };
-        if (G == 1) work(0);
-        else {
-            std::vector<std::thread> th;
-            for (int g = 0; g < G; ++g) th.emplace_back(work, g);
-            for (auto& t : th) t.join();
-        }
-        collect_times(idx);
-        for (int g = 0; g < G; ++g) if (rc[g]) { g_err = errs[g]; return rc[g]; }
+        run_batch(idx, kModeMs, seqs, offsets, n_reads, pointers, lengths, out);
         return 0;
     });
 }
@@ -1532,40 +1550,7 @@ static int mems_impl(moni_gpu_index* idx, int mode, const char* seqs, const uint
     for (int q = 0; q < out.ncol; ++q)
         if (!out.col[q] && out.cap) { g_err = "null output"; return MONI_GPU_EINVAL; }
     return guarded([&]() -> int {
-        const int G = (int)idx->reps.size();
-        std::vector<uint64_t> cut;
-        split_by_bases(offsets, n_reads, G, cut);
-        uint64_t needed = 0;
-        if (G == 1) {
-            run_shard(idx, *idx->reps[0], mode, seqs, offsets, 0, n_reads, nullptr, nullptr, out, &needed);
-            collect_times(idx);
-        } else {
-            // every shard keeps its records on its GPU until the totals of the shards before it are known, then copies
-            // them straight to their final place in the caller's arrays (input order, no host-side stitching)
-            Rendezvous rv(G);
-            std::vector<uint64_t> k(G, 0);
-            std::vector<int> rc(G, 0);
-            std::vector<std::string> errs(G);
-            std::vector<std::thread> th;
-            for (int g = 0; g < G; ++g)
-                th.emplace_back([&, g]() {
-                    bool published = false;
-                    rc[g] = guarded([&]() -> int {
-                        if (cut[g + 1] > cut[g]) {
-                            run_shard(idx, *idx->reps[g], mode, seqs, offsets, cut[g], cut[g + 1], nullptr, nullptr, out, &k[g], &rv, g);
-                            published = true;
-                        }
-                        return 0;
-                    });
-                    if (rc[g]) errs[g] = g_err;
-                    if (!published) rv.publish(g, rc[g] ? -2 : 0);     // empty or failed shard: never leave the others waiting
-                });
-            for (auto& t : th) t.join();
-            collect_times(idx);
-            for (int g = 0; g < G; ++g) if (rc[g]) { g_err = errs[g]; return rc[g]; }
-            for (int g = 0; g < G; ++g) needed += k[g];
-            mem_offsets[n_reads] = needed;      // also covers trailing shards without reads
-        }
+        const uint64_t needed = run_batch(idx, mode, seqs, offsets, n_reads, nullptr, nullptr, out);
         if (needed > out.cap) {
             g_err = "mem_capacity too small: " + std::to_string(needed) + " records needed";
             return MONI_GPU_ENOMEM;

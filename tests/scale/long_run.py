@@ -63,11 +63,17 @@ def main():
     ap.add_argument("--parity-reads", type=int, default=20_000)
     ap.add_argument("--runs-reads", type=int, default=200_000)
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "long_run.json"))
+    ap.add_argument("--opt", action="append", default=[], help="library option key=value, repeatable (e.g. lanes=8)")
+    ap.add_argument("--dynamic", default="0,1", help="comma list of the dynamic settings to time")
     args = ap.parse_args()
     OUT = args.out
     import moni_align_b200 as m
     from scale_run import cli_vs_reference, hash64
     cores = os.cpu_count() or 1
+    for kv in args.opt:
+        k_, _, v_ = kv.partition("=")
+        m.set_option(k_, v_)
+    RES["options"] = args.opt
     w = workloads.WORKLOADS[args.workload]
     RES["workload"] = w["desc"] + f"; {args.reads} ONT-like reads (mean 10 kbp, 5/5/5 % sub/ins/del)"
     RES["host_cores"] = cores
@@ -103,7 +109,8 @@ def main():
     rec = m.pinned_empty(cap, np.uint32)
     RES["e2e"] = {}
     hashes = {}
-    for dyn in (0, 1):
+    dyns = [int(x) for x in args.dynamic.split(",")]
+    for dyn in dyns:
         m.set_option("dynamic", dyn)
         t = time.time()
         ix = m.MoniIndex(prefix, gpus=[0])
@@ -121,9 +128,9 @@ def main():
             RES["e2e"][f"mems_packed_dynamic{dyn}"] = {"error": f"{type(e).__name__}: {e}"}
         log(dyn, json.dumps(RES["e2e"][f"mems_packed_dynamic{dyn}"])[:600])
         save()
-        if dyn == 0:
+        if dyn != dyns[-1]:
             ix.close()
-    RES["e2e"]["same_hash_dynamic_0_1"] = bool(len(hashes) == 2 and hashes[0] == hashes[1])
+    RES["e2e"]["same_hash_dynamic_0_1"] = bool(len(hashes) == 2 and len(set(hashes.values())) == 1) if len(dyns) == 2 else None
 
     # ms as restart runs on a prefix; expanded on the host and compared with moni_gpu_ms on a sample of it
     try:
