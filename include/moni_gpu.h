@@ -188,6 +188,29 @@ int moni_gpu_batch_fetch_mems(moni_gpu_batch* b, uint64_t* mem_offsets, uint64_t
                               uint64_t mem_capacity);
 void moni_gpu_batch_free(moni_gpu_batch* b);
 
+/* ---- allocation-free call ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Computes exactly what moni_gpu_ms computes
+ * -- pointers[] and lengths[] of every base, laid out like seqs -- but
+ *   - seqs, offsets (n_reads + 1 entries, offsets[0] = 0, offsets[n_reads] = n_bases), pointers and lengths (n_bases entries
+ *     each) are DEVICE pointers on the GPU of `gpu_slot` (index into the `gpus` list of moni_gpu_index_load), owned by the caller;
+ *   - everything the kernels exchange (staged read bytes, restart flags, restart pointers / records, restarts per read) lives in
+ *     one fixed array in the library's device image, about 21 MiB, which every GPU that loads the library holds until the process
+ *     exits.  Hence the limits: at most MONI_GPU_NOALLOC_MAX_READS reads and MONI_GPU_NOALLOC_MAX_BASES bases per call; anything
+ *     larger is refused with MONI_GPU_EINVAL and a message that says so (split the batch, or use moni_gpu_ms);
+ *   - the call itself performs no cudaMalloc / cudaFree / cudaHostAlloc and calls no allocating library routine (no cub, no
+ *     torch): one memset of the status word, one check kernel over offsets (bad offsets -> MONI_GPU_EINVAL), a device-to-device
+ *     copy of the reads into the array, the three ms kernels (one read per lane; no length sort), on `stream` (a cudaStream_t, NULL
+ *     = the default stream).  It returns after `stream` has drained, results in place.
+ * All calls share the one array per GPU and it keeps the last call's contents (the call clears what has to start at zero: the
+ * status word and the 16 bytes behind the reads).  Calls through this entry point are serialised inside the process; work from
+ * ANOTHER process's copy of the library has its own array.  Two calls that overlap on one GPU would race on it -- there is no
+ * way to do that through this synchronous entry point short of bypassing its lock, and none should be added. */
+#define MONI_GPU_NOALLOC_MAX_READS 65536u
+#define MONI_GPU_NOALLOC_MAX_BASES 1048576u
+int moni_gpu_ms_noalloc(moni_gpu_index* idx, int gpu_slot, const char* d_seqs, const uint64_t* d_offsets, uint64_t n_reads,
+                        uint64_t n_bases, uint64_t* d_pointers, uint64_t* d_lengths, void* stream);
+
 /* Diagnostics: the random-access roofline of CUDA device `gpu` ("measured random-sector bandwidth of the box,
  * obtained by a gather micro-benchmark").  Dependent chains over a `table_bytes` table (next granule = hash of the words just
  * loaded: the access pattern of an LF step over the move table, include/ms/ms_pointers.hpp:476-481 + rle_string::rank); a miss

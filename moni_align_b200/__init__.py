@@ -28,6 +28,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MONI_GPU_LIB") or os.path.join(_HERE, "libmoni_gpu.so")   # the override is for A/B builds of the same library
 
 _u64p = ctypes.POINTER(ctypes.c_uint64)
+NOALLOC_MAX_READS, NOALLOC_MAX_BASES = 65536, 1048576      # MONI_GPU_NOALLOC_MAX_* of include/moni_gpu.h
 _lib = None
 
 
@@ -44,7 +45,7 @@ EXPORTS = [
     "moni_gpu_batch_create", "moni_gpu_batch_run", "moni_gpu_batch_fetch_ms", "moni_gpu_batch_fetch_mems",
     "moni_gpu_batch_free", "moni_gpu_launch_count", "moni_gpu_last_error", "moni_gpu_version",
     "moni_gpu_probe_random_lines", "moni_gpu_probe_release", "moni_gpu_ms_runs", "moni_gpu_ms_runs_packed", "moni_gpu_ms_runs_expand",
-    "moni_gpu_populate_seeds",
+    "moni_gpu_populate_seeds", "moni_gpu_ms_noalloc",
 ]
 
 
@@ -86,6 +87,7 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_ms_runs.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, _u64p, ctypes.c_uint64]
     L.moni_gpu_ms_runs_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, vp, ctypes.c_uint64]
     L.moni_gpu_ms_runs_expand.argtypes = [_u64p, ctypes.c_uint64, _u64p, vp, vp, _u64p, _u64p, _u64p]
+    L.moni_gpu_ms_noalloc.argtypes = [vp, ci, vp, vp, ctypes.c_uint64, ctypes.c_uint64, vp, vp, vp]
     L.moni_gpu_batch_create.argtypes = [vp, ci, vp, _u64p, ctypes.c_uint64, ctypes.POINTER(vp)]
     L.moni_gpu_batch_run.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_float)]
     L.moni_gpu_batch_fetch_ms.argtypes = [vp, _u64p, _u64p]
@@ -219,6 +221,15 @@ class MoniIndex:
             ptr, ln = out
         _check(self._L.moni_gpu_ms(self._h, _ptr(seqs), _u64(offsets), nr, _u64(ptr), _u64(ln)))
         return ptr[:total], ln[:total]
+
+    def matching_statistics_noalloc(self, d_seqs: int, d_offsets: int, n_reads: int, n_bases: int, d_pointers: int, d_lengths: int,
+                                    stream: int = 0, gpu_slot: int = 0) -> None:
+        """moni_gpu_ms_noalloc: matching_statistics on DEVICE buffers (raw addresses on GPU `gpus[gpu_slot]`, e.g. torch
+        tensors' data_ptr()), with the library's fixed scratch array instead of allocated scratch -- the call allocates nothing.
+        At most NOALLOC_MAX_READS reads / NOALLOC_MAX_BASES bases per call.  No counterpart in the reference."""
+        _check(self._L.moni_gpu_ms_noalloc(self._h, int(gpu_slot), ctypes.c_void_p(int(d_seqs)), ctypes.c_void_p(int(d_offsets)), int(n_reads),
+                                           int(n_bases), ctypes.c_void_p(int(d_pointers)), ctypes.c_void_p(int(d_lengths)),
+                                           ctypes.c_void_p(int(stream))))
 
     def matching_statistics_packed(self, seqs: np.ndarray, offsets: np.ndarray, out=None):
         """(ptr_lo uint32, ptr_hi uint8, lengths uint16) -- moni_gpu_ms_packed; unpack_pointers() gives the u64 pointers."""

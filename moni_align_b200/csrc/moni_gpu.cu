@@ -1981,3 +1981,117 @@ void moni_gpu_batch_free(moni_gpu_batch* b) {
 }
 
 }  // extern "C"
+
+// ================================================================================ allocation-free entry point
+// moni_gpu_ms_noalloc: moni_gpu_ms for callers that may not allocate (include/moni_gpu.h).  What the two passes exchange -- the
+// staged read bytes, restart flags, pointers at the restarts, restart records, restarts per read -- lives in ONE file-scope array
+// that every GPU holding the library's module carries until the process exits, instead of the cudaMalloc'ed Scratch of a lane.
+// The kernels are the ones above, handed addresses inside the array.
+constexpr uint64_t kNoAllocMaxBases = MONI_GPU_NOALLOC_MAX_BASES, kNoAllocMaxReads = MONI_GPU_NOALLOC_MAX_READS;
+constexpr uint64_t na_round(uint64_t x) { return (x + 255) & ~255ull; }
+constexpr uint64_t kNaRunEntries = kNoAllocMaxBases + 4 * kNoAllocMaxReads + 8;      // ChunkPlan::run_entries()
+constexpr uint64_t kNaFlagWords = kNoAllocMaxBases / 32 + kNoAllocMaxReads + 2;      // ChunkPlan::flag_words()
+constexpr uint64_t kNaOffStatus = 0;                                                  // one u32, cleared by every call
+constexpr uint64_t kNaOffSeqs = 256;                                                  // bases + 16 bytes of slack (load8)
+constexpr uint64_t kNaOffFlags = kNaOffSeqs + na_round(kNoAllocMaxBases + 16);
+constexpr uint64_t kNaOffRcnt = kNaOffFlags + na_round(kNaFlagWords * 4);
+constexpr uint64_t kNaOffRptr = kNaOffRcnt + na_round((kNoAllocMaxReads + 1) * 4);
+constexpr uint64_t kNaOffRrec = kNaOffRptr + na_round(kNaRunEntries * 8);
+constexpr uint64_t kNaBytes = kNaOffRrec + na_round(kNaRunEntries * 8);
+static_assert(kNaBytes <= (32ull << 20), "the allocation-free scratch is meant to stay modest");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+namespace {
+
+// offsets[] as the caller left them on the device: 0 = offsets[0] <= offsets[1] <= ... <= offsets[n] = n_bases, or status != 0
+__global__ void k_noalloc_check(const uint64_t* __restrict__ offs, uint32_t n, uint64_t n_bases, uint32_t* __restrict__ status) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r > n) return;
+    const uint64_t a = offs[r];
+    bool bad = a > n_bases;
+    if (r == 0 && a != 0) bad = true;
+    if (r == n && a != n_bases) bad = true;
+    if (r < n && offs[r + 1] < a) bad = true;
+    if (bad) atomicOr(status, 1u);
+}
+
+std::mutex g_noalloc_mu;                    // one caller at a time per process: every call uses the same array
+unsigned char* g_noalloc_ptr[64] = {};      // device address of g_noalloc_scratch on CUDA device d (the host-side name is only a handle)
+
+unsigned char* noalloc_scratch_on(int dev) {   // with `dev` current
+    if (dev < 0 || dev >= 64) throw BadBatch("device ordinal out of range for the allocation-free scratch");
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr[dev] = (unsigned char*)p;
+    }
+    return g_noalloc_ptr[dev];
+}
+
+bool on_device(const void* p, int dev) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return (a.type == cudaMemoryTypeDevice && a.device == dev) || a.type == cudaMemoryTypeManaged;
+}
+
+}  // namespace
+
+extern "C" int moni_gpu_ms_noalloc(moni_gpu_index* idx, int gpu_slot, const char* d_seqs, const uint64_t* d_offsets, uint64_t n_reads,
+                                   uint64_t n_bases, uint64_t* d_pointers, uint64_t* d_lengths, void* stream) {
+    if (!idx || gpu_slot < 0 || gpu_slot >= (int)idx->reps.size() || !d_offsets || (n_bases && (!d_seqs || !d_pointers || !d_lengths))) {
+        g_err = "bad arguments";
+        return MONI_GPU_EINVAL;
+    }
+    if (n_reads > kNoAllocMaxReads || n_bases > kNoAllocMaxBases) {
+        g_err = "moni_gpu_ms_noalloc takes at most " + std::to_string(kNoAllocMaxReads) + " reads and " + std::to_string(kNoAllocMaxBases) +
+                " bases per call (got " + std::to_string(n_reads) + " reads, " + std::to_string(n_bases) +
+                " bases): its scratch is a fixed array; split the batch or use moni_gpu_ms";
+        return MONI_GPU_EINVAL;
+    }
+    return guarded([&]() -> int {
+        Replica& R = *idx->reps[gpu_slot];
+        std::lock_guard<std::mutex> lock(g_noalloc_mu);
+        CK(cudaSetDevice(R.dev));
+        if (!on_device(d_offsets, R.dev) || (n_bases && (!on_device(d_seqs, R.dev) || !on_device(d_pointers, R.dev) || !on_device(d_lengths, R.dev))))
+            throw BadBatch("moni_gpu_ms_noalloc takes device pointers on the GPU of gpu_slot (seqs, offsets, pointers, lengths)");
+        unsigned char* const base = noalloc_scratch_on(R.dev);
+        cudaStream_t st = (cudaStream_t)stream;
+        uint32_t* status = (uint32_t*)(base + kNaOffStatus);
+        uint8_t* seqs = base + kNaOffSeqs;
+        CK(cudaMemsetAsync(status, 0, 256, st));
+        const uint32_t n = (uint32_t)n_reads;
+        k_noalloc_check<<<(n + 1 + 255) / 256, 256, 0, st>>>(d_offsets, n, n_bases, status);
+        g_launches++;
+        CK(cudaGetLastError());
+        uint32_t h_status = 0;
+        CK(cudaMemcpyAsync(&h_status, status, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (h_status) throw BadBatch("offsets must start at 0, be non-decreasing and end at n_bases");
+        if (!n_reads || !n_bases) return 0;
+        // the reads, with the 16 bytes the 8-byte compares may touch behind the last one (the array keeps the last call's bytes)
+        CK(cudaMemcpyAsync(seqs, d_seqs, n_bases, cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemsetAsync(seqs + n_bases, 0, 16, st));
+        ChunkPlan p;
+        p.first = 0; p.n = n_reads; p.base = 0; p.bases = n_bases;
+        ChunkMap cm;
+        cm.offs = d_offsets; cm.perm = nullptr; cm.base = 0; cm.n_reads = n;
+        cm.seq_bytes = n_bases + 16; cm.flag_words = p.flag_words(); cm.run_entries = p.run_entries();
+        uint32_t* flags = (uint32_t*)(base + kNaOffFlags);
+        uint32_t* rcnt = (uint32_t*)(base + kNaOffRcnt);
+        uint64_t* rptr = (uint64_t*)(base + kNaOffRptr);
+        uint64_t* rrec = (uint64_t*)(base + kNaOffRrec);
+        const dim3 grid((unsigned)((n_reads + kBlock - 1) / kBlock));
+        k_ms_pointers<false><<<grid, kBlock, 0, st>>>(R.view, seqs, cm, rptr, flags, rcnt, nullptr);
+        RunBufs B;
+        B.seqs = seqs; B.flags = flags; B.rptr = rptr; B.rrec = rrec; B.rec = nullptr; B.rec_ref = nullptr;
+        B.seq_bytes = cm.seq_bytes; B.flag_words = cm.flag_words; B.run_entries = cm.run_entries; B.rec_entries = 0;
+        k_ms_lengths<0, false><<<grid, kBlock, 0, st>>>(R.view, B, cm, rcnt, nullptr, nullptr, 0);
+        k_ms_expand<false><<<dim3((unsigned)((n_reads * 32 + kBlock - 1) / kBlock)), kBlock, 0, st>>>(cm, rptr, rrec, flags, rcnt, d_pointers, d_lengths,
+                                                                                                    nullptr, nullptr, nullptr);
+        g_launches += 3;
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(st));
+        return 0;
+    });
+}
