@@ -259,7 +259,7 @@ def cpu_baseline_and_parity(args, prefix, reads_flat, n_reads, read_len, gpu_mem
     return cpu, par
 
 
-API_NAMES = {"mems_u64": "moni_gpu_mems", "mems_u32": "moni_gpu_mems32", "mems_packed32": "moni_gpu_mems_packed",
+API_NAMES = {"mems_u64": "moni_gpu_mems", "mems_u64_link": "moni_gpu_mems", "mems_u32": "moni_gpu_mems32", "mems_packed32": "moni_gpu_mems_packed",
              "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed",
              "ms_runs": "moni_gpu_ms_runs", "ms_runs_packed": "moni_gpu_ms_runs_packed"}
 
@@ -404,6 +404,19 @@ def ours_arm(args) -> None:
     legs["mems_u64"] = e2e_leg(ix.maxrimal_exact_matches, (h_mo, pool_a, pool_b))
     same = {"mems_u64": bool(np.array_equal(h_mo, mo) and np.array_equal(pool_a[:n_mems], mp) and np.array_equal(pool_b[:n_mems], ml))}
     gpu_mems = (h_mo.copy(), pool_a[:n_mems].copy(), pool_b[:n_mems].copy())      # for the parity sample: what the ABI call returned
+    # A/B of the same call with the u64 columns crossing the link as they are (option widen_threads = 0) instead of packed + widened by host threads
+    allowed_cpus = len(os.sched_getaffinity(0))
+    widen_threads = next((int(o.split("=", 1)[1]) for o in args.opt if o.startswith("widen_threads=")), -1)
+    if widen_threads < 0:
+        widen_threads = 0 if allowed_cpus < 4 else min(16, allowed_cpus * 2 // 3)     # WidenPool::default_threads (csrc/host_widen.cpp)
+    if widen_threads > 0:
+        h_mo[:] = 0
+        m.set_option("widen_threads", 0)
+        try:
+            legs["mems_u64_link"] = e2e_leg(ix.maxrimal_exact_matches, (h_mo, pool_a, pool_b))
+        finally:
+            m.set_option("widen_threads", widen_threads)
+        same["mems_u64_link"] = bool(np.array_equal(h_mo, mo) and np.array_equal(pool_a[:n_mems], mp) and np.array_equal(pool_b[:n_mems], ml))
     a32, b32 = pool_a.view(np.uint32)[:total], pool_b.view(np.uint32)[:total]
     h_mo[:] = 0
     legs["mems_u32"] = e2e_leg(ix.maxrimal_exact_matches, (h_mo, a32, b32))
@@ -516,7 +529,8 @@ def ours_arm(args) -> None:
     value_ms = all_reads * args.steps / (dev_ms_ms / 1e3)
     rate = lambda leg: all_reads * args.steps / (legs[leg]["wall"] / 1e3)
     stage_names = ["h2d", "pass1", "pass2", "compact", "d2h", "total"]
-    d2h = {"mems_u64": 8 * (n_reads + 1) + 16 * n_mems, "mems_u32": 8 * (n_reads + 1) + 8 * n_mems,
+    link_rec = 16 if widen_threads == 0 else (2 if int(read_len) < 256 else 4 if int(read_len) < 65536 else 8)   # bytes per record that cross the link
+    d2h = {"mems_u64": 8 * (n_reads + 1) + link_rec * n_mems, "mems_u64_link": 8 * (n_reads + 1) + 16 * n_mems, "mems_u32": 8 * (n_reads + 1) + 8 * n_mems,
            "mems_packed32": 8 * (n_reads + 1) + 4 * n_mems, "mems_packed16": 8 * (n_reads + 1) + 2 * n_mems,
            "ms_u64": 16 * total, "ms_packed": 7 * total, "ms_runs": 8 * (n_reads + 1) + 16 * n_runs,
            "ms_runs_packed": 8 * (n_reads + 1) + 9 * n_runs}
@@ -588,7 +602,10 @@ def ours_arm(args) -> None:
                      "other_kernel": {"kernel": kname[oth], "achieved": alg[oth] / (per[oth] / 1e3) / 1e9,
                                       "frac": alg[oth] / (per[oth] / 1e3) / 1e9 / peak}},
         "counters_per_step": cnt,
-        "e2e": leg_json("mems_u64"),
+        "e2e": {**leg_json("mems_u64"), "host_widen_threads": widen_threads, "link_bytes_per_record": link_rec, "host_bytes_per_record": 16,
+                "note": "u64 (query offset, length) columns in the caller's host arrays; with host_widen_threads > 0 the records cross the link "
+                        "packed and host threads of the library widen them (csrc/host_widen.cpp); e2e_mems_u64_link is the same call with the "
+                        "u64 columns copied over the link (option widen_threads=0)"},
         **{"e2e_" + k: leg_json(k) for k in legs if k.startswith("mems_") and k != "mems_u64"},
         "ms": {"value": value_ms, "unit": "reads/s", "bases_per_s": value_ms * read_len, "ms_per_step": dev_ms_ms / args.steps,
                "stage_ms_per_step": {"pass1": kms_ms[0] / args.steps, "pass2": kms_ms[1] / args.steps, "expand": kms_ms[2] / args.steps},

@@ -32,6 +32,7 @@
 
 #include "../../include/moni_gpu.h"
 #include "device_image.hpp"
+#include "host_widen.hpp"
 #include "index_files.hpp"
 #include "ms_core.cuh"
 
@@ -574,6 +575,7 @@ namespace {
 
 thread_local std::string g_err;
 std::atomic<uint64_t> g_launches{0};
+std::atomic<bool> g_widen_ready{false};   // the widening pool has the size option "widen_threads" asks for
 std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
@@ -587,6 +589,7 @@ struct Options {
     uint32_t l2_fetch = 0;          // 0 = leave the device default
     uint32_t lanes = 4;
     int dynamic = 2;                // 0 = one read per lane, 1 = persistent kernels whose lanes pull reads, 2 = auto (pull when reads are ragged)
+    int widen_threads = -1;         // host threads that widen packed MEM records into the caller's u64 columns; 0 = off (u64 over the link), -1 = auto
 };
 Options g_opt;
 inline double wall_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
@@ -708,9 +711,28 @@ struct Scratch {   // device buffers of one chunk
 constexpr int kMaxLanes = 8;     // chunks in flight per GPU (option "lanes"): copies of one overlap the kernels of the others
 constexpr int kEv = 6;           // events per chunk: start, h2d done, pass 1 done, pass 2 done, compaction done, d2h done
 
+// Pinned host staging of a lane: packed records land here and host threads widen them into the caller's u64 columns.
+struct HostBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    void reserve(size_t bytes) {
+        if (bytes <= cap) return;
+        release();
+        const size_t want = bytes + bytes / 4 + 4096;
+        CK(cudaHostAlloc(&p, want, cudaHostAllocDefault));
+        cap = want;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
 struct Lane {
     cudaStream_t stream = nullptr;
     Scratch scratch;
+    HostBuf stage;
     std::vector<cudaEvent_t> events;     // kEv per chunk processed on this lane in the current call
     size_t used = 0;
     cudaEvent_t* take() {
@@ -747,6 +769,7 @@ struct Replica {
         for (DevBuf* b : {&pop_qpos, &pop_above, &pop_slot, &pop_head, &pop_up, &pop_down, &pop_parent, &pop_len, &pop_hq, &pop_hoff, &pop_hout}) b->release();
         for (Lane& L : lanes) {
             L.scratch.release();
+            L.stage.release();
             for (auto& e : L.events) if (e) cudaEventDestroy(e);
             if (L.stream) cudaStreamDestroy(L.stream);
         }
@@ -1011,6 +1034,7 @@ struct ChunkFeed {
     std::vector<uint64_t> prefix{0};     // prefix[c] = records of chunks 0..c-1, valid for c <= known
     size_t known = 0;
     bool failed = false;
+    bool widen = false;                  // moni_gpu_mems: records cross the link packed, host threads widen them (host_widen.hpp)
 
     // every worker reports how many bases of scratch its GPU can take per lane; chunks are planned once all have (smallest wins)
     void arrive(uint64_t fit) {
@@ -1071,6 +1095,91 @@ struct RecOut {
     uint32_t min_len = 0;                        // seeds
 };
 
+// Size the process-wide widening pool as option "widen_threads" asks (auto: from the CPUs this process may run on).
+int widen_pool_threads() {
+    moni::WidenPool& P = moni::WidenPool::get();
+    if (!g_widen_ready.load()) {
+        std::lock_guard<std::mutex> lock(g_opt_mu);
+        if (!g_widen_ready.load()) {
+            const int want = g_opt.widen_threads < 0 ? moni::WidenPool::default_threads() : g_opt.widen_threads;
+            if (want != P.threads()) P.resize(want);
+            g_widen_ready.store(true);
+        }
+    }
+    return P.threads();
+}
+
+// One per GPU worker of a moni_gpu_mems call: takes (event, staged packed records, destination) jobs in chunk order, waits for the
+// chunk's device->host copy and has the pool widen the records into the caller's u64 columns.  A lane's staging buffer is free again
+// when its job is done (wait_lane).
+class Widener {
+  public:
+    struct Job {
+        cudaEvent_t ev;
+        int cfmt;
+        const void *src, *src2;
+        uint64_t k;
+        uint64_t *dpos, *dlen;
+        size_t lane;
+    };
+    Widener(int dev, size_t lanes) : dev_(dev), pending_(lanes, 0) {}
+    ~Widener() { finish(); }
+    void start() { if (!th_.joinable()) th_ = std::thread([this] { loop(); }); }
+    void push(const Job& j) {
+        { std::lock_guard<std::mutex> lock(mu_); jobs_.push_back(j); ++pending_[j.lane]; }
+        cv_.notify_all();
+    }
+    void wait_lane(size_t lane) {
+        std::unique_lock<std::mutex> lock(mu_);
+        cv_.wait(lock, [&] { return pending_[lane] == 0; });
+    }
+    // all jobs done, thread joined; returns the first CUDA error text seen (empty if none)
+    std::string finish() {
+        if (th_.joinable()) {
+            { std::lock_guard<std::mutex> lock(mu_); stop_ = true; }
+            cv_.notify_all();
+            th_.join();
+        }
+        return err_;
+    }
+    double busy_ms = 0;      // time the pool spent widening
+    uint64_t bytes = 0;      // bytes written to the caller's columns
+
+  private:
+    void loop() {
+        cudaSetDevice(dev_);
+        for (;;) {
+            Job j;
+            {
+                std::unique_lock<std::mutex> lock(mu_);
+                cv_.wait(lock, [&] { return stop_ || !jobs_.empty(); });
+                if (jobs_.empty()) return;
+                j = jobs_.front();
+                jobs_.erase(jobs_.begin());
+            }
+            const cudaError_t e = cudaEventSynchronize(j.ev);
+            if (e != cudaSuccess) {
+                if (err_.empty()) err_ = std::string("cudaEventSynchronize (widening): ") + cudaGetErrorString(e);
+            } else if (err_.empty()) {
+                const double t0 = wall_s();
+                moni::WidenPool::get().widen(j.cfmt, j.src, j.src2, j.k, j.dpos, j.dlen);
+                busy_ms += (wall_s() - t0) * 1e3;
+                bytes += j.k * 16;
+            }
+            { std::lock_guard<std::mutex> lock(mu_); --pending_[j.lane]; }
+            cv_.notify_all();
+        }
+    }
+    int dev_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::vector<Job> jobs_;
+    std::vector<int> pending_;
+    bool stop_ = false;
+    std::string err_;
+    std::thread th_;
+};
+
 void collect_times(moni_gpu_index* idx) {
     for (int k = 0; k < 6; ++k) {
         idx->t[k] = 0;
@@ -1086,7 +1195,10 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
     const bool mems = mode != kModeMs;
     uint64_t* const rec_off = out.off;
     const uint64_t rec_cap = out.cap;
-    struct InFlight { ChunkPlan p; size_t c, lane, ev_at; };
+    struct InFlight { ChunkPlan p; size_t c, lane, ev_at; int cfmt; };
+    const bool widen = feed.widen && mems && out.fmt == 8;
+    Widener W(R.dev, R.lanes.size());
+    if (widen) W.start();
     std::vector<InFlight> done;
     std::vector<InFlight> q;                 // chunks enqueued and not yet finished, oldest first (at most one per lane)
     const size_t kLanes_ = R.lanes.size();
@@ -1096,7 +1208,9 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
         Lane& L = R.lanes[issued % kLanes_];
         Scratch& S = L.scratch;
         S.reserve(p, mode);
-        InFlight f{p, c, issued % kLanes_, L.used};
+        // format the chunk's records take on the device: the caller's, or -- when host threads widen them -- the narrowest that holds them
+        const int cfmt = !widen ? out.fmt : (p.max_len <= 0xFFull ? 1 : p.max_len <= 0xFFFFull ? 2 : 4);
+        InFlight f{p, c, issued % kLanes_, L.used, cfmt};
         ++issued;
         L.take();
         cudaEvent_t* e = L.events.data() + f.ev_at;
@@ -1118,7 +1232,7 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
         launch_pass2(R, S, p, mode, L.stream, out.min_len);
         CK(cudaEventRecord(e[3], L.stream));
         if (mems) {
-            launch_compact(S, p, out.fmt, L.stream);
+            launch_compact(S, p, cfmt, L.stream);
             CK(cudaEventRecord(e[4], L.stream));
         } else {
             const bool packed = out.fmt == 7;      // moni_gpu_ms_packed: col[] = u32 pointer halves, u8 pointer bits 32..39, u16 lengths
@@ -1160,6 +1274,21 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
         const bool last = p.first + p.n == n_reads;
         DevBuf* const chunk_col[3] = {&S.mem_pos, &S.mem_len, out.fmt == 9 ? &S.out_hi : &S.mem_ref};
         CK(cudaMemcpyAsync(rec_off + p.first, S.moff.p, (p.n + (last ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, L.stream));
+        if (widen) {
+            if (k && before + k <= rec_cap) {
+                W.wait_lane(f.lane);                      // the lane's previous chunk has left the staging buffer
+                const size_t w = f.cfmt == 1 ? 2 : 4, col_bytes = (k * w + 63) & ~(size_t)63;
+                L.stage.reserve(f.cfmt == 4 ? 2 * col_bytes : col_bytes);
+                CK(cudaMemcpyAsync(L.stage.p, S.mem_pos.p, k * w, cudaMemcpyDeviceToHost, L.stream));
+                if (f.cfmt == 4) CK(cudaMemcpyAsync((char*)L.stage.p + col_bytes, S.mem_len.p, k * w, cudaMemcpyDeviceToHost, L.stream));
+                CK(cudaEventRecord(e[5], L.stream));
+                W.push({e[5], f.cfmt, L.stage.p, f.cfmt == 4 ? (char*)L.stage.p + col_bytes : nullptr, k, (uint64_t*)out.col[0] + before,
+                        (uint64_t*)out.col[1] + before, f.lane});
+            } else {
+                CK(cudaEventRecord(e[5], L.stream));
+            }
+            return;
+        }
         for (int col = 0; col < out.ncol && k && before + k <= rec_cap; ++col)
             CK(cudaMemcpyAsync((char*)out.col[col] + before * out.width[col], chunk_col[col]->p, k * out.width[col], cudaMemcpyDeviceToHost, L.stream));
         CK(cudaEventRecord(e[5], L.stream));
@@ -1189,11 +1318,17 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
             q.erase(q.begin());
         }
         for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
+        const std::string werr = W.finish();
+        if (!werr.empty()) throw CudaError(werr);
+        if (widen && getenv("MONI_GPU_TRACE"))
+            fprintf(stderr, "[moni-gpu trace] gpu %d widened %.1f MB of records on %d host threads in %.2f ms (%.1f GB/s written)\n", R.dev,
+                    W.bytes / 1e6, moni::WidenPool::get().threads(), W.busy_ms, W.busy_ms > 0 ? W.bytes / W.busy_ms / 1e6 : 0.0);
     } catch (...) {
         // a bad offset found mid-batch (or a CUDA failure): the other GPUs stop, and nothing may still be writing the caller's
         // buffers when we return
         feed.fail();
         for (Lane& L : R.lanes) cudaStreamSynchronize(L.stream);
+        W.finish();
         throw;
     }
     if (!done.empty() && getenv("MONI_GPU_TRACE")) {      // per-chunk timeline (ms since the first event): where the pipeline idles
@@ -1226,6 +1361,7 @@ uint64_t run_batch(moni_gpu_index* idx, int mode, const char* seqs, const uint64
     feed.n_reads = n_reads;
     feed.chunk_bases = idx->opt.chunk_bases;
     feed.workers = G;
+    feed.widen = mode == kModeMems && out.fmt == 8 && widen_pool_threads() > 0;
     // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
     // would cut a 1 G-base batch into two chunks and leave lanes (and the copy/compute overlap) unused, so the minimum shrinks
     // until the batch makes at least two chunks per lane.
@@ -1308,6 +1444,7 @@ int moni_gpu_set_option(const char* key, const char* value) {
     else if (k == "chunk_min_reads" && v >= 0) g_opt.chunk_min_reads = (uint64_t)v;
     else if (k == "lanes" && v >= 1 && v <= kMaxLanes) g_opt.lanes = (uint32_t)v;
     else if (k == "dynamic" && v >= 0 && v <= 2) g_opt.dynamic = (int)v;
+    else if (k == "widen_threads" && v >= -1 && v <= 256) { g_opt.widen_threads = (int)v; g_widen_ready.store(false); }
     else if (k == "l2_fetch" && (v == 0 || v == 32 || v == 64 || v == 128)) g_opt.l2_fetch = (uint32_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }
     return 0;

@@ -712,6 +712,50 @@ def test_populate_seeds_equals_reference(case, m, oracle_mod, tmp_path):
     ix.close()
 
 
+def test_mems_u64_widened_on_host_equals_link_copy(m, oracle_mod):
+    """moni_gpu_mems with its records crossing the link packed and widened by host threads (option widen_threads, the default where
+    the process may use 4 or more CPUs) against the same call with the u64 columns copied as they are (widen_threads = 0) and
+    against the oracle: chunks of reads shorter than 256 bases (2-byte records), shorter than 65536 (4-byte) and longer (two u32
+    columns) in one batch, over several lanes, on one GPU and sharded over three replicas."""
+    import synth
+    pre = os.path.join(GOLDEN, "pan4.fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = [r for r in synth.short_reads(text, 6000, 100, 21, err=0.03)]
+    reads += synth.long_reads(text, 60, 22, mean=2000, sd=800, lo=300, hi=5000)
+    reads += [r for r in synth.short_reads(text, 3000, 250, 23, err=0.02)]
+    reads.append(np.tile(text[:20000], 4)[:70000])          # a read of 65536 bases or more: u32 columns
+    reads += [r for r in synth.short_reads(text, 2000, 60, 24, err=0.05)]
+    reads.insert(5, np.zeros(0, np.uint8))
+    flat, offs = m.pack_reads(reads)
+    m.set_option("chunk_bases", 50_000)
+    m.set_option("chunk_min_reads", 1)
+    try:
+        one = m.MoniIndex(pre)
+        three = m.MoniIndex(pre, gpus=[0, 0, 0])
+    finally:
+        m.set_option("chunk_bases", 1 << 24)
+        m.set_option("chunk_min_reads", 96 * 1024)
+    want = orc.mems(flat, offs)
+    try:
+        for threads in (0, 3, 1, -1):
+            m.set_option("widen_threads", threads)
+            for ix in (one, three):
+                got = ix.maxrimal_exact_matches(flat, offs)
+                assert all(np.array_equal(x, y) for x, y in zip(got, want)), threads
+        # capacity error path with widening on: offsets still say how much is needed
+        m.set_option("widen_threads", 2)
+        mo = np.zeros(len(reads) + 1, np.uint64)
+        small = np.zeros(16, np.uint64)
+        with pytest.raises(m.MoniGpuError) as e:
+            one.maxrimal_exact_matches(flat, offs, out=(mo, small, small.copy()))
+        assert e.value.code == -4 and int(mo[-1]) == int(want[0][-1])
+    finally:
+        m.set_option("widen_threads", -1)
+    one.close()
+    three.close()
+
+
 def test_index_larger_than_l2_against_reference_binaries(m, tmp_path):
     """BASELINE configs[2] (cfg3: n = 1.28 G, 4.8 GB image, far larger than the 126 MB L2) when its index travels with the snapshot
     (data/cfg3, what bench.py times): 20 000 reads sampled from the text through the CUDA path and through the unmodified reference
@@ -740,6 +784,47 @@ def test_index_larger_than_l2_against_reference_binaries(m, tmp_path):
     synth.write_fastq_matrix(fq, reads)
     build_index.run_reference("ms", pre, fq, os.path.join(str(tmp_path), "ref"), threads=os.cpu_count() or 1)
     build_index.run_reference("mems", pre, fq, os.path.join(str(tmp_path), "ref"), threads=os.cpu_count() or 1)
+    _, _, pv = refparse.parse_values(os.path.join(str(tmp_path), "ref.pointers"))
+    _, _, lv = refparse.parse_values(os.path.join(str(tmp_path), "ref.lengths"))
+    assert np.array_equal(pv, ptr) and np.array_equal(lv, ln)
+    _, cnt, qo, ql = refparse.parse_mems(os.path.join(str(tmp_path), "ref.mems"))
+    assert np.array_equal(cnt.astype(np.int64), np.diff(mo.astype(np.int64)))
+    assert np.array_equal(qo, mp) and np.array_equal(ql, ml)
+
+
+def test_index_larger_than_l2_built_on_the_box(m, tmp_path):
+    """An index whose image (move table + text, > 300 MB) does not fit the 126 MB L2, built on the spot with the unmodified reference
+    builder (8 x 20 Mbp, about a minute): 30 000 paired reads through the CUDA path (all result forms) and through the unmodified
+    reference `ms` / `mems` binaries -- pointers, lengths and MEM records equal number by number.  Unlike the cfg3 test above it
+    needs nothing that does not travel with the snapshot, so it runs wherever the GPU suite runs."""
+    import build_index
+    import refparse
+    import synth
+    import workloads
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "bin", "rlebwt_ms_build")):
+        pytest.skip("reference builder binaries not present")
+    recs = synth.pangenome(20_000_000, 8, 55, 1e-3, 1e-4)
+    fa = str(tmp_path / "l2.fa")
+    synth.write_fasta(fa, recs)
+    build_index.build_index(fa)
+    text = synth.text_of(recs)
+    del recs
+    reads = workloads.paired_reads(text, 15_000, 150, 56)
+    flat, offs = m.pack_reads(reads)
+    ix = m.MoniIndex(fa)
+    assert ix.device_bytes > 300_000_000 and ix.n > 150_000_000
+    ptr, ln = ix.matching_statistics(flat, offs)
+    mo, mp, ml = ix.maxrimal_exact_matches(flat, offs)
+    ro, rq, rl, rp = ix.matching_statistics_runs(flat, offs)
+    xp, xl = m.expand_runs(offs, ro, rq, rl, rp)
+    assert np.array_equal(xp, ptr) and np.array_equal(xl, ln)
+    po, prec = ix.maxrimal_exact_matches_packed16(flat, offs)
+    assert np.array_equal(po, mo) and np.array_equal(prec >> 8, mp) and np.array_equal(prec & 0xFF, ml)
+    ix.close()
+    fq = os.path.join(str(tmp_path), "s.fq")
+    synth.write_fastq_matrix(fq, reads)
+    build_index.run_reference("ms", fa, fq, os.path.join(str(tmp_path), "ref"), threads=os.cpu_count() or 1)
+    build_index.run_reference("mems", fa, fq, os.path.join(str(tmp_path), "ref"), threads=os.cpu_count() or 1)
     _, _, pv = refparse.parse_values(os.path.join(str(tmp_path), "ref.pointers"))
     _, _, lv = refparse.parse_values(os.path.join(str(tmp_path), "ref.lengths"))
     assert np.array_equal(pv, ptr) and np.array_equal(lv, ln)
