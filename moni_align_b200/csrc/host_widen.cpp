@@ -54,6 +54,37 @@ __attribute__((target("avx2"))) void column_avx2_u32(const uint32_t* src, uint64
     for (; i < k; ++i) out[i] = ((uint64_t)src[i] >> shift) & mask;
 }
 
+constexpr uint64_t kWrapFrom = (1ull << 40) - (1ull << 31);
+
+inline uint64_t decode40(uint32_t lo, uint8_t hi) {
+    const uint64_t v = (uint64_t)lo | ((uint64_t)hi << 32);
+    return v >= kWrapFrom ? v - (1ull << 40) : v;
+}
+
+void pointers_sse2(const uint32_t* lo, const uint8_t* hi, uint64_t k, uint64_t* out) {
+    uint64_t i = 0;
+    while (i < k && ((uintptr_t)(out + i) & 15u)) { out[i] = decode40(lo[i], hi[i]); ++i; }
+    for (; i + 2 <= k; i += 2)
+        _mm_stream_si128((__m128i*)(out + i), _mm_set_epi64x((long long)decode40(lo[i + 1], hi[i + 1]), (long long)decode40(lo[i], hi[i])));
+    for (; i < k; ++i) out[i] = decode40(lo[i], hi[i]);
+}
+
+__attribute__((target("avx2"))) void pointers_avx2(const uint32_t* lo, const uint8_t* hi, uint64_t k, uint64_t* out) {
+    uint64_t i = 0;
+    while (i < k && ((uintptr_t)(out + i) & 31u)) { out[i] = decode40(lo[i], hi[i]); ++i; }
+    const __m256i thr = _mm256_set1_epi64x((long long)(kWrapFrom - 1)), wrap = _mm256_set1_epi64x(1ll << 40);
+    for (; i + 4 <= k; i += 4) {
+        const __m256i l = _mm256_cvtepu32_epi64(_mm_loadu_si128((const __m128i*)(lo + i)));
+        int h4;
+        __builtin_memcpy(&h4, hi + i, 4);
+        const __m256i h = _mm256_slli_epi64(_mm256_cvtepu8_epi64(_mm_cvtsi32_si128(h4)), 32);
+        __m256i v = _mm256_or_si256(l, h);                                  // < 2^40: signed compare is fine
+        v = _mm256_sub_epi64(v, _mm256_and_si256(_mm256_cmpgt_epi64(v, thr), wrap));
+        _mm256_stream_si256((__m256i*)(out + i), v);
+    }
+    for (; i < k; ++i) out[i] = decode40(lo[i], hi[i]);
+}
+
 const bool g_avx2 = __builtin_cpu_supports("avx2");
 
 void column(const uint16_t* src, uint64_t k, unsigned shift, uint64_t mask, uint64_t* out) {
@@ -84,6 +115,13 @@ void widen_records(int cfmt, const void* src, const void* src2, uint64_t k, uint
             column((const uint32_t*)src2 + a, n, 0, 0xFFFFFFFFFFFFFFFFull, dlen + a);
         }
     }
+    _mm_sfence();
+}
+
+void widen_ms(const uint32_t* lo, const uint8_t* hi, const uint16_t* len, uint64_t k, uint64_t* dptr, uint64_t* dlen) {
+    if (g_avx2) pointers_avx2(lo, hi, k, dptr);
+    else pointers_sse2(lo, hi, k, dptr);
+    column(len, k, 0, 0xFFFFFFFFFFFFFFFFull, dlen);
     _mm_sfence();
 }
 
@@ -172,6 +210,16 @@ void WidenPool::widen(int cfmt, const void* src, const void* src2, uint64_t k, u
     parallel_for(slices, [&](int s) {
         const uint64_t a = (uint64_t)s * per, n = std::min(per, k - a);
         widen_records(cfmt, (const char*)src + a * w, src2 ? (const char*)src2 + a * 4 : nullptr, n, dpos + a, dlen + a);
+    });
+}
+
+void WidenPool::widen_ms(const uint32_t* lo, const uint8_t* hi, const uint16_t* len, uint64_t k, uint64_t* dptr, uint64_t* dlen) {
+    if (!k) return;
+    const uint64_t parts = (uint64_t)std::max(n_, 1) * 4;
+    const uint64_t per = std::max<uint64_t>(1 << 15, ((k + parts - 1) / parts + 63) & ~63ull);
+    parallel_for((int)((k + per - 1) / per), [&](int s) {
+        const uint64_t a = (uint64_t)s * per, n = std::min(per, k - a);
+        moni::widen_ms(lo + a, hi + a, len + a, n, dptr + a, dlen + a);
     });
 }
 

@@ -14,6 +14,11 @@ namespace moni {
 //       4 = two u32 columns (src = query offsets, src2 = lengths).  Writes dpos[0..k), dlen[0..k).
 void widen_records(int cfmt, const void* src, const void* src2, uint64_t k, uint64_t* dpos, uint64_t* dlen);
 
+// moni_gpu_ms: the 7-byte-per-base form of moni_gpu_ms_packed (pointer low word, pointer bits 32..39, u16 length) to the two u64
+// vectors.  A 40-bit value >= 2^40 - 2^31 is one of the reference's wrapped pointers 2^64 - j (include/moni_gpu.h) and is
+// widened as such.
+void widen_ms(const uint32_t* lo, const uint8_t* hi, const uint16_t* len, uint64_t k, uint64_t* dptr, uint64_t* dlen);
+
 // Process-wide pool.  threads() == 0: widening is off (too few CPUs allowed, or option "widen_threads" = 0).
 class WidenPool {
   public:
@@ -24,6 +29,7 @@ class WidenPool {
     void parallel_for(int n_slices, const std::function<void(int)>& fn);
     // widen_records split over the pool
     void widen(int cfmt, const void* src, const void* src2, uint64_t k, uint64_t* dpos, uint64_t* dlen);
+    void widen_ms(const uint32_t* lo, const uint8_t* hi, const uint16_t* len, uint64_t k, uint64_t* dptr, uint64_t* dlen);
     static int default_threads();                              // from the CPUs this process may run on
 
   private:

@@ -1117,7 +1117,7 @@ class Widener {
     struct Job {
         cudaEvent_t ev;
         int cfmt;
-        const void *src, *src2;
+        const void *src, *src2, *src3;      // cfmt 7 (ms): pointer low words, pointer bits 32..39, u16 lengths
         uint64_t k;
         uint64_t *dpos, *dlen;
         size_t lane;
@@ -1162,7 +1162,8 @@ class Widener {
                 if (err_.empty()) err_ = std::string("cudaEventSynchronize (widening): ") + cudaGetErrorString(e);
             } else if (err_.empty()) {
                 const double t0 = wall_s();
-                moni::WidenPool::get().widen(j.cfmt, j.src, j.src2, j.k, j.dpos, j.dlen);
+                if (j.cfmt == 7) moni::WidenPool::get().widen_ms((const uint32_t*)j.src, (const uint8_t*)j.src2, (const uint16_t*)j.src3, j.k, j.dpos, j.dlen);
+                else moni::WidenPool::get().widen(j.cfmt, j.src, j.src2, j.k, j.dpos, j.dlen);
                 busy_ms += (wall_s() - t0) * 1e3;
                 bytes += j.k * 16;
             }
@@ -1197,8 +1198,10 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
     const uint64_t rec_cap = out.cap;
     struct InFlight { ChunkPlan p; size_t c, lane, ev_at; int cfmt; };
     const bool widen = feed.widen && mems && out.fmt == 8;
+    // moni_gpu_ms (u64 vectors): 7 bytes per base cross the link (the moni_gpu_ms_packed form) and host threads widen them, chunk by chunk
+    const bool widen_ms = feed.widen && mode == kModeMs && out.fmt != 7 && idx->hdr.n <= (1ull << 40) - (1ull << 31);
     Widener W(R.dev, R.lanes.size());
-    if (widen) W.start();
+    if (widen || widen_ms) W.start();
     std::vector<InFlight> done;
     std::vector<InFlight> q;                 // chunks enqueued and not yet finished, oldest first (at most one per lane)
     const size_t kLanes_ = R.lanes.size();
@@ -1235,10 +1238,24 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
             launch_compact(S, p, cfmt, L.stream);
             CK(cudaEventRecord(e[4], L.stream));
         } else {
-            const bool packed = out.fmt == 7;      // moni_gpu_ms_packed: col[] = u32 pointer halves, u8 pointer bits 32..39, u16 lengths
-            if (packed && p.max_len > 0xFFFFull) throw BadBatch("packed matching statistics need reads shorter than 65536 bases");
+            const bool staged = widen_ms && p.max_len <= 0xFFFFull;      // this chunk leaves packed and is widened on the host
+            const bool packed = out.fmt == 7 || staged;      // moni_gpu_ms_packed: col[] = u32 pointer halves, u8 pointer bits 32..39, u16 lengths
+            if (out.fmt == 7 && p.max_len > 0xFFFFull) throw BadBatch("packed matching statistics need reads shorter than 65536 bases");
             launch_expand(S, p, L.stream, packed);
             CK(cudaEventRecord(e[4], L.stream));
+            if (p.bases && staged) {
+                W.wait_lane(f.lane);                         // the lane's previous chunk has left the staging buffer
+                const size_t a4 = (p.bases * 4 + 63) & ~(size_t)63, a1 = (p.bases + 63) & ~(size_t)63, a2 = (p.bases * 2 + 63) & ~(size_t)63;
+                L.stage.reserve(a4 + a1 + a2);
+                char* const st0 = (char*)L.stage.p;
+                CK(cudaMemcpyAsync(st0, S.out_ptr.p, p.bases * 4, cudaMemcpyDeviceToHost, L.stream));
+                CK(cudaMemcpyAsync(st0 + a4, S.out_hi.p, p.bases, cudaMemcpyDeviceToHost, L.stream));
+                CK(cudaMemcpyAsync(st0 + a4 + a1, S.out_len.p, p.bases * 2, cudaMemcpyDeviceToHost, L.stream));
+                CK(cudaEventRecord(e[5], L.stream));
+                W.push({e[5], 7, st0, st0 + a4, st0 + a4 + a1, p.bases, pointers + p.base, lengths + p.base, f.lane});
+                q.push_back(f);
+                return;
+            }
             if (p.bases && packed) {
                 DevBuf* const src[3] = {&S.out_ptr, &S.out_hi, &S.out_len};
                 for (int k = 0; k < 3; ++k)
@@ -1282,7 +1299,7 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
                 CK(cudaMemcpyAsync(L.stage.p, S.mem_pos.p, k * w, cudaMemcpyDeviceToHost, L.stream));
                 if (f.cfmt == 4) CK(cudaMemcpyAsync((char*)L.stage.p + col_bytes, S.mem_len.p, k * w, cudaMemcpyDeviceToHost, L.stream));
                 CK(cudaEventRecord(e[5], L.stream));
-                W.push({e[5], f.cfmt, L.stage.p, f.cfmt == 4 ? (char*)L.stage.p + col_bytes : nullptr, k, (uint64_t*)out.col[0] + before,
+                W.push({e[5], f.cfmt, L.stage.p, f.cfmt == 4 ? (char*)L.stage.p + col_bytes : nullptr, nullptr, k, (uint64_t*)out.col[0] + before,
                         (uint64_t*)out.col[1] + before, f.lane});
             } else {
                 CK(cudaEventRecord(e[5], L.stream));
@@ -1320,7 +1337,7 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
         for (Lane& L : R.lanes) CK(cudaStreamSynchronize(L.stream));
         const std::string werr = W.finish();
         if (!werr.empty()) throw CudaError(werr);
-        if (widen && getenv("MONI_GPU_TRACE"))
+        if ((widen || widen_ms) && getenv("MONI_GPU_TRACE"))
             fprintf(stderr, "[moni-gpu trace] gpu %d widened %.1f MB of records on %d host threads in %.2f ms (%.1f GB/s written)\n", R.dev,
                     W.bytes / 1e6, moni::WidenPool::get().threads(), W.busy_ms, W.busy_ms > 0 ? W.bytes / W.busy_ms / 1e6 : 0.0);
     } catch (...) {
@@ -1361,7 +1378,7 @@ uint64_t run_batch(moni_gpu_index* idx, int mode, const char* seqs, const uint64
     feed.n_reads = n_reads;
     feed.chunk_bases = idx->opt.chunk_bases;
     feed.workers = G;
-    feed.widen = mode == kModeMems && out.fmt == 8 && widen_pool_threads() > 0;
+    feed.widen = ((mode == kModeMems && out.fmt == 8) || (mode == kModeMs && out.fmt != 7)) && widen_pool_threads() > 0;
     // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
     // would cut a 1 G-base batch into two chunks and leave lanes (and the copy/compute overlap) unused, so the minimum shrinks
     // until the batch makes at least two chunks per lane.

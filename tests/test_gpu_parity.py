@@ -737,12 +737,26 @@ def test_mems_u64_widened_on_host_equals_link_copy(m, oracle_mod):
         m.set_option("chunk_bases", 1 << 24)
         m.set_option("chunk_min_reads", 96 * 1024)
     want = orc.mems(flat, offs)
+    want_ms = orc.ms(flat, offs)
     try:
         for threads in (0, 3, 1, -1):
             m.set_option("widen_threads", threads)
             for ix in (one, three):
                 got = ix.maxrimal_exact_matches(flat, offs)
                 assert all(np.array_equal(x, y) for x, y in zip(got, want)), threads
+                # moni_gpu_ms: 7 bytes per base cross the link and are widened (chunks with a read of 65536 bases or more go as u64)
+                gp, gl = ix.matching_statistics(flat, offs)
+                assert np.array_equal(gp, want_ms[0]) and np.array_equal(gl, want_ms[1]), threads
+        # wrapped pointers (2^64 - k after absent symbols) survive the 40-bit form: the withN reads, widened and not
+        names, seqs = read_fastq(os.path.join(GOLDEN, "withN.fq"))
+        wflat, woffs = pack(seqs)
+        wn = m.MoniIndex(os.path.join(GOLDEN, "withN.fa"))
+        for threads in (0, 2):
+            m.set_option("widen_threads", threads)
+            p2, l2 = wn.matching_statistics(wflat, woffs)
+            assert m.format_ms(names, woffs, p2) == open(os.path.join(GOLDEN, "withN.pointers"), "rb").read()
+            assert m.format_ms(names, woffs, l2) == open(os.path.join(GOLDEN, "withN.lengths"), "rb").read()
+        wn.close()
         # capacity error path with widening on: offsets still say how much is needed
         m.set_option("widen_threads", 2)
         mo = np.zeros(len(reads) + 1, np.uint64)
