@@ -260,7 +260,7 @@ def cpu_baseline_and_parity(args, prefix, reads_flat, n_reads, read_len, gpu_mem
 
 
 API_NAMES = {"mems_u64": "moni_gpu_mems", "mems_u64_link": "moni_gpu_mems", "mems_u32": "moni_gpu_mems32", "mems_packed32": "moni_gpu_mems_packed",
-             "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed",
+             "mems_packed16": "moni_gpu_mems_packed16", "ms_u64": "moni_gpu_ms", "ms_u64_link": "moni_gpu_ms", "ms_packed": "moni_gpu_ms_packed",
              "ms_runs": "moni_gpu_ms_runs", "ms_runs_packed": "moni_gpu_ms_runs_packed"}
 
 
@@ -399,16 +399,21 @@ def ours_arm(args) -> None:
         log(f"rank {rank}: {getattr(call, '__name__', 'call')} per-step wall ms: " + " ".join(f"{x:.1f}" for x in per_step))
         return {"dev": max_over_ranks(dev_sum, dev), "wall": max_over_ranks(wall, dev), "stage": stage, "per_step": per_step}
 
+    # host threads the library uses to widen packed results into u64 columns (moni_gpu_mems, moni_gpu_ms)
+    allowed_cpus = len(os.sched_getaffinity(0))
+    widen_threads = next((int(o.split("=", 1)[1]) for o in args.opt if o.startswith("widen_threads=")), -1)
+    if widen_threads < 0:
+        widen_threads = 0 if allowed_cpus < 4 else min(16, allowed_cpus * 2 // 3)     # WidenPool::default_threads (csrc/host_widen.cpp)
+        if world > 1:
+            # the ranks of one box share its CPUs and the library cannot see its sibling processes: give each rank its share
+            widen_threads = max(1, widen_threads // world) if allowed_cpus // world >= 2 else 0
+            m.set_option("widen_threads", widen_threads)
     legs = {}
     # mems, u64 records: the reference's own record type (std::pair<size_t,size_t>, src/mems.cpp:277-279)
     legs["mems_u64"] = e2e_leg(ix.maxrimal_exact_matches, (h_mo, pool_a, pool_b))
     same = {"mems_u64": bool(np.array_equal(h_mo, mo) and np.array_equal(pool_a[:n_mems], mp) and np.array_equal(pool_b[:n_mems], ml))}
     gpu_mems = (h_mo.copy(), pool_a[:n_mems].copy(), pool_b[:n_mems].copy())      # for the parity sample: what the ABI call returned
     # A/B of the same call with the u64 columns crossing the link as they are (option widen_threads = 0) instead of packed + widened by host threads
-    allowed_cpus = len(os.sched_getaffinity(0))
-    widen_threads = next((int(o.split("=", 1)[1]) for o in args.opt if o.startswith("widen_threads=")), -1)
-    if widen_threads < 0:
-        widen_threads = 0 if allowed_cpus < 4 else min(16, allowed_cpus * 2 // 3)     # WidenPool::default_threads (csrc/host_widen.cpp)
     if widen_threads > 0:
         h_mo[:] = 0
         m.set_option("widen_threads", 0)
@@ -433,6 +438,13 @@ def ours_arm(args) -> None:
     legs["ms_u64"] = e2e_leg(ix.matching_statistics, (pool_a, pool_b))
     same["ms_u64"] = bool(np.array_equal(pool_a[:total], r_ptr) and np.array_equal(pool_b[:total], r_len))
     gpu_ms = (pool_a[:total].copy(), pool_b[:total].copy()) if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
+    if widen_threads > 0:
+        m.set_option("widen_threads", 0)
+        try:
+            legs["ms_u64_link"] = e2e_leg(ix.matching_statistics, (pool_a, pool_b))
+        finally:
+            m.set_option("widen_threads", widen_threads)
+        same["ms_u64_link"] = bool(np.array_equal(pool_a[:total], r_ptr) and np.array_equal(pool_b[:total], r_len))
     lo, hi, l16 = pool_a.view(np.uint32)[:total], pool_b.view(np.uint8)[:total], pool_b.view(np.uint16)[total:2 * total]
     legs["ms_packed"] = e2e_leg(ix.matching_statistics_packed, (lo, hi, l16))
     same["ms_packed"] = bool(np.array_equal(m.unpack_pointers(lo, hi), r_ptr) and np.array_equal(l16, r_len))
@@ -532,7 +544,7 @@ def ours_arm(args) -> None:
     link_rec = 16 if widen_threads == 0 else (2 if int(read_len) < 256 else 4 if int(read_len) < 65536 else 8)   # bytes per record that cross the link
     d2h = {"mems_u64": 8 * (n_reads + 1) + link_rec * n_mems, "mems_u64_link": 8 * (n_reads + 1) + 16 * n_mems, "mems_u32": 8 * (n_reads + 1) + 8 * n_mems,
            "mems_packed32": 8 * (n_reads + 1) + 4 * n_mems, "mems_packed16": 8 * (n_reads + 1) + 2 * n_mems,
-           "ms_u64": 16 * total, "ms_packed": 7 * total, "ms_runs": 8 * (n_reads + 1) + 16 * n_runs,
+           "ms_u64": (7 if widen_threads > 0 and int(read_len) < 65536 else 16) * total, "ms_u64_link": 16 * total, "ms_packed": 7 * total, "ms_runs": 8 * (n_reads + 1) + 16 * n_runs,
            "ms_runs_packed": 8 * (n_reads + 1) + 9 * n_runs}
     api = API_NAMES
     h2d = int(total)            # reads of one length: the library computes their offsets on the device (k_uniform_offsets)
@@ -609,7 +621,8 @@ def ours_arm(args) -> None:
         **{"e2e_" + k: leg_json(k) for k in legs if k.startswith("mems_") and k != "mems_u64"},
         "ms": {"value": value_ms, "unit": "reads/s", "bases_per_s": value_ms * read_len, "ms_per_step": dev_ms_ms / args.steps,
                "stage_ms_per_step": {"pass1": kms_ms[0] / args.steps, "pass2": kms_ms[1] / args.steps, "expand": kms_ms[2] / args.steps},
-               "e2e": leg_json("ms_u64"), "e2e_packed": leg_json("ms_packed"), "e2e_runs": leg_json("ms_runs"),
+               "e2e": {**leg_json("ms_u64"), "host_widen_threads": widen_threads, "host_bytes_per_base": 16},
+               **({"e2e_u64_link": leg_json("ms_u64_link")} if "ms_u64_link" in legs else {}), "e2e_packed": leg_json("ms_packed"), "e2e_runs": leg_json("ms_runs"),
                "e2e_runs_packed": leg_json("ms_runs_packed"), "runs_per_step": n_runs},
         "mem_records_per_step": n_mems,
         "gpu_launches": int(launches), "gpu_launches_ms_leg": int(launches_ms), "options": args.opt, "cpu_placement": numa_note,

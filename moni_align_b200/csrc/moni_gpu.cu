@@ -576,6 +576,7 @@ namespace {
 thread_local std::string g_err;
 std::atomic<uint64_t> g_launches{0};
 std::atomic<bool> g_widen_ready{false};   // the widening pool has the size option "widen_threads" asks for
+std::atomic<int> g_dyn_rpt{2};            // option "dyn_reads_per_lane": reads per thread the persistent kernels are sized for
 std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
@@ -840,13 +841,18 @@ void launch_prepare(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
     CK(cudaGetLastError());
 }
 
-// Blocks of one resident wave of a persistent kernel (never more than the chunk has reads for).
+// Blocks of a persistent kernel: at most one resident wave, and few enough that a thread takes several reads of the chunk ("dyn_reads_per_lane",
+// default 2).  A read is a chain of dependent steps, so a kernel with as many threads as reads lasts as long as its longest read while the
+// threads of the short ones idle (ONT-like reads: longest 24.8 kbp, mean 10 kbp -> 40 % of the thread-steps used); with the reads handed out
+// longest first and fewer threads than reads, a thread that finishes early takes another read and the threads end together.  The chains in
+// flight that the memory system needs come from the lanes' kernels running side by side.
 template <typename K>
 unsigned persistent_grid(const Replica& R, K kernel, uint64_t n_reads) {
     int per_sm = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlock, 0));
     const uint64_t wave = (uint64_t)std::max(per_sm, 1) * (uint64_t)std::max(R.sms, 1);
-    return (unsigned)std::min<uint64_t>(wave, (n_reads + kBlock - 1) / kBlock);
+    const uint64_t per_block = (uint64_t)kBlock * (uint64_t)std::max(g_dyn_rpt.load(), 1);
+    return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(wave, (n_reads + per_block - 1) / per_block));
 }
 
 bool use_dynamic(const Replica& R, const ChunkPlan& p) { return R.dynamic == 1 || (R.dynamic == 2 && p.ragged()); }
@@ -1461,6 +1467,7 @@ int moni_gpu_set_option(const char* key, const char* value) {
     else if (k == "chunk_min_reads" && v >= 0) g_opt.chunk_min_reads = (uint64_t)v;
     else if (k == "lanes" && v >= 1 && v <= kMaxLanes) g_opt.lanes = (uint32_t)v;
     else if (k == "dynamic" && v >= 0 && v <= 2) g_opt.dynamic = (int)v;
+    else if (k == "dyn_reads_per_lane" && v >= 1 && v <= 64) g_dyn_rpt.store((int)v);
     else if (k == "widen_threads" && v >= -1 && v <= 256) { g_opt.widen_threads = (int)v; g_widen_ready.store(false); }
     else if (k == "l2_fetch" && (v == 0 || v == 32 || v == 64 || v == 128)) g_opt.l2_fetch = (uint32_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }

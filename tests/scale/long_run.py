@@ -109,9 +109,10 @@ def main():
     rec = m.pinned_empty(cap, np.uint32)
     RES["e2e"] = {}
     hashes = {}
-    dyns = [int(x) for x in args.dynamic.split(",")]
+    dyns = [int(x) for x in args.dynamic.split(",")]      # 0 / 1, or 1xx = persistent kernels sized for xx reads per thread
     for dyn in dyns:
-        m.set_option("dynamic", dyn)
+        m.set_option("dynamic", min(dyn, 1))
+        m.set_option("dyn_reads_per_lane", dyn - 100 if dyn >= 100 else 2)
         t = time.time()
         ix = m.MoniIndex(prefix, gpus=[0])
         load_s = time.time() - t

@@ -671,8 +671,9 @@ def test_dynamic_and_static_kernels_agree(case, m, oracle_mod):
     rng.shuffle(reads)
     flat, offs = m.pack_reads(reads)
     res = {}
-    for dyn in (0, 1):
-        m.set_option("dynamic", dyn)
+    for dyn in (0, 1, 11, 17):           # 11, 17: persistent kernels sized for 1 resp. 7 reads per thread (dyn_reads_per_lane; default 2)
+        m.set_option("dynamic", min(dyn, 1))
+        m.set_option("dyn_reads_per_lane", {11: 1, 17: 7}.get(dyn, 2))
         m.set_option("chunk_bases", 60000)
         m.set_option("chunk_min_reads", 200)
         try:
@@ -684,8 +685,10 @@ def test_dynamic_and_static_kernels_agree(case, m, oracle_mod):
         res[dyn] = (ix.matching_statistics(flat, offs), ix.maxrimal_exact_matches(flat, offs), ix.find_mems(flat, offs, 12),
                     ix.matching_statistics_runs(flat, offs))
         ix.close()
-    for a, b in zip(res[0], res[1]):
-        assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    m.set_option("dyn_reads_per_lane", 2)
+    for other in (1, 11, 17):
+        for a, b in zip(res[0], res[other]):
+            assert all(np.array_equal(x, y) for x, y in zip(a, b)), other
     wp, wl = orc.ms(flat, offs)
     assert np.array_equal(res[1][0][0], wp) and np.array_equal(res[1][0][1], wl)
     wm = orc.mems(flat, offs)
