@@ -577,6 +577,8 @@ thread_local std::string g_err;
 std::atomic<uint64_t> g_launches{0};
 std::atomic<bool> g_widen_ready{false};   // the widening pool has the size option "widen_threads" asks for
 std::atomic<int> g_dyn_rpt{2};            // option "dyn_reads_per_lane": reads per thread the persistent kernels are sized for
+std::atomic<int> g_ramp{0};               // option "ramp": 0 off (default: measured no better on 1 M ONT-like reads), 1 on, 2 = for batches of long reads
+std::atomic<int> g_guided{1};             // option "guided": chunks shrink towards the end of a batch of long reads
 std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
@@ -588,7 +590,7 @@ struct Options {
     uint64_t chunk_bases = 1ull << 24;
     uint64_t chunk_min_reads = 96 * 1024;
     uint32_t l2_fetch = 0;          // 0 = leave the device default
-    uint32_t lanes = 4;
+    uint32_t lanes = 0;             // chunks in flight per GPU; 0 = auto (4, or 6 for batches of long reads)
     int dynamic = 2;                // 0 = one read per lane, 1 = persistent kernels whose lanes pull reads, 2 = auto (pull when reads are ragged)
     int widen_threads = -1;         // host threads that widen packed MEM records into the caller's u64 columns; 0 = off (u64 over the link), -1 = auto
 };
@@ -676,16 +678,30 @@ struct Scratch {   // device buffers of one chunk
     }
     // HBM bytes per base of a chunk in this mode (plus a few dozen bytes per read): what bounds the chunk size on a device
     // whose memory is mostly taken (large indexes, several replicas or processes per GPU)
-    static double bytes_per_base(int mode) {
-        const double common = 1.0 + 8.0 + 1.0 / 8.0;                  // seqs, rptr, flags
-        switch (mode) {
-            case kModeMs: return (common + 8.0 + 16.0 + 1.0) * 1.125;     // rrec, out_ptr + out_len, out_hi
-            case kModeMems: return (common + 8.0 + 16.0) * 1.125;         // rec, mem_pos + mem_len
-            case kModeSeeds: return (common + 8.0 + 16.0 + 16.0) * 1.125; // + rec_ref, mem_ref
-            default: return (common + 8.0 + 16.0 + 1.0) * 1.125;          // runs: rrec, compacted columns
+    // bytes per record of the two compacted columns for a launch_compact format: records of one word need one narrow column
+    static void column_bytes(int fmt, size_t& pos_b, size_t& len_b) {
+        switch (fmt) {
+            case 1: pos_b = 2; len_b = 0; break;          // u16 (offset:8, length:8)
+            case 2: pos_b = 4; len_b = 0; break;          // u32 (offset:16, length:16)
+            case 8: pos_b = 8; len_b = 8; break;          // two u64 columns
+            default: pos_b = 4; len_b = 4; break;         // 4, 12 (seeds), 16 / 9 (runs): two u32 columns
         }
     }
-    void reserve(const ChunkPlan& p, int mode) {
+    static double bytes_per_base(int mode, int fmt = 8) {
+        const double common = 1.0 + 8.0 + 1.0 / 8.0;                  // seqs, rptr, flags
+        size_t pb = 8, lb = 8;
+        column_bytes(fmt, pb, lb);
+        switch (mode) {
+            case kModeMs: return (common + 8.0 + 16.0 + 1.0) * 1.125;     // rrec, out_ptr + out_len, out_hi
+            case kModeMems: return (common + 8.0 + (double)(pb + lb)) * 1.125;         // rec, mem_pos + mem_len
+            case kModeSeeds: return (common + 8.0 + 8.0 + 16.0) * 1.125;  // rec, mem_pos + mem_len (u32), rec_ref, mem_ref
+            default: return (common + 8.0 + 8.0 + 8.0 + 1.0) * 1.125;     // runs: rrec, two u32 columns, pointers, out_hi
+        }
+    }
+    // fmt: the launch_compact format the chunk's records will take (ignored for ms)
+    void reserve(const ChunkPlan& p, int mode, int fmt = 8) {
+        size_t pb = 8, lb = 8;
+        column_bytes(fmt, pb, lb);
         seqs.reserve(p.bases + 16);
         offs.reserve((p.n + 1) * 8);
         flags.reserve(p.flag_words() * 4);
@@ -701,8 +717,8 @@ struct Scratch {   // device buffers of one chunk
         }
         if (mode != kModeMs) {
             moff.reserve((p.n + 1) * 16);
-            mem_pos.reserve(p.bases * 8 + 16);
-            mem_len.reserve(p.bases * 8 + 16);
+            mem_pos.reserve(p.bases * pb + 16);
+            if (lb) mem_len.reserve(p.bases * lb + 16);
         }
         if (mode == kModeSeeds) { rec_ref.reserve(p.bases * 8 + 16); mem_ref.reserve(p.bases * 8 + 16); }
         if (mode == kModeRuns) { mem_ref.reserve(p.bases * 8 + 16); out_hi.reserve(p.bases + 16); }
@@ -1040,6 +1056,9 @@ struct ChunkFeed {
     std::vector<uint64_t> prefix{0};     // prefix[c] = records of chunks 0..c-1, valid for c <= known
     size_t known = 0;
     bool failed = false;
+    int lanes = 4;                       // chunks in flight per GPU in this call
+    bool ramp = false;                   // shorter first chunks (see next())
+    bool guided = true;                  // shrinking last chunks (see next())
     bool widen = false;                  // moni_gpu_mems: records cross the link packed, host threads widen them (host_widen.hpp)
 
     // every worker reports how many bases of scratch its GPU can take per lane; chunks are planned once all have (smallest wins)
@@ -1056,7 +1075,20 @@ struct ChunkFeed {
         std::lock_guard<std::mutex> lock(mu);
         if (failed) throw std::runtime_error("another GPU's part of the batch failed");
         if (next_read >= n_reads) return false;
-        p = plan_chunk(offsets, next_read, n_reads, std::min(chunk_bases, hard_cap), min_reads, hard_cap);
+        // ramp: the first chunk of every lane is cut shorter (1/L, 2/L, ... of the nominal size), so that the lanes -- which all start at
+        // once -- do not copy at the same time and compute at the same time for the rest of the batch, but spread over the period
+        uint64_t cb = std::min(chunk_bases, hard_cap), mr = min_reads, hc = hard_cap;
+        // guided: where the read-count rule decides the chunk size (long reads), chunks shrink with what is left of the batch, so that
+        // the batch does not end with one or two large chunks on a GPU whose other lanes have run dry
+        if (guided) mr = std::max<uint64_t>(std::min<uint64_t>(1024, min_reads), std::min(min_reads, (n_reads - next_read) / (2 * (uint64_t)std::max(lanes, 1) * (uint64_t)std::max(workers, 1))));
+        const uint64_t c_now = count.size();
+        if (ramp && lanes > 1 && c_now < (uint64_t)lanes) {
+            const uint64_t num = c_now + 1, den = (uint64_t)lanes;
+            cb = std::max<uint64_t>(1, cb * num / den);
+            mr = std::max<uint64_t>(1, mr * num / den);
+            hc = std::max<uint64_t>(1u << 16, hc * num / den);
+        }
+        p = plan_chunk(offsets, next_read, n_reads, cb, mr, hc);
         next_read += p.n;
         c = count.size();
         count.push_back(-1);
@@ -1210,15 +1242,15 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
     if (widen || widen_ms) W.start();
     std::vector<InFlight> done;
     std::vector<InFlight> q;                 // chunks enqueued and not yet finished, oldest first (at most one per lane)
-    const size_t kLanes_ = R.lanes.size();
+    const size_t kLanes_ = std::min<size_t>(R.lanes.size(), std::max(feed.lanes, 1));
     size_t issued = 0;
 
     auto enqueue = [&](const ChunkPlan& p, size_t c) {
         Lane& L = R.lanes[issued % kLanes_];
         Scratch& S = L.scratch;
-        S.reserve(p, mode);
         // format the chunk's records take on the device: the caller's, or -- when host threads widen them -- the narrowest that holds them
         const int cfmt = !widen ? out.fmt : (p.max_len <= 0xFFull ? 1 : p.max_len <= 0xFFFFull ? 2 : 4);
+        S.reserve(p, mode, cfmt);
         InFlight f{p, c, issued % kLanes_, L.used, cfmt};
         ++issued;
         L.take();
@@ -1329,7 +1361,7 @@ void run_worker(moni_gpu_index* idx, Replica& R, int mode, const char* seqs, con
             CK(cudaMemGetInfo(&free_b, &total_b));
             for (Lane& L : R.lanes) held += L.scratch.held();
             const double share = 0.85 * (double)(free_b + held) / (double)kLanes_;
-            feed.arrive((uint64_t)(share / Scratch::bytes_per_base(mode)));
+            feed.arrive((uint64_t)(share / Scratch::bytes_per_base(mode, widen ? 4 : out.fmt)));
         }
         for (;;) {
             ChunkPlan p;
@@ -1388,7 +1420,13 @@ uint64_t run_batch(moni_gpu_index* idx, int mode, const char* seqs, const uint64
     // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
     // would cut a 1 G-base batch into two chunks and leave lanes (and the copy/compute overlap) unused, so the minimum shrinks
     // until the batch makes at least two chunks per lane.
-    feed.min_reads = std::min<uint64_t>(idx->opt.chunk_min_reads, std::max<uint64_t>(1024, n_reads / (2 * idx->opt.lanes * (uint64_t)G)));
+    // Lanes: option "lanes", or by default 4 for short reads and 6 for long ones -- a long read is a long chain of dependent steps, the
+    // persistent kernels run with fewer threads than reads, and what keeps the memory system busy is the number of reads in flight.
+    const uint64_t mean_len = n_reads ? (offsets[n_reads] - offsets[0]) / n_reads : 0;
+    feed.lanes = idx->opt.lanes ? (int)idx->opt.lanes : (mean_len >= 4096 ? 6 : 4);
+    feed.guided = g_guided.load() != 0;
+    feed.ramp = g_ramp.load() == 1 || (g_ramp.load() == 2 && mean_len >= 4096 && G == 1);
+    feed.min_reads = std::min<uint64_t>(idx->opt.chunk_min_reads, std::max<uint64_t>(1024, n_reads / (2 * (uint64_t)feed.lanes * (uint64_t)G)));
     if (G == 1) {
         run_worker(idx, *idx->reps[0], mode, seqs, offsets, n_reads, feed, pointers, lengths, out);
     } else {
@@ -1465,9 +1503,11 @@ int moni_gpu_set_option(const char* key, const char* value) {
     else if (k == "count") { g_opt.count = v != 0; g_count.store(v != 0); }
     else if (k == "chunk_bases" && v >= 1 && v <= (1ll << 31)) g_opt.chunk_bases = (uint64_t)v;
     else if (k == "chunk_min_reads" && v >= 0) g_opt.chunk_min_reads = (uint64_t)v;
-    else if (k == "lanes" && v >= 1 && v <= kMaxLanes) g_opt.lanes = (uint32_t)v;
+    else if (k == "lanes" && v >= 0 && v <= kMaxLanes) g_opt.lanes = (uint32_t)v;
     else if (k == "dynamic" && v >= 0 && v <= 2) g_opt.dynamic = (int)v;
     else if (k == "dyn_reads_per_lane" && v >= 1 && v <= 64) g_dyn_rpt.store((int)v);
+    else if (k == "ramp" && v >= 0 && v <= 2) g_ramp.store((int)v);
+    else if (k == "guided" && v >= 0 && v <= 1) g_guided.store((int)v);
     else if (k == "widen_threads" && v >= -1 && v <= 256) { g_opt.widen_threads = (int)v; g_widen_ready.store(false); }
     else if (k == "l2_fetch" && (v == 0 || v == 32 || v == 64 || v == 128)) g_opt.l2_fetch = (uint32_t)v;
     else { g_err = "unknown option or value out of range: " + k; return MONI_GPU_EINVAL; }
@@ -1614,7 +1654,7 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             CK(cudaSetDevice(R->dev));
             CK(cudaDeviceGetAttribute(&R->sms, cudaDevAttrMultiProcessorCount, R->dev));
             if (idx->opt.l2_fetch) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, idx->opt.l2_fetch));
-            R->lanes.resize(idx->opt.lanes);
+            R->lanes.resize(idx->opt.lanes ? idx->opt.lanes : 6);
             for (Lane& L : R->lanes) CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
             cudaStream_t st = R->stream();
             const Replica* src = g ? idx->reps[0].get() : nullptr;      // replica 0 is complete (synchronized) by now

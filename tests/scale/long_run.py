@@ -109,14 +109,36 @@ def main():
     rec = m.pinned_empty(cap, np.uint32)
     RES["e2e"] = {}
     hashes = {}
-    dyns = [int(x) for x in args.dynamic.split(",")]      # 0 / 1, or 1xx = persistent kernels sized for xx reads per thread
-    for dyn in dyns:
-        m.set_option("dynamic", min(dyn, 1))
-        m.set_option("dyn_reads_per_lane", dyn - 100 if dyn >= 100 else 2)
+    # 0 / 1, or 1xx = persistent kernels sized for xx reads per thread, or L<lanes>R<reads per thread> (e.g. L8R3)
+    def parse_dyn(tok):
+        if tok.startswith("L"):                 # L<lanes>R<reads per thread>[P<ramp 0|1>]
+            l_, r_ = tok[1:].split("R")
+            ramp, guided = 0, 1
+            if "G" in r_:
+                r_, g_ = r_.split("G")
+                guided = int(g_)
+            if "P" in r_:
+                r_, p_ = r_.split("P")
+                ramp = int(p_)
+            m.set_option("ramp", ramp)
+            m.set_option("guided", guided)
+            return tok, 1, int(r_), int(l_)
+        v = int(tok)
+        return v, min(v, 1), (v - 100 if v >= 100 else 2), 0
+    dyns = []
+    for tok in args.dynamic.split(","):
+        dyn, dflag, rpt, lanes = parse_dyn(tok)
+        dyns.append(dyn)
+    for tok in args.dynamic.split(","):
+        dyn, dflag, rpt, lanes = parse_dyn(tok)
+        m.set_option("dynamic", dflag)
+        m.set_option("dyn_reads_per_lane", rpt)
+        m.set_option("lanes", lanes)
         t = time.time()
         ix = m.MoniIndex(prefix, gpus=[0])
         load_s = time.time() - t
         m.set_option("dynamic", 2)
+        m.set_option("lanes", 0)
         try:
             ix.maxrimal_exact_matches_packed(h_seqs, h_offs, out=(mo, rec))
             t = time.perf_counter()
