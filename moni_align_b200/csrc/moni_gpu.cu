@@ -576,9 +576,10 @@ namespace {
 thread_local std::string g_err;
 std::atomic<uint64_t> g_launches{0};
 std::atomic<bool> g_widen_ready{false};   // the widening pool has the size option "widen_threads" asks for
-std::atomic<int> g_dyn_rpt{2};            // option "dyn_reads_per_lane": reads per thread the persistent kernels are sized for
+std::atomic<int> g_dyn_rpt{3};            // option "dyn_reads_per_lane": reads per thread the persistent kernels are sized for
 std::atomic<int> g_ramp{0};               // option "ramp": 0 off (default: measured no better on 1 M ONT-like reads), 1 on, 2 = for batches of long reads
-std::atomic<int> g_guided{1};             // option "guided": chunks shrink towards the end of a batch of long reads
+std::atomic<int> g_guided{0};             // option "guided": chunks shrink towards the end of a batch of long reads (default off: measured
+                                          // 5.8 against 9.6 G bases/s on 1 M ONT-like reads -- small chunks make small, latency-bound kernels)
 std::atomic<bool> g_count{false};   // "count" option: read at every launch, so it can be toggled on a loaded index
 
 struct Options {
@@ -858,7 +859,7 @@ void launch_prepare(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
 }
 
 // Blocks of a persistent kernel: at most one resident wave, and few enough that a thread takes several reads of the chunk ("dyn_reads_per_lane",
-// default 2).  A read is a chain of dependent steps, so a kernel with as many threads as reads lasts as long as its longest read while the
+// default 3).  A read is a chain of dependent steps, so a kernel with as many threads as reads lasts as long as its longest read while the
 // threads of the short ones idle (ONT-like reads: longest 24.8 kbp, mean 10 kbp -> 40 % of the thread-steps used); with the reads handed out
 // longest first and fewer threads than reads, a thread that finishes early takes another read and the threads end together.  The chains in
 // flight that the memory system needs come from the lanes' kernels running side by side.
@@ -1420,10 +1421,8 @@ uint64_t run_batch(moni_gpu_index* idx, int mode, const char* seqs, const uint64
     // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
     // would cut a 1 G-base batch into two chunks and leave lanes (and the copy/compute overlap) unused, so the minimum shrinks
     // until the batch makes at least two chunks per lane.
-    // Lanes: option "lanes", or by default 4 for short reads and 6 for long ones -- a long read is a long chain of dependent steps, the
-    // persistent kernels run with fewer threads than reads, and what keeps the memory system busy is the number of reads in flight.
     const uint64_t mean_len = n_reads ? (offsets[n_reads] - offsets[0]) / n_reads : 0;
-    feed.lanes = idx->opt.lanes ? (int)idx->opt.lanes : (mean_len >= 4096 ? 6 : 4);
+    feed.lanes = idx->opt.lanes ? (int)idx->opt.lanes : 4;      // 6 and 8 lanes measured the same on 1 M ONT-like reads (profiles/r02_r_*)
     feed.guided = g_guided.load() != 0;
     feed.ramp = g_ramp.load() == 1 || (g_ramp.load() == 2 && mean_len >= 4096 && G == 1);
     feed.min_reads = std::min<uint64_t>(idx->opt.chunk_min_reads, std::max<uint64_t>(1024, n_reads / (2 * (uint64_t)feed.lanes * (uint64_t)G)));
@@ -1654,7 +1653,7 @@ int moni_gpu_index_load(const char* prefix, const int* gpus, int n_gpus, moni_gp
             CK(cudaSetDevice(R->dev));
             CK(cudaDeviceGetAttribute(&R->sms, cudaDevAttrMultiProcessorCount, R->dev));
             if (idx->opt.l2_fetch) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, idx->opt.l2_fetch));
-            R->lanes.resize(idx->opt.lanes ? idx->opt.lanes : 6);
+            R->lanes.resize(idx->opt.lanes ? idx->opt.lanes : 4);
             for (Lane& L : R->lanes) CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
             cudaStream_t st = R->stream();
             const Replica* src = g ? idx->reps[0].get() : nullptr;      // replica 0 is complete (synchronized) by now
