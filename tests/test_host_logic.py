@@ -354,3 +354,14 @@ def test_runs_expand_rebuilds_the_reference_vectors(case):
     bad[0] = 1
     with pytest.raises(m.MoniGpuError):
         m.expand_runs(offs, ro, bad, ln[at].astype(np.uint32), ptr[at])
+
+
+def test_host_widening_of_packed_results(tmp_path):
+    """csrc/host_widen.cpp (moni_gpu_mems / moni_gpu_ms: results cross the link packed and host threads widen them into the u64
+    columns): every record format, misaligned destinations, pool sizes 0..5, wrapped 40-bit pointers -- compiled with g++ and run here."""
+    import subprocess
+    exe = str(tmp_path / "host_widen_test")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-pthread", os.path.join(ROOT, "tests", "host_widen_test.cpp"),
+                           os.path.join(ROOT, "moni_align_b200", "csrc", "host_widen.cpp"), "-o", exe])
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.strip() == "ok", out.stdout + out.stderr
