@@ -414,7 +414,7 @@ def ours_arm(args) -> None:
     same = {"mems_u64": bool(np.array_equal(h_mo, mo) and np.array_equal(pool_a[:n_mems], mp) and np.array_equal(pool_b[:n_mems], ml))}
     gpu_mems = (h_mo.copy(), pool_a[:n_mems].copy(), pool_b[:n_mems].copy())      # for the parity sample: what the ABI call returned
     # A/B of the same call with the u64 columns crossing the link as they are (option widen_threads = 0) instead of packed + widened by host threads
-    if widen_threads > 0:
+    if widen_threads >= 2:
         h_mo[:] = 0
         m.set_option("widen_threads", 0)
         try:
@@ -438,7 +438,7 @@ def ours_arm(args) -> None:
     legs["ms_u64"] = e2e_leg(ix.matching_statistics, (pool_a, pool_b))
     same["ms_u64"] = bool(np.array_equal(pool_a[:total], r_ptr) and np.array_equal(pool_b[:total], r_len))
     gpu_ms = (pool_a[:total].copy(), pool_b[:total].copy()) if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
-    if widen_threads > 0:
+    if widen_threads >= 6:
         m.set_option("widen_threads", 0)
         try:
             legs["ms_u64_link"] = e2e_leg(ix.matching_statistics, (pool_a, pool_b))
@@ -541,10 +541,10 @@ def ours_arm(args) -> None:
     value_ms = all_reads * args.steps / (dev_ms_ms / 1e3)
     rate = lambda leg: all_reads * args.steps / (legs[leg]["wall"] / 1e3)
     stage_names = ["h2d", "pass1", "pass2", "compact", "d2h", "total"]
-    link_rec = 16 if widen_threads == 0 else (2 if int(read_len) < 256 else 4 if int(read_len) < 65536 else 8)   # bytes per record that cross the link
+    link_rec = 16 if widen_threads < 2 else (2 if int(read_len) < 256 else 4 if int(read_len) < 65536 else 8)   # bytes per record that cross the link
     d2h = {"mems_u64": 8 * (n_reads + 1) + link_rec * n_mems, "mems_u64_link": 8 * (n_reads + 1) + 16 * n_mems, "mems_u32": 8 * (n_reads + 1) + 8 * n_mems,
            "mems_packed32": 8 * (n_reads + 1) + 4 * n_mems, "mems_packed16": 8 * (n_reads + 1) + 2 * n_mems,
-           "ms_u64": (7 if widen_threads > 0 and int(read_len) < 65536 else 16) * total, "ms_u64_link": 16 * total, "ms_packed": 7 * total, "ms_runs": 8 * (n_reads + 1) + 16 * n_runs,
+           "ms_u64": (7 if widen_threads >= 6 and int(read_len) < 65536 else 16) * total, "ms_u64_link": 16 * total, "ms_packed": 7 * total, "ms_runs": 8 * (n_reads + 1) + 16 * n_runs,
            "ms_runs_packed": 8 * (n_reads + 1) + 9 * n_runs}
     api = API_NAMES
     h2d = int(total)            # reads of one length: the library computes their offsets on the device (k_uniform_offsets)
@@ -621,7 +621,8 @@ def ours_arm(args) -> None:
         **{"e2e_" + k: leg_json(k) for k in legs if k.startswith("mems_") and k != "mems_u64"},
         "ms": {"value": value_ms, "unit": "reads/s", "bases_per_s": value_ms * read_len, "ms_per_step": dev_ms_ms / args.steps,
                "stage_ms_per_step": {"pass1": kms_ms[0] / args.steps, "pass2": kms_ms[1] / args.steps, "expand": kms_ms[2] / args.steps},
-               "e2e": {**leg_json("ms_u64"), "host_widen_threads": widen_threads, "host_bytes_per_base": 16},
+               "e2e": {**leg_json("ms_u64"), "host_widen_threads": widen_threads if widen_threads >= 6 else 0, "host_bytes_per_base": 16,
+                       "note": "moni_gpu_ms widens on the host from 7 bytes per base when the pool has 6 threads or more"},
                **({"e2e_u64_link": leg_json("ms_u64_link")} if "ms_u64_link" in legs else {}), "e2e_packed": leg_json("ms_packed"), "e2e_runs": leg_json("ms_runs"),
                "e2e_runs_packed": leg_json("ms_runs_packed"), "runs_per_step": n_runs},
         "mem_records_per_step": n_mems,

@@ -162,7 +162,7 @@ int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
  * "grammar" ("plain" = <prefix>.plain.slp, falling back to <prefix>.slp when only that exists; "shaped" = <prefix>.slp, the file `-q` names,
  * SelfShapedSlp::load, thirdparty/ShapedSlp/SelfShapedSlp.hpp:378-397; default "plain"),
  * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
- * "chunk_bases" (bases per device chunk, default 2^24) and "chunk_min_reads" (a chunk is not closed before it holds this many reads, default 98304, less when reads are long enough that it would leave lanes idle; hard cap 2^30 bases, less when free HBM is short), "dynamic" (0 = one read per lane, 1 = persistent kernels whose lanes pull reads, 2 = pull for ragged chunks; default 2), "dyn_reads_per_lane" (reads per thread the persistent kernels are sized for, default 3: fewer threads than reads, so that lanes that finish a short read take another; applies at once), "lanes" (chunks in flight per GPU, 1..8; default 0 = 4), "widen_threads" (moni_gpu_mems and moni_gpu_ms: host threads that widen the results, which then cross the link in 2 / 4 / 8 bytes per record resp. 7 bytes per base, into the u64 columns; 0 = off, the u64 columns cross the link; -1 = auto, the default: two thirds of the CPUs the process may run on, at most 16, off below 4 CPUs; applies at once), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
+ * "chunk_bases" (bases per device chunk, default 2^24) and "chunk_min_reads" (a chunk is not closed before it holds this many reads, default 98304, less when reads are long enough that it would leave lanes idle; hard cap 2^30 bases, less when free HBM is short), "dynamic" (0 = one read per lane, 1 = persistent kernels whose lanes pull reads, 2 = pull for ragged chunks; default 2), "dyn_reads_per_lane" (reads per thread the persistent kernels are sized for, default 3: fewer threads than reads, so that lanes that finish a short read take another; applies at once), "lanes" (chunks in flight per GPU, 1..8; default 0 = 4), "widen_threads" (moni_gpu_mems and moni_gpu_ms: host threads that widen the results, which then cross the link in 2 / 4 / 8 bytes per record resp. 7 bytes per base, into the u64 columns; 0 = off, the u64 columns cross the link; -1 = auto, the default: two thirds of the CPUs the process may run on, at most 16, off below 4 CPUs; moni_gpu_mems widens with 2 threads or more, moni_gpu_ms with 6 or more; applies at once), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
 int moni_gpu_set_option(const char* key, const char* value);
 /* Environment: MONI_GPU_VERBOSE=1 prints the exporter's and the index load's phase times on stderr (as option "verbose");
  * MONI_GPU_TRACE=1 prints a per-chunk timeline of every call. */

@@ -1417,7 +1417,10 @@ uint64_t run_batch(moni_gpu_index* idx, int mode, const char* seqs, const uint64
     feed.n_reads = n_reads;
     feed.chunk_bases = idx->opt.chunk_bases;
     feed.workers = G;
-    feed.widen = ((mode == kModeMems && out.fmt == 8) || (mode == kModeMs && out.fmt != 7)) && widen_pool_threads() > 0;
+    // measured on the bench boxes: a widening thread writes 9-15 GB/s; two of them beat 16-byte records on a shared link, moni_gpu_ms
+    // (4.8 GB written per 2 M reads against 2.7 GB less on the link) needs six
+    const int wt = ((mode == kModeMems && out.fmt == 8) || (mode == kModeMs && out.fmt != 7)) ? widen_pool_threads() : 0;
+    feed.widen = mode == kModeMems ? wt >= 2 : wt >= 6;
     // A chunk is kept open until it holds chunk_min_reads reads so that its kernels fill the GPU; with long reads that rule alone
     // would cut a 1 G-base batch into two chunks and leave lanes (and the copy/compute overlap) unused, so the minimum shrinks
     // until the batch makes at least two chunks per lane.

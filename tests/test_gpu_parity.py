@@ -742,7 +742,7 @@ def test_mems_u64_widened_on_host_equals_link_copy(m, oracle_mod):
     want = orc.mems(flat, offs)
     want_ms = orc.ms(flat, offs)
     try:
-        for threads in (0, 3, 1, -1):
+        for threads in (0, 3, 7, 1, -1):      # moni_gpu_mems widens from 2 threads, moni_gpu_ms from 6
             m.set_option("widen_threads", threads)
             for ix in (one, three):
                 got = ix.maxrimal_exact_matches(flat, offs)
@@ -754,7 +754,7 @@ def test_mems_u64_widened_on_host_equals_link_copy(m, oracle_mod):
         names, seqs = read_fastq(os.path.join(GOLDEN, "withN.fq"))
         wflat, woffs = pack(seqs)
         wn = m.MoniIndex(os.path.join(GOLDEN, "withN.fa"))
-        for threads in (0, 2):
+        for threads in (0, 6):
             m.set_option("widen_threads", threads)
             p2, l2 = wn.matching_statistics(wflat, woffs)
             assert m.format_ms(names, woffs, p2) == open(os.path.join(GOLDEN, "withN.pointers"), "rb").read()
