@@ -158,11 +158,32 @@ int moni_gpu_counters(moni_gpu_index* idx, uint64_t c[8], int reset);
  * t[4]=device->host copies, t[5]=whole call (first copy to last copy). */
 int moni_gpu_timing(const moni_gpu_index* idx, double t[6]);
 
-/* Options ("leaf_len", "max_scan", "chunk_bases" apply to indexes loaded afterwards; "count" and "verbose" apply at once): "leaf_len" (grammar literal block length; default 0 = auto: the whole text as one literal block if it fits "text_budget" bytes, default 64 GiB, else 128),
- * "grammar" ("plain" = <prefix>.plain.slp, falling back to <prefix>.slp when only that exists; "shaped" = <prefix>.slp, the file `-q` names,
- * SelfShapedSlp::load, thirdparty/ShapedSlp/SelfShapedSlp.hpp:378-397; default "plain"),
- * "max_scan" (move-table balancing target, default 8), "verbose" (0/1), "count" (0/1),
- * "chunk_bases" (bases per device chunk, default 2^24) and "chunk_min_reads" (a chunk is not closed before it holds this many reads, default 98304, less when reads are long enough that it would leave lanes idle; hard cap 2^30 bases, less when free HBM is short), "dynamic" (0 = one read per lane, 1 = persistent kernels whose lanes pull reads, 2 = pull for ragged chunks; default 2), "dyn_reads_per_lane" (reads per thread the persistent kernels are sized for, default 3: fewer threads than reads, so that lanes that finish a short read take another; applies at once), "lanes" (chunks in flight per GPU, 1..8; default 0 = 4), "widen_threads" (moni_gpu_mems and moni_gpu_ms: host threads that widen the results, which then cross the link in 2 / 4 / 8 bytes per record resp. 7 bytes per base, into the u64 columns; 0 = off, the u64 columns cross the link; -1 = auto, the default: two thirds of the CPUs the process may run on, at most 16, off below 4 CPUs; moni_gpu_mems widens with 2 threads or more, moni_gpu_ms with 6 or more; applies at once), "l2_fetch" (cudaLimitMaxL2FetchGranularity hint; 0 = device default). */
+/* Options.  "leaf_len", "text_budget", "max_scan", "grammar", "chunk_bases", "chunk_min_reads", "lanes", "dynamic", "l2_fetch" apply to
+ * indexes loaded afterwards; the others apply at once.
+ *   index image
+ *     "leaf_len"      grammar literal block length; default 0 = auto: the whole text as one literal block if it fits "text_budget"
+ *                     bytes (default 64 GiB), else 128
+ *     "grammar"       "plain" = <prefix>.plain.slp, falling back to <prefix>.slp when only that exists; "shaped" = <prefix>.slp, the
+ *                     file `-q` names (SelfShapedSlp::load, thirdparty/ShapedSlp/SelfShapedSlp.hpp:378-397); default "plain"
+ *     "max_scan"      move-table balancing target, default 8
+ *   batching
+ *     "chunk_bases"   bases per device chunk, default 2^24
+ *     "chunk_min_reads"  a chunk is not closed before it holds this many reads, default 98304 (less when the batch has too few reads to
+ *                     give every lane two chunks); hard cap 2^30 bases, less when free HBM is short
+ *     "lanes"         chunks in flight per GPU, 1..8; default 0 = 4
+ *     "guided", "ramp"   chunk-size schedules for batches of long reads, both off by default (measured no better)
+ *   kernels
+ *     "dynamic"       0 = one read per lane, 1 = persistent kernels whose lanes pull reads, 2 = pull for ragged chunks; default 2
+ *     "dyn_reads_per_lane"  reads per thread the persistent kernels are sized for, default 2: fewer threads than reads, so that lanes
+ *                     that finish a short read take another
+ *     "l2_fetch"      cudaLimitMaxL2FetchGranularity hint; 0 = device default
+ *   results
+ *     "widen_threads" moni_gpu_mems and moni_gpu_ms: host threads that widen the results -- which then cross the link in 2 / 4 / 8 bytes
+ *                     per record resp. 7 bytes per base -- into the u64 columns.  0 = off (the u64 columns cross the link); -1 = auto,
+ *                     the default: two thirds of the CPUs the process may run on, at most 16, off below 4 CPUs.  moni_gpu_mems widens
+ *                     with 2 pool threads or more, moni_gpu_ms with 6 or more
+ *   diagnostics
+ *     "verbose" (0/1), "count" (0/1: event counters, moni_gpu_counters) */
 int moni_gpu_set_option(const char* key, const char* value);
 /* Environment: MONI_GPU_VERBOSE=1 prints the exporter's and the index load's phase times on stderr (as option "verbose");
  * MONI_GPU_TRACE=1 prints a per-chunk timeline of every call. */

@@ -87,7 +87,8 @@ def load_library() -> ctypes.CDLL:
     L.moni_gpu_ms_runs.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, _u64p, ctypes.c_uint64]
     L.moni_gpu_ms_runs_packed.argtypes = [vp, vp, _u64p, ctypes.c_uint64, _u64p, vp, vp, vp, ctypes.c_uint64]
     L.moni_gpu_ms_runs_expand.argtypes = [_u64p, ctypes.c_uint64, _u64p, vp, vp, _u64p, _u64p, _u64p]
-    L.moni_gpu_ms_noalloc.argtypes = [vp, ci, vp, vp, ctypes.c_uint64, ctypes.c_uint64, vp, vp, vp]
+    if hasattr(L, "moni_gpu_ms_noalloc"):        # absent from A/B builds of older trees (MONI_GPU_LIB)
+        L.moni_gpu_ms_noalloc.argtypes = [vp, ci, vp, vp, ctypes.c_uint64, ctypes.c_uint64, vp, vp, vp]
     L.moni_gpu_batch_create.argtypes = [vp, ci, vp, _u64p, ctypes.c_uint64, ctypes.POINTER(vp)]
     L.moni_gpu_batch_run.argtypes = [vp, ci, ctypes.POINTER(ctypes.c_float)]
     L.moni_gpu_batch_fetch_ms.argtypes = [vp, _u64p, _u64p]

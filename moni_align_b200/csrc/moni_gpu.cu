@@ -576,7 +576,7 @@ namespace {
 thread_local std::string g_err;
 std::atomic<uint64_t> g_launches{0};
 std::atomic<bool> g_widen_ready{false};   // the widening pool has the size option "widen_threads" asks for
-std::atomic<int> g_dyn_rpt{3};            // option "dyn_reads_per_lane": reads per thread the persistent kernels are sized for
+std::atomic<int> g_dyn_rpt{2};            // option "dyn_reads_per_lane": reads per thread the persistent kernels are sized for
 std::atomic<int> g_ramp{0};               // option "ramp": 0 off (default: measured no better on 1 M ONT-like reads), 1 on, 2 = for batches of long reads
 std::atomic<int> g_guided{0};             // option "guided": chunks shrink towards the end of a batch of long reads (default off: measured
                                           // 5.8 against 9.6 G bases/s on 1 M ONT-like reads -- small chunks make small, latency-bound kernels)
@@ -859,7 +859,7 @@ void launch_prepare(Scratch& S, const ChunkPlan& p, cudaStream_t st) {
 }
 
 // Blocks of a persistent kernel: at most one resident wave, and few enough that a thread takes several reads of the chunk ("dyn_reads_per_lane",
-// default 3).  A read is a chain of dependent steps, so a kernel with as many threads as reads lasts as long as its longest read while the
+// default 2).  A read is a chain of dependent steps, so a kernel with as many threads as reads lasts as long as its longest read while the
 // threads of the short ones idle (ONT-like reads: longest 24.8 kbp, mean 10 kbp -> 40 % of the thread-steps used); with the reads handed out
 // longest first and fewer threads than reads, a thread that finishes early takes another read and the threads end together.  The chains in
 // flight that the memory system needs come from the lanes' kernels running side by side.

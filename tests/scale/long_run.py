@@ -132,13 +132,19 @@ def main():
     for tok in args.dynamic.split(","):
         dyn, dflag, rpt, lanes = parse_dyn(tok)
         m.set_option("dynamic", dflag)
-        m.set_option("dyn_reads_per_lane", rpt)
-        m.set_option("lanes", lanes)
+        for k_, v_ in (("dyn_reads_per_lane", rpt), ("lanes", lanes)):
+            try:
+                m.set_option(k_, v_)
+            except m.MoniGpuError:          # an A/B library of an older tree (MONI_GPU_LIB) does not know the option
+                pass
         t = time.time()
         ix = m.MoniIndex(prefix, gpus=[0])
         load_s = time.time() - t
         m.set_option("dynamic", 2)
-        m.set_option("lanes", 0)
+        try:
+            m.set_option("lanes", 0)
+        except m.MoniGpuError:
+            pass
         try:
             ix.maxrimal_exact_matches_packed(h_seqs, h_offs, out=(mo, rec))
             t = time.perf_counter()
