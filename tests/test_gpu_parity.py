@@ -695,6 +695,34 @@ def test_dynamic_and_static_kernels_agree(case, m, oracle_mod):
     assert all(np.array_equal(x, y) for x, y in zip(res[1][1], wm))
 
 
+def test_chunk_schedules_keep_the_bits(m, oracle_mod):
+    """The chunk-size schedules (options "ramp": shorter first chunks, "guided": chunks that shrink towards the end of the batch), the
+    number of chunks in flight ("lanes") and the sizing of the persistent kernels change how a batch is cut and run, never what comes
+    back: ragged reads over many small chunks, every combination against the oracle."""
+    import synth
+    pre = os.path.join(GOLDEN, "pan4.fa")
+    orc = oracle_mod.OracleIndex(pre)
+    text = np.array([orc.char_at(i) for i in range(orc.text_len)], dtype=np.uint8)
+    reads = synth.long_reads(text, 400, 41, mean=900, sd=500, lo=1, hi=3000)
+    reads += [r for r in synth.short_reads(text, 1500, 80, 42, err=0.04)]
+    reads.insert(100, np.zeros(0, np.uint8))
+    flat, offs = m.pack_reads(reads)
+    want_ms, want_mems = orc.ms(flat, offs), orc.mems(flat, offs)
+    try:
+        for ramp, guided, lanes, rpt in ((1, 0, 0, 2), (0, 1, 3, 1), (1, 1, 8, 4), (2, 1, 1, 2)):
+            for k, v in (("ramp", ramp), ("guided", guided), ("lanes", lanes), ("dyn_reads_per_lane", rpt), ("chunk_bases", 20_000), ("chunk_min_reads", 64)):
+                m.set_option(k, v)
+            ix = m.MoniIndex(pre)
+            got = ix.matching_statistics(flat, offs)
+            assert np.array_equal(got[0], want_ms[0]) and np.array_equal(got[1], want_ms[1]), (ramp, guided, lanes, rpt)
+            gm = ix.maxrimal_exact_matches(flat, offs)
+            assert all(np.array_equal(x, y) for x, y in zip(gm, want_mems)), (ramp, guided, lanes, rpt)
+            ix.close()
+    finally:
+        for k, v in (("ramp", 0), ("guided", 0), ("lanes", 0), ("dyn_reads_per_lane", 2), ("chunk_bases", 1 << 24), ("chunk_min_reads", 96 * 1024)):
+            m.set_option(k, v)
+
+
 @pytest.mark.parametrize("case", CASES)
 def test_populate_seeds_equals_reference(case, m, oracle_mod, tmp_path):
     """moni_gpu_seeds + moni_gpu_populate_seeds on the `moni align` index == the reference's find_mems + populate_seeds with seed
