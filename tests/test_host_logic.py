@@ -365,3 +365,20 @@ def test_host_widening_of_packed_results(tmp_path):
                            os.path.join(ROOT, "moni_align_b200", "csrc", "host_widen.cpp"), "-o", exe])
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0 and out.stdout.strip() == "ok", out.stdout + out.stderr
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/moni_gpu.h is the drop-in boundary: it must compile as strict C99 (plain pointers and sizes, no C++ or torch types), and
+    a C program must link against the library with nothing but the header."""
+    import subprocess
+    src = tmp_path / "abi.c"
+    src.write_text('#include "moni_gpu.h"\n#include <stdio.h>\n'
+                   'int main(void) { moni_gpu_index* ix = 0; int rc = moni_gpu_index_load("/nonexistent/prefix", 0, 1, &ix);\n'
+                   '  printf("%d %s\\n", rc, moni_gpu_version()); return rc == 0; }\n')
+    exe = str(tmp_path / "abi")
+    lib_dir = os.path.join(ROOT, "moni_align_b200")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), str(src), "-o", exe,
+                           "-L", lib_dir, "-lmoni_gpu", "-Wl,-rpath," + lib_dir])
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr          # the load fails (no such index, or no device here): an error code, not a crash
+    assert out.stdout.split()[0].startswith("-") and "moni-gpu" in out.stdout
