@@ -406,7 +406,7 @@ def ours_arm(args) -> None:
         widen_threads = 0 if allowed_cpus < 4 else min(16, allowed_cpus * 2 // 3)     # WidenPool::default_threads (csrc/host_widen.cpp)
         if world > 1:
             # the ranks of one box share its CPUs and the library cannot see its sibling processes: give each rank its share
-            widen_threads = max(1, min(10, (allowed_cpus - world) // world)) if allowed_cpus // world >= 2 else 0     # one CPU per rank stays with its caller thread
+            widen_threads = max(1, min(8, (allowed_cpus - 2 * world) // world)) if allowed_cpus // world >= 2 else 0     # one CPU per rank stays with its caller thread
             m.set_option("widen_threads", widen_threads)
     legs = {}
     # mems, u64 records: the reference's own record type (std::pair<size_t,size_t>, src/mems.cpp:277-279)
